@@ -1,0 +1,1 @@
+from . import distributed  # noqa: F401

@@ -1,0 +1,1 @@
+from . import parallel  # noqa: F401

@@ -1,0 +1,117 @@
+"""Process-group plumbing and the two gradient-communication backends.
+
+``init_process_group`` keeps the reference's call (ref:restnet_ddp.py:94:
+``backend='nccl', init_method='tcp://ip:port', world_size, rank``); torch's TCPStore does the
+bootstrap (torch:distributed/rendezvous.py:162-239).  On top of the group sit two
+interchangeable backends for the arena collectives DDP needs:
+
+* ``TorchComm``  — ``torch.distributed`` calls on arena slices (gloo on CPU; NCCL as the
+  *labelled baseline* on GPU, ``--backend nccl``).
+* ``NativeComm`` — (parallel/symm.py) symmetric-memory arenas + our sm_100a peer-memory
+  kernels (K1–K3, K5); the product path on a multi-GPU box.
+"""
+from __future__ import annotations
+
+import datetime
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+
+def init_process_group(backend: str = "nccl", init_method: Optional[str] = None, world_size: int = -1,
+                       rank: int = -1, timeout: Optional[datetime.timedelta] = None, **kw):
+    if backend == "nccl" and not torch.cuda.is_available():
+        backend = "gloo"          # CPU plumbing path (BASELINE.json config 1)
+    if timeout is None:
+        timeout = datetime.timedelta(minutes=10)   # ProcessGroupNCCL.hpp:156-157 default
+    return dist.init_process_group(backend=backend, init_method=init_method, world_size=world_size,
+                                   rank=rank, timeout=timeout, **kw)
+
+
+def get_rank() -> int:
+    return dist.get_rank() if dist.is_initialized() else 0
+
+
+def get_world_size() -> int:
+    return dist.get_world_size() if dist.is_initialized() else 1
+
+
+def is_initialized() -> bool:
+    return dist.is_available() and dist.is_initialized()
+
+
+def destroy_process_group() -> None:
+    if is_initialized():
+        dist.destroy_process_group()
+
+
+def reduce(tensor: torch.Tensor, dst: int = 0, op=None, group=None):
+    """``dist.reduce(x, 0)`` of the validation loop (ref:restnet_ddp.py:63-64)."""
+    if not is_initialized() or get_world_size() == 1:
+        return None
+    return dist.reduce(tensor, dst, op=op if op is not None else dist.ReduceOp.SUM, group=group)
+
+
+class TorchComm:
+    """Arena collectives through torch.distributed (gloo / NCCL)."""
+
+    name = "torch"
+    fuses_unscale = False
+
+    def __init__(self, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group) if is_initialized() else 1
+        self.rank = dist.get_rank(group) if is_initialized() else 0
+        self._works: List = []
+
+    def register_arena(self, arena) -> None:      # nothing to map
+        return None
+
+    def broadcast_(self, flat: torch.Tensor, src: int = 0) -> None:
+        if self.world > 1:
+            dist.broadcast(flat, src, group=self.group)
+
+    def allreduce_range(self, flat: torch.Tensor, start: int, end: int, *, average: bool = True,
+                        wire_dtype: Optional[torch.dtype] = None, inv_scale=None, found_inf=None) -> None:
+        if self.world == 1:
+            return
+        seg = flat[start:end]
+        if wire_dtype is not None and wire_dtype != seg.dtype:
+            # fp16/bf16_compress_hook semantics (torch:distributed/algorithms/ddp_comm_hooks/
+            # default_hooks.py:57-134): cast, pre-divide, reduce, copy back.
+            wire = seg.to(wire_dtype)
+            if average:
+                wire.div_(self.world)
+            work = dist.all_reduce(wire, group=self.group, async_op=True)
+            self._works.append((work, seg, wire))
+        else:
+            if average:
+                seg.div_(self.world)
+            work = dist.all_reduce(seg, group=self.group, async_op=True)
+            self._works.append((work, None, None))
+
+    def wait_all(self) -> None:
+        for work, seg, wire in self._works:
+            work.wait()
+            if seg is not None:
+                seg.copy_(wire)
+        self._works.clear()
+
+
+def make_comm(backend: str = "auto", group=None):
+    """auto: native on multi-GPU CUDA with symmetric memory available, else torch."""
+    if backend in ("nccl", "gloo", "torch"):
+        return TorchComm(group)
+    want_native = backend == "native"
+    if torch.cuda.is_available() and is_initialized() and dist.get_backend(group) == "nccl" \
+            and dist.get_world_size(group) > 1:
+        try:
+            from .symm import NativeComm
+            return NativeComm(group)
+        except Exception:
+            if want_native:
+                raise
+    elif want_native and is_initialized() and dist.get_world_size(group) > 1:
+        raise RuntimeError("backend='native' needs CUDA + an NCCL process group for the bootstrap")
+    return TorchComm(group)

@@ -1,0 +1,78 @@
+"""Top-level functions for spawned children (must be importable by name)."""
+import os
+import time
+
+import torch
+
+
+def tiny_cfg(mode, **kw):
+    from pytorch_distributed_b200.config import TrainConfig
+    base = dict(mode=mode, epochs=1, batch_size=4, max_steps=3, max_val_steps=1, image_size=32, num_classes=10,
+                train_samples=64, val_samples=16, width=8, layers=(1, 1, 1, 1), device="cpu", num_workers=0)
+    base.update(kw)
+    return TrainConfig(**base)
+
+
+def child_ok(rank, out_dir):
+    with open(os.path.join(out_dir, f"ok{rank}"), "w") as f:
+        f.write(str(rank))
+
+
+def child_raises(rank):
+    if rank == 1:
+        raise ValueError("boom from rank 1")
+    time.sleep(30)
+
+
+def child_killed(rank):
+    if rank == 0:
+        os.kill(os.getpid(), 9)
+    time.sleep(30)
+
+
+def child_suspends(rank):
+    from pytorch_distributed_b200 import suspend
+    if rank == 0:
+        suspend.go_suspend()
+    time.sleep(30)
+
+
+def ddp_worker(rank, world, port, out_dir, use_ours, steps, sync_bn=False):
+    import torch.distributed as dist
+    from pytorch_distributed_b200.models import ResNet
+    from pytorch_distributed_b200.optim import SGD
+    from pytorch_distributed_b200.parallel import DistributedDataParallel, convert_sync_batchnorm
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", world_size=world, rank=rank)
+    torch.manual_seed(1234 + rank)          # different init per rank: the ctor broadcast must fix it
+    model = ResNet((1, 1, 1, 1), num_classes=10, width=8)
+    if sync_bn:
+        model = convert_sync_batchnorm(model) if use_ours else torch.nn.SyncBatchNorm.convert_sync_batchnorm(model)
+    if use_ours:
+        ddp = DistributedDataParallel(model)
+        opt = SGD(ddp.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
+    else:
+        ddp = torch.nn.parallel.DistributedDataParallel(model)
+        opt = torch.optim.SGD(ddp.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
+    g = torch.Generator().manual_seed(99)
+    xs = torch.randn(steps, world, 4, 3, 32, 32, generator=g)
+    ys = torch.randint(0, 10, (steps, world, 4), generator=g)
+    losses = []
+    for s in range(steps):
+        out = ddp(xs[s, rank])
+        opt.zero_grad()
+        loss = torch.nn.functional.cross_entropy(out, ys[s, rank])
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    flat = torch.cat([p.detach().reshape(-1) for p in ddp.module.parameters()])
+    bufs = torch.cat([b.detach().float().reshape(-1) for b in ddp.module.buffers()])
+    torch.save({"losses": losses, "params": flat.clone(), "bufs": bufs.clone()},
+               os.path.join(out_dir, f"{'ours' if use_ours else 'torch'}_{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def harness_worker(rank, cfg):
+    from pytorch_distributed_b200 import harness
+    torch.set_num_threads(1)
+    harness.main(cfg, rank)

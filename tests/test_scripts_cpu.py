@@ -1,0 +1,86 @@
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from pytorch_distributed_b200 import harness, launcher, suspend
+from pytorch_distributed_b200.suspend import SUSPEND_EXIT_CODE
+
+from . import _mp_helpers as H
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TINY = ["--device", "cpu", "--epochs", "1", "--batch-size", "4", "--steps", "3", "--val-steps", "1",
+        "--image-size", "32", "--num-classes", "10", "--train-samples", "64", "--val-samples", "16",
+        "--width", "8", "--workers", "0"]
+
+
+def _run(script, extra, env=None, timeout=600):
+    e = dict(os.environ, OMP_NUM_THREADS="1", **(env or {}))
+    return subprocess.run([sys.executable, os.path.join(ROOT, script), *TINY, *extra], cwd=ROOT, env=e,
+                          capture_output=True, text=True, timeout=timeout)
+
+
+def test_shims_import():
+    import hf_env
+    import hfai
+    import hfai.nccl.distributed as hdist
+    from hfai.nn.parallel import DistributedDataParallel
+    hf_env.set_env("202111")
+    assert hf_env.requested_env == "202111"
+    assert hfai.client.receive_suspend_command() is False
+    assert callable(hfai.go_suspend) and callable(hfai.client.go_suspend)      # quirk Q2
+    assert callable(hfai.multiprocessing.spawn) and callable(hdist.init_process_group)
+    assert DistributedDataParallel.__name__ == "DistributedDataParallel"
+    ds = hfai.datasets.ImageNet(split="val", transform=None, num_samples=8, image_size=8)
+    assert hasattr(ds, "loader") and len(ds) == 8
+
+
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("script,extra", [
+    ("resnet_single_gpu.py", []),
+    ("resnet_dp.py", ["--gpus", "2"]),
+    ("restnet_ddp.py", ["--gpus", "2"]),
+    ("resnet_ddp_apex.py", ["--gpus", "2"]),
+])
+def test_entry_points_run(script, extra, tmp_path, free_port):
+    r = _run(script, [*extra, "--save-path", str(tmp_path)], env={"MASTER_PORT": str(free_port)})
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "cost time per epoch:" in r.stdout and "Acc1:" in r.stdout
+    assert r.stdout.count("cost time per epoch:") == 1          # rank-0-only print in the DDP modes
+
+
+def test_suspend_writes_latest_once_and_resume_continues(tmp_path):
+    cfg = H.tiny_cfg("single", save_path=str(tmp_path), max_steps=6)
+    sentinel = tmp_path / "suspend.flag"
+    os.environ[suspend.SENTINEL_ENV] = str(sentinel)
+    try:
+        sentinel.write_text("x")
+        with pytest.raises(SystemExit) as ei:
+            harness.main(cfg, 0)
+        assert ei.value.code == SUSPEND_EXIT_CODE and not sentinel.exists()
+        ck = torch.load(tmp_path / "latest.pt", map_location="cpu", weights_only=False)
+        assert (ck["epoch"], ck["step"]) == (0, 1)              # 'step' is the next step to run
+        steps_seen = []
+        orig = harness.to_device
+        harness.to_device = lambda b, d: (steps_seen.append(1), orig(b, d))[1]
+        try:
+            harness.main(cfg, 0)
+        finally:
+            harness.to_device = orig
+        assert len(steps_seen) == 5 + 1                         # steps 1..5 of the epoch + 1 val batch
+    finally:
+        os.environ.pop(suspend.SENTINEL_ENV, None)
+        suspend.clear()
+
+
+@pytest.mark.timeout(600)
+def test_ddp_suspend_only_rank0_saves(tmp_path, free_port):
+    sentinel = tmp_path / "s.flag"
+    sentinel.write_text("x")
+    env = {"MASTER_PORT": str(free_port), suspend.SENTINEL_ENV: str(sentinel)}
+    r = _run("restnet_ddp.py", ["--gpus", "2", "--save-path", str(tmp_path / "out")], env=env)
+    assert r.returncode == 0, r.stderr[-2000:]                  # suspend tears the group down cleanly
+    assert (tmp_path / "out" / "latest.pt").exists()
+    assert "cost time per epoch" not in r.stdout
