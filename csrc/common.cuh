@@ -1,0 +1,128 @@
+// Shared helpers for the sm_100a kernel library.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+
+#include "pdb200.h"
+
+namespace pdb {
+
+void set_error(const char* fmt, ...);   // defined in error.cu
+
+#define PDB_CHECK_ARG(cond, ...)            \
+  do {                                      \
+    if (!(cond)) {                          \
+      ::pdb::set_error(__VA_ARGS__);        \
+      return 1;                             \
+    }                                       \
+  } while (0)
+
+#define PDB_CUDA(expr)                                                                     \
+  do {                                                                                     \
+    cudaError_t e__ = (expr);                                                              \
+    if (e__ != cudaSuccess) {                                                              \
+      ::pdb::set_error("%s: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+      return 2;                                                                            \
+    }                                                                                      \
+  } while (0)
+
+#define PDB_LAUNCH_CHECK() PDB_CUDA(cudaGetLastError())
+
+inline int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+// ---- 16-bit element traits --------------------------------------------------------------
+template <typename T> struct Elem;
+template <> struct Elem<__nv_bfloat16> {
+  using T2 = __nv_bfloat162;
+  static __device__ __forceinline__ float2 to_f2(T2 v) { return __bfloat1622float2(v); }
+  static __device__ __forceinline__ T2 from_f2(float a, float b) { return __floats2bfloat162_rn(a, b); }
+  static __device__ __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
+  static __device__ __forceinline__ __nv_bfloat16 from_f(float v) { return __float2bfloat16_rn(v); }
+};
+template <> struct Elem<__half> {
+  using T2 = __half2;
+  static __device__ __forceinline__ float2 to_f2(T2 v) { return __half22float2(v); }
+  static __device__ __forceinline__ T2 from_f2(float a, float b) { return __floats2half2_rn(a, b); }
+  static __device__ __forceinline__ float to_f(__half v) { return __half2float(v); }
+  static __device__ __forceinline__ __half from_f(float v) { return __float2half_rn(v); }
+};
+
+// 8 x 16-bit = one 128-bit access
+struct alignas(16) Vec8 {
+  uint4 raw;
+};
+
+template <typename T>
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  using T2 = typename Elem<T>::T2;
+  const T2* h = reinterpret_cast<const T2*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = Elem<T>::to_f2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  using T2 = typename Elem<T>::T2;
+  uint4 v;
+  T2* h = reinterpret_cast<T2*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = Elem<T>::from_f2(f[2 * i], f[2 * i + 1]);
+  return v;
+}
+
+__device__ __forceinline__ uint4 ldg128(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+// streaming load: read-once data should not displace reusable lines in L1
+__device__ __forceinline__ uint4 ldg128_stream(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg128(void* p, const uint4& v) { *reinterpret_cast<uint4*>(p) = v; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// dispatch on the 16-bit dtype tag of the C ABI
+#define PDB_DISPATCH_16(dtype, T, ...)                         \
+  do {                                                         \
+    if ((dtype) == PDB_BF16) {                                 \
+      using T = __nv_bfloat16;                                 \
+      __VA_ARGS__;                                             \
+    } else if ((dtype) == PDB_FP16) {                          \
+      using T = __half;                                        \
+      __VA_ARGS__;                                             \
+    } else {                                                   \
+      ::pdb::set_error("unsupported dtype tag %d", (int)(dtype)); \
+      return 1;                                                \
+    }                                                          \
+  } while (0)
+
+}  // namespace pdb

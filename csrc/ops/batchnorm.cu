@@ -1,0 +1,438 @@
+// K8: BatchNorm (+ReLU, +residual) forward / backward on NHWC 16-bit activations, fp32 statistics.
+//
+// The delegate (cuDNN spatial-persistent BN + separate ATen ReLU / add kernels, torch:nn/modules/
+// batchnorm.py:144-210) makes 3-4 passes over the activation per BN layer.  Here:
+//   forward : statistics come out of the producing convolution's epilogue (or pdb_bn_stats), then ONE
+//             pass normalises, adds the residual and applies ReLU; the per-channel finalisation
+//             (mean/rstd, running-stat update) is done inside that pass's prologue, not in a launch
+//             of its own;
+//   backward: one reduction pass (ReLU mask folded in) and one apply pass that also emits the residual
+//             branch gradient and the dgamma/dbeta accumulation.
+// Layout [rows, C] with C contiguous: a thread owns 8 consecutive channels (one 128-bit access).
+#include "common.cuh"
+
+namespace pdb {
+
+constexpr int kThreads = 256;
+constexpr int kMaxC = 4096;
+
+// ------------------------------------------------------------------------------------------------
+// Channel reductions.  Block = cx channel-groups (8 ch each) x ry rows.
+// MODE 0: (sum x, sum x^2)           — forward statistics
+// MODE 1: (sum g, sum g*xhat), g = dz * (z>0)   — backward reductions
+template <typename T, int MODE, bool kHasZ>
+__device__ __forceinline__ void reduce_rows(const T* __restrict__ a, const T* __restrict__ z,
+                                            const T* __restrict__ x, int64_t rows, int C, int cg, int cx, int ry,
+                                            int ty, const float* __restrict__ mean, const float* __restrict__ rstd,
+                                            float (&s0)[8], float (&s1)[8]) {
+  float mu[8], rs[8];
+  if (MODE == 1) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      mu[k] = mean[cg * 8 + k];
+      rs[k] = rstd[cg * 8 + k];
+    }
+  }
+  for (int64_t r = (int64_t)blockIdx.x * ry + ty; r < rows; r += (int64_t)gridDim.x * ry) {
+    const int64_t off = r * C + (int64_t)cg * 8;
+    float fa[8];
+    unpack8<T>(ldg128_stream(a + off), fa);
+    if (MODE == 0) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        s0[k] += fa[k];
+        s1[k] = fmaf(fa[k], fa[k], s1[k]);
+      }
+    } else {
+      float fx[8];
+      unpack8<T>(ldg128_stream(x + off), fx);
+      if (kHasZ) {
+        float fz[8];
+        unpack8<T>(ldg128_stream(z + off), fz);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) fa[k] = fz[k] > 0.f ? fa[k] : 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        s0[k] += fa[k];
+        s1[k] = fmaf(fa[k], (fx[k] - mu[k]) * rs[k], s1[k]);
+      }
+    }
+  }
+}
+
+// Folds the per-thread accumulators over ty in shared memory; thread (ty==0) ends with the block total.
+__device__ __forceinline__ void block_fold(float (&s0)[8], float (&s1)[8], int tx, int ty, int cx, int ry,
+                                           float* smem /* [ry][cx][16] */) {
+  float* mine = smem + ((size_t)ty * cx + tx) * 16;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    mine[k] = s0[k];
+    mine[8 + k] = s1[k];
+  }
+  __syncthreads();
+  if (ty == 0) {
+    for (int j = 1; j < ry; ++j) {
+      const float* o = smem + ((size_t)j * cx + tx) * 16;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        s0[k] += o[k];
+        s1[k] += o[8 + k];
+      }
+    }
+  }
+  __syncthreads();
+}
+
+struct StatsScratch {      // layout of the caller-provided scratch buffer of pdb_bn_stats
+  unsigned int ticket;     // blocks finished so far; the last one folds and resets it
+  unsigned int pad[63];    // keep the partials 256-byte aligned
+  // float partial[gridDim.x][2*C] follows
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) bn_stats_kernel(const T* __restrict__ x, int64_t rows, int C, int cx,
+                                                            int ry, float* __restrict__ sums,
+                                                            StatsScratch* __restrict__ scratch) {
+  extern __shared__ float smem[];
+  __shared__ bool is_last;
+  const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
+  float* partial = reinterpret_cast<float*>(scratch + 1) + (size_t)blockIdx.x * 2 * C;
+  const int ncg = C / 8;
+  for (int cg = tx; cg < ncg; cg += cx) {
+    float s0[8] = {0}, s1[8] = {0};
+    if (ty < ry) reduce_rows<T, 0, false>(x, nullptr, nullptr, rows, C, cg, cx, ry, ty, nullptr, nullptr, s0, s1);
+    block_fold(s0, s1, tx, ty, cx, ry, smem);
+    if (ty == 0) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        partial[cg * 8 + k] = s0[k];
+        partial[C + cg * 8 + k] = s1[k];
+      }
+    }
+  }
+  // publish the partial, take a ticket; the last block folds all partials in block order
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(&scratch->ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    const float* all = reinterpret_cast<const float*>(scratch + 1);
+    for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
+      float acc = 0.f;
+      for (unsigned b = 0; b < gridDim.x; ++b) acc += __ldcg(all + (size_t)b * 2 * C + c);
+      sums[c] = acc;
+    }
+    if (threadIdx.x == 0) scratch->ticket = 0;     // ready for the next launch on this scratch
+  }
+}
+
+template <typename T, bool kHasZ>
+__global__ void __launch_bounds__(kThreads) bn_bwd_reduce_kernel(const T* __restrict__ dz, const T* __restrict__ z,
+                                                                 const T* __restrict__ x, int64_t rows, int C, int cx,
+                                                                 int ry, const float* __restrict__ mean,
+                                                                 const float* __restrict__ rstd,
+                                                                 float* __restrict__ dsums) {
+  extern __shared__ float smem[];
+  const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
+  const int ncg = C / 8;
+  for (int cg = tx; cg < ncg; cg += cx) {
+    float s0[8] = {0}, s1[8] = {0};
+    if (ty < ry) reduce_rows<T, 1, kHasZ>(dz, z, x, rows, C, cg, cx, ry, ty, mean, rstd, s0, s1);
+    block_fold(s0, s1, tx, ty, cx, ry, smem);
+    if (ty == 0) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        atomicAdd(dsums + cg * 8 + k, s0[k]);
+        atomicAdd(dsums + C + cg * 8 + k, s1[k]);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Forward apply.
+template <typename T, bool kRes, bool kRelu>
+__global__ void __launch_bounds__(kThreads) bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res,
+                                                            T* __restrict__ y, int64_t nvec, int C,
+                                                            const float* __restrict__ sums, double count,
+                                                            const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, float eps, float momentum,
+                                                            float* running_mean, float* running_var,
+                                                            int64_t* num_batches_tracked, float* save_mean,
+                                                            float* save_rstd) {
+  extern __shared__ float smem[];        // scale[C] | shift[C]
+  float* scale = smem;
+  float* shift = smem + C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const double m = (double)sums[c] / count;
+    double v = (double)sums[C + c] / count - m * m;
+    v = v > 0.0 ? v : 0.0;
+    const float rstd = rsqrtf((float)v + eps);
+    const float sc = gamma[c] * rstd;
+    scale[c] = sc;
+    shift[c] = beta[c] - (float)m * sc;
+    if (blockIdx.x == 0) {
+      if (save_mean) save_mean[c] = (float)m;
+      if (save_rstd) save_rstd[c] = rstd;
+      if (running_mean) {
+        const double unbiased = count > 1.0 ? v * count / (count - 1.0) : v;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)m;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+      }
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches_tracked) *num_batches_tracked += 1;
+  __syncthreads();
+  const int cvec = C / 8;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const int c0 = (int)(i % cvec) * 8;
+    float f[8];
+    unpack8<T>(ldg128_stream(x + i * 8), f);
+    if (kRes) {
+      float r[8];
+      unpack8<T>(ldg128_stream(res + i * 8), r);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], scale[c0 + k], shift[c0 + k]) + r[k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], scale[c0 + k], shift[c0 + k]);
+    }
+    if (kRelu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+    }
+    stg128(y + i * 8, pack8<T>(f));
+  }
+}
+
+template <typename T, bool kRes, bool kRelu>
+__global__ void __launch_bounds__(kThreads) bn_apply_eval_kernel(const T* __restrict__ x, const T* __restrict__ res,
+                                                                 T* __restrict__ y, int64_t nvec, int C,
+                                                                 const float* __restrict__ rm,
+                                                                 const float* __restrict__ rv,
+                                                                 const float* __restrict__ gamma,
+                                                                 const float* __restrict__ beta, float eps) {
+  extern __shared__ float smem[];
+  float* scale = smem;
+  float* shift = smem + C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float sc = gamma[c] * rsqrtf(rv[c] + eps);
+    scale[c] = sc;
+    shift[c] = beta[c] - rm[c] * sc;
+  }
+  __syncthreads();
+  const int cvec = C / 8;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const int c0 = (int)(i % cvec) * 8;
+    float f[8];
+    unpack8<T>(ldg128_stream(x + i * 8), f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], scale[c0 + k], shift[c0 + k]);
+    if (kRes) {
+      float r[8];
+      unpack8<T>(ldg128_stream(res + i * 8), r);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] += r[k];
+    }
+    if (kRelu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+    }
+    stg128(y + i * 8, pack8<T>(f));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Backward apply: dx = A*g + B*x + Cc with per-channel A = gamma*rstd, B = -A*k2*rstd,
+// Cc = -B*mean - A*k1, k1 = dsums[c]/count, k2 = dsums[C+c]/count.
+template <typename T, bool kHasZ, bool kDres>
+__global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const T* __restrict__ dz, const T* __restrict__ z,
+                                                                const T* __restrict__ x, T* __restrict__ dx,
+                                                                T* __restrict__ dres, int64_t nvec, int C,
+                                                                const float* __restrict__ mean,
+                                                                const float* __restrict__ rstd,
+                                                                const float* __restrict__ gamma,
+                                                                const float* __restrict__ dsums, double count,
+                                                                float* dgamma, float* dbeta) {
+  extern __shared__ float smem[];        // A[C] | B[C] | Cc[C]
+  float* A = smem;
+  float* B = smem + C;
+  float* Cc = smem + 2 * C;
+  const float inv = (float)(1.0 / count);
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float a = gamma[c] * rstd[c];
+    const float k1 = dsums[c] * inv, k2 = dsums[C + c] * inv;
+    const float b = -a * k2 * rstd[c];
+    A[c] = a;
+    B[c] = b;
+    Cc[c] = -b * mean[c] - a * k1;
+    if (blockIdx.x == 0) {
+      if (dgamma) dgamma[c] += dsums[C + c];
+      if (dbeta) dbeta[c] += dsums[c];
+    }
+  }
+  __syncthreads();
+  const int cvec = C / 8;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const int c0 = (int)(i % cvec) * 8;
+    float g[8], fx[8];
+    unpack8<T>(ldg128_stream(dz + i * 8), g);
+    unpack8<T>(ldg128_stream(x + i * 8), fx);
+    if (kHasZ) {
+      float fz[8];
+      unpack8<T>(ldg128_stream(z + i * 8), fz);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = fz[k] > 0.f ? g[k] : 0.f;
+    }
+    if (kDres) stg128(dres + i * 8, pack8<T>(g));
+    float o[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[k] = fmaf(A[c0 + k], g[k], fmaf(B[c0 + k], fx[k], Cc[c0 + k]));
+    stg128(dx + i * 8, pack8<T>(o));
+  }
+}
+
+static void reduce_geometry(int C, int* cx, int* ry) {
+  int ncg = C / 8;
+  int x = ncg < kThreads ? ncg : kThreads;
+  *cx = x;
+  *ry = kThreads / x;
+}
+
+static int reduce_grid(int64_t rows, int ry) {
+  int64_t want = (rows + ry - 1) / ry;
+  int64_t cap = (int64_t)num_sms() * 4;
+  return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
+static int ew_grid(int64_t nvec) {
+  int64_t want = (nvec + kThreads - 1) / kThreads;
+  int64_t cap = (int64_t)num_sms() * 8;
+  return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
+}  // namespace pdb
+
+using namespace pdb;
+
+extern "C" size_t pdb_bn_stats_scratch_bytes(int C) {
+  return sizeof(StatsScratch) + (size_t)num_sms() * 4 * 2 * (size_t)C * sizeof(float);
+}
+
+extern "C" int pdb_bn_stats(const void* x, int dtype, int64_t rows, int C, float* sums, void* scratch,
+                            size_t scratch_bytes, void* stream) {
+  PDB_CHECK_ARG(x && sums && scratch, "pdb_bn_stats: null pointer");
+  PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC, "pdb_bn_stats: C=%d must be a multiple of 8 and <= %d", C, kMaxC);
+  PDB_CHECK_ARG(rows > 0, "pdb_bn_stats: rows must be positive");
+  int cx, ry;
+  reduce_geometry(C, &cx, &ry);
+  const int grid = reduce_grid(rows, ry);
+  const size_t need = sizeof(StatsScratch) + (size_t)grid * 2 * C * sizeof(float);
+  PDB_CHECK_ARG(scratch_bytes >= need, "pdb_bn_stats: scratch too small (%zu < %zu bytes)", scratch_bytes, need);
+  PDB_CHECK_ARG(((uintptr_t)scratch) % 256 == 0, "pdb_bn_stats: scratch must be 256-byte aligned");
+  const size_t smem = (size_t)kThreads * 16 * sizeof(float);
+  PDB_DISPATCH_16(dtype, T, (bn_stats_kernel<T><<<grid, kThreads, smem, (cudaStream_t)stream>>>(
+                                (const T*)x, rows, C, cx, ry, sums, (StatsScratch*)scratch)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const void* x, int dtype, int64_t rows, int C,
+                                 const float* mean, const float* rstd, float* dsums, void* stream) {
+  PDB_CHECK_ARG(dz && x && mean && rstd && dsums, "pdb_bn_bwd_reduce: null pointer");
+  PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_bwd_reduce: bad shape rows=%lld C=%d",
+                (long long)rows, C);
+  int cx, ry;
+  reduce_geometry(C, &cx, &ry);
+  const int grid = reduce_grid(rows, ry);
+  const size_t smem = (size_t)kThreads * 16 * sizeof(float);
+  cudaStream_t st = (cudaStream_t)stream;
+  PDB_DISPATCH_16(dtype, T, {
+    if (z)
+      bn_bwd_reduce_kernel<T, true><<<grid, kThreads, smem, st>>>((const T*)dz, (const T*)z, (const T*)x, rows, C, cx,
+                                                                  ry, mean, rstd, dsums);
+    else
+      bn_bwd_reduce_kernel<T, false><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, (const T*)x, rows, C, cx, ry,
+                                                                   mean, rstd, dsums);
+  });
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_bn_apply(const void* x, const void* residual, void* y, int dtype, int64_t rows, int C,
+                            const float* sums, double count, const float* gamma, const float* beta, float eps,
+                            float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
+                            float* save_mean, float* save_rstd, int relu, void* stream) {
+  PDB_CHECK_ARG(x && y && sums && gamma && beta, "pdb_bn_apply: null pointer");
+  PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0 && count > 0, "pdb_bn_apply: bad shape rows=%lld C=%d",
+                (long long)rows, C);
+  const int64_t nvec = rows * C / 8;
+  const int grid = ew_grid(nvec);
+  const size_t smem = 2 * (size_t)C * sizeof(float);
+  cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH(RES, RELU)                                                                                         \
+  bn_apply_kernel<T, RES, RELU><<<grid, kThreads, smem, st>>>((const T*)x, (const T*)residual, (T*)y, nvec, C, sums, \
+                                                              count, gamma, beta, eps, momentum, running_mean,    \
+                                                              running_var, num_batches_tracked, save_mean, save_rstd)
+  PDB_DISPATCH_16(dtype, T, {
+    if (residual && relu) LAUNCH(true, true);
+    else if (residual) LAUNCH(true, false);
+    else if (relu) LAUNCH(false, true);
+    else LAUNCH(false, false);
+  });
+#undef LAUNCH
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_bn_apply_eval(const void* x, const void* residual, void* y, int dtype, int64_t rows, int C,
+                                 const float* running_mean, const float* running_var, const float* gamma,
+                                 const float* beta, float eps, int relu, void* stream) {
+  PDB_CHECK_ARG(x && y && running_mean && running_var && gamma && beta, "pdb_bn_apply_eval: null pointer");
+  PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_apply_eval: bad shape");
+  const int64_t nvec = rows * C / 8;
+  const int grid = ew_grid(nvec);
+  const size_t smem = 2 * (size_t)C * sizeof(float);
+  cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH(RES, RELU)                                                                                    \
+  bn_apply_eval_kernel<T, RES, RELU><<<grid, kThreads, smem, st>>>((const T*)x, (const T*)residual, (T*)y, nvec, C, \
+                                                                   running_mean, running_var, gamma, beta, eps)
+  PDB_DISPATCH_16(dtype, T, {
+    if (residual && relu) LAUNCH(true, true);
+    else if (residual) LAUNCH(true, false);
+    else if (relu) LAUNCH(false, true);
+    else LAUNCH(false, false);
+  });
+#undef LAUNCH
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_bn_bwd_apply(const void* dz, const void* z, const void* x, void* dx, void* dres, int dtype,
+                                int64_t rows, int C, const float* mean, const float* rstd, const float* gamma,
+                                const float* dsums, double count, float* dgamma, float* dbeta, void* stream) {
+  PDB_CHECK_ARG(dz && x && dx && mean && rstd && gamma && dsums, "pdb_bn_bwd_apply: null pointer");
+  PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0 && count > 0, "pdb_bn_bwd_apply: bad shape");
+  const int64_t nvec = rows * C / 8;
+  const int grid = ew_grid(nvec);
+  const size_t smem = 3 * (size_t)C * sizeof(float);
+  cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH(HZ, DR)                                                                                              \
+  bn_bwd_apply_kernel<T, HZ, DR><<<grid, kThreads, smem, st>>>((const T*)dz, (const T*)z, (const T*)x, (T*)dx,     \
+                                                               (T*)dres, nvec, C, mean, rstd, gamma, dsums, count, \
+                                                               dgamma, dbeta)
+  PDB_DISPATCH_16(dtype, T, {
+    if (z && dres) LAUNCH(true, true);
+    else if (z) LAUNCH(true, false);
+    else if (dres) LAUNCH(false, true);
+    else LAUNCH(false, false);
+  });
+#undef LAUNCH
+  PDB_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,670 @@
+// K7 / K11: convolutions and the fc layer as implicit GEMMs on the 5th-generation tensor cores.
+//
+//   fprop / dgrad :  D[M, N] = A[M, K] * B[N, K]^T      (pdb_conv_fprop)
+//       A = NHWC activation.  1x1/stride-1 (and pre-gathered) inputs are a plain [M, C] matrix loaded
+//       with tiled TMA; everything else uses TMA *im2col* mode, which walks 128 consecutive output
+//       pixels (wrapping rows and images), applies the filter-tap offset and zero-fills the halo.
+//       B = weights [Cout, kh, kw, Cin] (K-major).  dgrad is the same kernel on dY with the flipped /
+//       transposed weight copy.
+//   wgrad         :  dW[Cout, K] += dY[M, Cout]^T * im2col(X)[M, K]   (pdb_conv_wgrad)
+//       the reduction runs over pixels, so both operands are MN-major in shared memory; the pixel range
+//       is split over CTAs and partial tiles are added to the fp32 gradient with vector reductions.
+//
+// Structure (both kernels): persistent CTAs, one per SM; warp 0 = TMA producer, warp 1 = MMA issuer
+// (one elected thread issues tcgen05.mma), warps 2-5 = epilogue.  kStages-deep smem ring guarded by
+// full/empty mbarriers; the fp32 accumulator lives in TMEM and is double-buffered so the epilogue of
+// tile i overlaps the main loop of tile i+1.  The fprop epilogue converts to 16-bit, stages the tile
+// in 128B-swizzled smem, writes it with TMA, and (optionally) accumulates the per-channel sum and
+// sum-of-squares that the following BatchNorm needs — the statistics pass of the delegate's BN kernel
+// (torch:nn/modules/batchnorm.py:144-210 over cuDNN) disappears.
+//
+// Delegates being replaced: cuDNN 9.22 convolutions and cuBLAS(Lt) linear.
+#include "common.cuh"
+#include "tc05.cuh"
+
+namespace pdb {
+using namespace tc05;
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;                 // 64 x 16-bit = 128 B = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kNumThreads = 192;            // 6 warps: producer, mma, 4 x epilogue
+constexpr int kEpiThreads = 128;
+constexpr uint32_t A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KB
+constexpr uint32_t CHUNK_BYTES = 64 * 128;                  // 64 rows x 128 B = 8 KB (wgrad boxes)
+
+struct FpropParams {
+  int M, N;
+  int num_m_blocks, num_n_blocks;
+  int taps, cin_blocks, S;
+  int P, Q, stride, pad;
+  int a_im2col;
+  float* stats;        // [2N]: sum | sumsq, accumulated with atomics; may be null
+  const float* bias;   // [N]; may be null
+};
+
+template <int BLOCK_N>
+struct FpropSmem {
+  static constexpr uint32_t B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
+  static constexpr uint32_t STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int kStages = BLOCK_N == 256 ? 3 : (BLOCK_N == 128 ? 5 : 6);
+  static constexpr uint32_t OUT_BYTES = (BLOCK_N / 64) * 16384;       // 128 rows x 128 B per 64-col chunk
+  static constexpr uint32_t BAR_OFFSET = kStages * STAGE_BYTES + OUT_BYTES;
+  static constexpr uint32_t TOTAL = BAR_OFFSET + 256 + 1024;           // barriers + alignment slack
+};
+
+template <bool kBf16>
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  if (kBf16) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+  } else {
+    __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&v);
+  }
+}
+template <bool kBf16>
+__device__ __forceinline__ float2 unpack2(uint32_t w) {
+  if (kBf16) return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w));
+  return __half22float2(*reinterpret_cast<__half2*>(&w));
+}
+
+template <int BLOCK_N, bool kBf16>
+__global__ void __launch_bounds__(kNumThreads, 1)
+conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const __grid_constant__ CUtensorMap tmD, const FpropParams p) {
+  using L = FpropSmem<BLOCK_N>;
+  constexpr int kStages = L::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* out_stage = smem + kStages * L::STAGE_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::BAR_OFFSET);
+  uint64_t* empty = full + kStages;
+  uint64_t* tfull = empty + kStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    prefetch_tmap(&tmD);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(full + i, 1);
+      mbar_init(empty + i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(tfull + i, 1);
+      mbar_init(tempty + i, 4);          // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<2 * BLOCK_N>(tmem_slot);
+  fence_before_thread_sync();
+  __syncthreads();
+  fence_after_thread_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+  const int num_kb = p.taps * p.cin_blocks;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_blk = tile % p.num_m_blocks, n_blk = tile / p.num_m_blocks;
+        int base_w = 0, base_h = 0, n_img = 0;
+        if (p.a_im2col) {
+          const int m0 = m_blk * BLOCK_M, pq = p.P * p.Q;
+          n_img = m0 / pq;
+          const int rem = m0 - n_img * pq;
+          const int pp = rem / p.Q, qq = rem - pp * p.Q;
+          base_w = qq * p.stride - p.pad;
+          base_h = pp * p.stride - p.pad;
+        }
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty + stage, phase ^ 1);
+          uint8_t* sA = smem + stage * L::STAGE_BYTES;
+          uint8_t* sB = sA + A_STAGE_BYTES;
+          mbar_arrive_expect_tx(full + stage, L::STAGE_BYTES);
+          if (p.a_im2col) {
+            const int tap = kb / p.cin_blocks, cb = kb - tap * p.cin_blocks;
+            const int r = tap / p.S, s = tap - r * p.S;
+            tma_load_im2col_4d(sA, &tmA, full + stage, cb * BLOCK_K, base_w, base_h, n_img, (uint16_t)s, (uint16_t)r);
+          } else {
+            tma_load_2d(sA, &tmA, full + stage, kb * BLOCK_K, m_blk * BLOCK_M);
+          }
+          tma_load_2d(sB, &tmB, full + stage, kb * BLOCK_K, n_blk * BLOCK_N);
+          if (++stage == kStages) stage = 0, phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    constexpr uint32_t idesc = umma_idesc_f16(kBf16 ? 1 : 0, BLOCK_M, BLOCK_N, 0, 0);
+    constexpr uint64_t desc_base = umma_desc_base(0, 1024);        // K-major SW128: SBO = 8 rows x 128 B
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(tempty + acc, acc_phase ^ 1);                       // epilogue has drained this accumulator
+      fence_after_thread_sync();
+      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(full + stage, phase);
+        fence_after_thread_sync();
+        if (elect_one()) {
+          const uint32_t a_addr = smem_u32(smem + stage * L::STAGE_BYTES);
+          const uint32_t b_addr = a_addr + A_STAGE_BYTES;
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            umma_f16(d_tmem, umma_desc(desc_base, a_addr + k * UMMA_K * 2), umma_desc(desc_base, b_addr + k * UMMA_K * 2),
+                     idesc, (kb | k) != 0);
+          }
+          umma_commit(empty + stage);                               // smem slot free once these MMAs retire
+          if (kb == num_kb - 1) umma_commit(tfull + acc);           // accumulator complete
+        }
+        __syncwarp();
+        if (++stage == kStages) stage = 0, phase ^= 1;
+      }
+      if ((acc ^= 1) == 0) acc_phase ^= 1;
+    }
+  } else {
+    // ================================ epilogue ====================================
+    const int quarter = warp & 3;                     // TMEM lanes [32*quarter, +32) are visible to this warp
+    const int row = quarter * 32 + lane;              // row of the 128-row tile owned by this thread
+    const int tid_e = threadIdx.x - 64;               // 0..127
+    const bool leader = tid_e == 0;
+    constexpr int PAIRS = BLOCK_N / 2;                // column pairs for the statistics pass
+    constexpr int G = kEpiThreads / PAIRS;            // row groups (1, 2, 4)
+    const int pair = tid_e % PAIRS, rg = tid_e / PAIRS;
+    float st_sum[2] = {0.f, 0.f}, st_sq[2] = {0.f, 0.f};
+    int st_nblk = -1;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_blk = tile % p.num_m_blocks, n_blk = tile / p.num_m_blocks;
+      const int n0 = n_blk * BLOCK_N;
+      if (p.stats && st_nblk != n_blk) {
+        if (st_nblk >= 0) {
+          const int c = st_nblk * BLOCK_N + pair * 2;
+          if (c < p.N) atomicAdd(p.stats + c, st_sum[0]), atomicAdd(p.stats + p.N + c, st_sq[0]);
+          if (c + 1 < p.N) atomicAdd(p.stats + c + 1, st_sum[1]), atomicAdd(p.stats + p.N + c + 1, st_sq[1]);
+        }
+        st_sum[0] = st_sum[1] = st_sq[0] = st_sq[1] = 0.f;
+        st_nblk = n_blk;
+      }
+      mbar_wait(tfull + acc, acc_phase);
+      fence_after_thread_sync();
+      // the previous tile's TMA store must have finished reading the staging buffer
+      if (leader) tma_store_wait_read0();
+      named_bar_sync(1, kEpiThreads);
+#pragma unroll
+      for (int j = 0; j < BLOCK_N / 64; ++j) {
+        uint32_t v0[32], v1[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BLOCK_N + j * 64;
+        tmem_ld_32x32(taddr, v0);
+        tmem_ld_32x32(taddr + 32, v1);
+        tmem_ld_wait();
+        if (p.bias) {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const int n = n0 + j * 64 + c;
+            v0[c] = __float_as_uint(__uint_as_float(v0[c]) + (n < p.N ? __ldg(p.bias + n) : 0.f));
+            v1[c] = __float_as_uint(__uint_as_float(v1[c]) + (n + 32 < p.N ? __ldg(p.bias + n + 32) : 0.f));
+          }
+        }
+        uint8_t* dst = out_stage + j * 16384 + row * 128;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {           // 16-byte chunks 0..3 come from v0, 4..7 from v1
+          uint4 w0, w1;
+          w0.x = pack2<kBf16>(__uint_as_float(v0[8 * c + 0]), __uint_as_float(v0[8 * c + 1]));
+          w0.y = pack2<kBf16>(__uint_as_float(v0[8 * c + 2]), __uint_as_float(v0[8 * c + 3]));
+          w0.z = pack2<kBf16>(__uint_as_float(v0[8 * c + 4]), __uint_as_float(v0[8 * c + 5]));
+          w0.w = pack2<kBf16>(__uint_as_float(v0[8 * c + 6]), __uint_as_float(v0[8 * c + 7]));
+          w1.x = pack2<kBf16>(__uint_as_float(v1[8 * c + 0]), __uint_as_float(v1[8 * c + 1]));
+          w1.y = pack2<kBf16>(__uint_as_float(v1[8 * c + 2]), __uint_as_float(v1[8 * c + 3]));
+          w1.z = pack2<kBf16>(__uint_as_float(v1[8 * c + 4]), __uint_as_float(v1[8 * c + 5]));
+          w1.w = pack2<kBf16>(__uint_as_float(v1[8 * c + 6]), __uint_as_float(v1[8 * c + 7]));
+          *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = w0;
+          *reinterpret_cast<uint4*>(dst + (((c + 4) ^ (row & 7)) << 4)) = w1;
+        }
+      }
+      // accumulator fully read: hand the TMEM stage back to the MMA warp
+      fence_before_thread_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty + acc);
+      fence_proxy_async();                       // generic-proxy smem writes -> visible to the TMA engine
+      named_bar_sync(1, kEpiThreads);
+      if (leader) {
+#pragma unroll
+        for (int j = 0; j < BLOCK_N / 64; ++j)
+          if (n0 + j * 64 < p.N) tma_store_2d(&tmD, out_stage + j * 16384, n0 + j * 64, m_blk * BLOCK_M);
+        tma_store_commit();
+      }
+      if (p.stats) {
+        // per-channel sum / sum of squares of the ROUNDED outputs, read back from the staged tile
+        // (rows past M are exact zeros: their A rows were zero-filled by TMA)
+        const int col = pair * 2;
+        const uint8_t* src = out_stage + (col >> 6) * 16384 + ((col & 7) << 1);
+        const int chunk = (col & 63) >> 3;
+#pragma unroll 8
+        for (int r = rg; r < BLOCK_M; r += G) {
+          const uint32_t w = *reinterpret_cast<const uint32_t*>(src + r * 128 + ((chunk ^ (r & 7)) << 4));
+          const float2 f = unpack2<kBf16>(w);
+          st_sum[0] += f.x, st_sum[1] += f.y;
+          st_sq[0] = fmaf(f.x, f.x, st_sq[0]), st_sq[1] = fmaf(f.y, f.y, st_sq[1]);
+        }
+      }
+      if ((acc ^= 1) == 0) acc_phase ^= 1;
+    }
+    if (p.stats && st_nblk >= 0) {
+      const int c = st_nblk * BLOCK_N + pair * 2;
+      if (c < p.N) atomicAdd(p.stats + c, st_sum[0]), atomicAdd(p.stats + p.N + c, st_sq[0]);
+      if (c + 1 < p.N) atomicAdd(p.stats + c + 1, st_sum[1]), atomicAdd(p.stats + p.N + c + 1, st_sq[1]);
+    }
+    if (leader) tma_store_wait0();
+  }
+  fence_before_thread_sync();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<2 * BLOCK_N>(tmem_base);
+}
+
+// ================================================================================================
+// wgrad: dW[Cout, Ktot] += dY^T * im2col(X); both operands MN-major (pixels are the reduction axis).
+struct WgradParams {
+  int Mpix;                 // reduction length (N*P*Q)
+  int Cout, Ktot;           // output is [Cout, Ktot] fp32, row pitch ldw
+  int Kvalid;               // columns >= Kvalid are computed but never written
+  int ldw;
+  int num_m_blocks;         // ceil(Cout / 128)
+  int num_n_blocks;         // ceil(Ktot / BLOCK_N)
+  int num_kb;               // ceil(Mpix / 64)
+  int kb_per_split, num_splits;
+  int cin_blocks, S;        // 64-wide column chunk j -> tap = j / cin_blocks, c0 = (j % cin_blocks)*64
+  int P, Q, stride, pad;
+  int b_im2col;
+  float* dw;
+};
+
+template <int BLOCK_N>
+struct WgradSmem {
+  static constexpr uint32_t A_BYTES = 2 * CHUNK_BYTES;                    // 128 couts x 64 pixels
+  static constexpr uint32_t B_BYTES = (BLOCK_N / 64) * CHUNK_BYTES;       // BLOCK_N cols x 64 pixels
+  static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int kStages = BLOCK_N == 256 ? 4 : 6;
+  static constexpr uint32_t BAR_OFFSET = kStages * STAGE_BYTES;
+  static constexpr uint32_t TOTAL = BAR_OFFSET + 256 + 1024;
+};
+
+template <int BLOCK_N, bool kBf16>
+__global__ void __launch_bounds__(kNumThreads, 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
+                  const __grid_constant__ CUtensorMap tmB /* X: tiled [Mpix, C] or im2col (C,W,H,N) */,
+                  const WgradParams p) {
+  using L = WgradSmem<BLOCK_N>;
+  constexpr int kStages = L::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::BAR_OFFSET);
+  uint64_t* empty = full + kStages;
+  uint64_t* tfull = empty + kStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(full + i, 1);
+      mbar_init(empty + i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(tfull + i, 1);
+      mbar_init(tempty + i, 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<2 * BLOCK_N>(tmem_slot);
+  fence_before_thread_sync();
+  __syncthreads();
+  fence_after_thread_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+  const int num_items = num_tiles * p.num_splits;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+        const int tile = item % num_tiles, split = item / num_tiles;
+        const int m_blk = tile % p.num_m_blocks, n_blk = tile / p.num_m_blocks;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.num_kb);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty + stage, phase ^ 1);
+          uint8_t* sA = smem + stage * L::STAGE_BYTES;
+          uint8_t* sB = sA + L::A_BYTES;
+          mbar_arrive_expect_tx(full + stage, L::STAGE_BYTES);
+          const int pix0 = kb * 64;
+          // A: two boxes of [64 pixels][64 couts]; couts past Cout are zero-filled
+          tma_load_2d(sA, &tmA, full + stage, m_blk * BLOCK_M, pix0);
+          tma_load_2d(sA + CHUNK_BYTES, &tmA, full + stage, m_blk * BLOCK_M + 64, pix0);
+          int base_w = 0, base_h = 0, n_img = 0;
+          if (p.b_im2col) {
+            const int pq = p.P * p.Q;
+            n_img = pix0 / pq;
+            const int rem = pix0 - n_img * pq;
+            const int pp = rem / p.Q, qq = rem - pp * p.Q;
+            base_w = qq * p.stride - p.pad;
+            base_h = pp * p.stride - p.pad;
+          }
+#pragma unroll
+          for (int j = 0; j < BLOCK_N / 64; ++j) {
+            const int chunk = n_blk * (BLOCK_N / 64) + j;          // global 64-column chunk index
+            if (p.b_im2col) {
+              int tap = chunk / p.cin_blocks;
+              const int cb = chunk - tap * p.cin_blocks;
+              const int r = tap / p.S, s = tap - r * p.S;
+              // chunks past Ktot: channel coordinate past C -> zero fill (tap clamped to stay in range)
+              tma_load_im2col_4d(sB + j * CHUNK_BYTES, &tmB, full + stage, chunk * 64 < p.Ktot ? cb * 64 : (1 << 20),
+                                 base_w, base_h, n_img, (uint16_t)s, (uint16_t)min(r, 15));
+            } else {
+              tma_load_2d(sB + j * CHUNK_BYTES, &tmB, full + stage, chunk * 64, pix0);
+            }
+          }
+          if (++stage == kStages) stage = 0, phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = umma_idesc_f16(kBf16 ? 1 : 0, BLOCK_M, BLOCK_N, 1, 1);
+    // MN-major SW128: LBO = distance between 64-element MN atoms (one TMA box), SBO = 8 K-rows x 128 B
+    constexpr uint64_t desc_base = umma_desc_base(CHUNK_BYTES, 1024);
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const int split = item / num_tiles;
+      const int kb0 = split * p.kb_per_split;
+      const int kb1 = min(kb0 + p.kb_per_split, p.num_kb);
+      mbar_wait(tempty + acc, acc_phase ^ 1);
+      fence_after_thread_sync();
+      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full + stage, phase);
+        fence_after_thread_sync();
+        if (elect_one()) {
+          const uint32_t a_addr = smem_u32(smem + stage * L::STAGE_BYTES);
+          const uint32_t b_addr = a_addr + L::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < 64 / UMMA_K; ++k) {       // 16 pixel rows x 128 B per MMA
+            umma_f16(d_tmem, umma_desc(desc_base, a_addr + k * UMMA_K * 128), umma_desc(desc_base, b_addr + k * UMMA_K * 128),
+                     idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty + stage);
+          if (kb == kb1 - 1) umma_commit(tfull + acc);
+        }
+        __syncwarp();
+        if (++stage == kStages) stage = 0, phase ^= 1;
+      }
+      if (kb1 > kb0) {
+        if ((acc ^= 1) == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const bool vec_ok = (p.ldw % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.dw) & 15) == 0);
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const int tile = item % num_tiles, split = item / num_tiles;
+      const int kb0 = split * p.kb_per_split;
+      if (kb0 >= p.num_kb) continue;
+      const int m_blk = tile % p.num_m_blocks, n_blk = tile / p.num_m_blocks;
+      mbar_wait(tfull + acc, acc_phase);
+      fence_after_thread_sync();
+      const int cout = m_blk * BLOCK_M + row;
+#pragma unroll
+      for (int j = 0; j < BLOCK_N / 32; ++j) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BLOCK_N + j * 32, v);
+        tmem_ld_wait();
+        const int col0 = n_blk * BLOCK_N + j * 32;
+        if (cout < p.Cout && col0 < p.Kvalid) {
+          float* dst = p.dw + (size_t)cout * p.ldw + col0;
+          if (vec_ok && col0 + 32 <= p.Kvalid) {
+#pragma unroll
+            for (int c = 0; c < 32; c += 4)
+              red_add_v4(dst + c, __uint_as_float(v[c]), __uint_as_float(v[c + 1]), __uint_as_float(v[c + 2]),
+                         __uint_as_float(v[c + 3]));
+          } else {
+#pragma unroll
+            for (int c = 0; c < 32; ++c)
+              if (col0 + c < p.Kvalid) atomicAdd(dst + c, __uint_as_float(v[c]));
+          }
+        }
+      }
+      fence_before_thread_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty + acc);
+      if ((acc ^= 1) == 0) acc_phase ^= 1;
+    }
+  }
+  fence_before_thread_sync();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<2 * BLOCK_N>(tmem_base);
+}
+
+// ================================================================================================
+// Host side: tensor maps through the driver entry points (no link-time libcuda dependency).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*,
+                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                   CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_tiled = nullptr;
+static EncodeIm2colFn g_im2col = nullptr;
+
+static int load_driver_fns() {
+  if (g_tiled && g_im2col) return 0;
+  cudaDriverEntryPointQueryResult q;
+  void* f = nullptr;
+  PDB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q));
+  PDB_CHECK_ARG(f && q == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled not available in this driver");
+  g_tiled = (EncodeTiledFn)f;
+  PDB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &f, cudaEnableDefault, &q));
+  PDB_CHECK_ARG(f && q == cudaDriverEntryPointSuccess, "cuTensorMapEncodeIm2col not available in this driver");
+  g_im2col = (EncodeIm2colFn)f;
+  return 0;
+}
+
+static CUtensorMapDataType tm_dtype(int dtype) {
+  return dtype == PDB_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+}
+
+// 2-D row-major [rows, cols] 16-bit matrix with row pitch ld (elements); box = [box_rows, box_cols]
+static int make_tiled_2d(CUtensorMap* m, const void* ptr, int dtype, uint64_t rows, uint64_t cols, uint64_t ld,
+                         uint32_t box_rows, uint32_t box_cols) {
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  PDB_CHECK_ARG((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld * 2) % 16 == 0,
+                "tensor map: base must be 16-byte aligned and the row pitch a multiple of 16 bytes (ld=%llu)",
+                (unsigned long long)ld);
+  CUresult r = g_tiled(m, tm_dtype(dtype), 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  PDB_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (rows=%llu cols=%llu ld=%llu box=%ux%u)",
+                (int)r, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows, box_cols);
+  return 0;
+}
+
+// NHWC activation as (C, W, H, N) in im2col mode; `pixels` consecutive output positions per load.
+static int make_im2col_4d(CUtensorMap* m, const void* ptr, int dtype, int N, int H, int W, int C, int R, int S,
+                          int stride, int pad, uint32_t pixels) {
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  int lower[2] = {-pad, -pad};
+  int upper[2] = {pad - (S - 1), pad - (R - 1)};
+  cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  PDB_CHECK_ARG((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (C * 2) % 16 == 0,
+                "im2col tensor map: base must be 16-byte aligned and C a multiple of 8");
+  CUresult r = g_im2col(m, tm_dtype(dtype), 4, const_cast<void*>(ptr), dims, strides, lower, upper, 64, pixels, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  PDB_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeIm2col failed with %d (N=%d H=%d W=%d C=%d R=%d S=%d stride=%d pad=%d)",
+                (int)r, N, H, W, C, R, S, stride, pad);
+  return 0;
+}
+
+template <typename K>
+static int set_smem(K kernel, uint32_t bytes) {
+  PDB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+
+template <int BLOCK_N, bool kBf16>
+static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const FpropParams& p,
+                        cudaStream_t st) {
+  static bool configured = false;
+  auto kernel = conv_fprop_kernel<BLOCK_N, kBf16>;
+  if (!configured) {
+    if (int e = set_smem(kernel, FpropSmem<BLOCK_N>::TOTAL)) return e;
+    configured = true;
+  }
+  const int tiles = p.num_m_blocks * p.num_n_blocks;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  kernel<<<grid, kNumThreads, FpropSmem<BLOCK_N>::TOTAL, st>>>(a, b, d, p);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int BLOCK_N, bool kBf16>
+static int launch_wgrad(const CUtensorMap& a, const CUtensorMap& b, const WgradParams& p, cudaStream_t st) {
+  static bool configured = false;
+  auto kernel = conv_wgrad_kernel<BLOCK_N, kBf16>;
+  if (!configured) {
+    if (int e = set_smem(kernel, WgradSmem<BLOCK_N>::TOTAL)) return e;
+    configured = true;
+  }
+  const int items = p.num_m_blocks * p.num_n_blocks * p.num_splits;
+  const int grid = items < num_sms() ? items : num_sms();
+  kernel<<<grid, kNumThreads, WgradSmem<BLOCK_N>::TOTAL, st>>>(a, b, p);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace pdb
+using namespace pdb;
+
+extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, const pdb_conv_shape* s, int64_t lda,
+                              int64_t ldd, float* stats, const float* bias, int block_n, void* stream) {
+  PDB_CHECK_ARG(x && w && y && s, "pdb_conv_fprop: null pointer");
+  PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16, "pdb_conv_fprop: dtype must be PDB_BF16 or PDB_FP16");
+  if (int e = load_driver_fns()) return e;
+  const int P = (s->H + 2 * s->pad - s->R) / s->stride + 1, Q = (s->W + 2 * s->pad - s->S) / s->stride + 1;
+  const int64_t M = (int64_t)s->N * P * Q;
+  const bool plain = s->R == 1 && s->S == 1 && s->stride == 1 && s->pad == 0;
+  PDB_CHECK_ARG(M > 0 && M < (1ll << 31) && s->K > 0 && s->C > 0, "pdb_conv_fprop: bad shape");
+  PDB_CHECK_ARG(s->C % 8 == 0, "pdb_conv_fprop: C=%d must be a multiple of 8 (16-byte rows)", s->C);
+  PDB_CHECK_ARG(plain || s->C % 64 == 0, "pdb_conv_fprop: im2col path needs C %% 64 == 0 (C=%d)", s->C);
+  if (lda <= 0) lda = s->C;
+  if (ldd <= 0) ldd = s->K;
+  int bn = block_n;
+  if (bn <= 0) bn = s->K <= 64 ? 64 : (s->K <= 128 ? 128 : 256);
+  PDB_CHECK_ARG(bn == 64 || bn == 128 || bn == 256, "pdb_conv_fprop: block_n must be 64, 128 or 256");
+
+  FpropParams p{};
+  p.M = (int)M, p.N = s->K;
+  p.num_m_blocks = (int)((M + BLOCK_M - 1) / BLOCK_M);
+  p.num_n_blocks = (s->K + bn - 1) / bn;
+  p.taps = s->R * s->S, p.cin_blocks = (s->C + BLOCK_K - 1) / BLOCK_K, p.S = s->S;
+  p.P = P, p.Q = Q, p.stride = s->stride, p.pad = s->pad;
+  p.a_im2col = plain ? 0 : 1;
+  p.stats = stats, p.bias = bias;
+
+  CUtensorMap tmA, tmB, tmD;
+  if (plain) {
+    if (int e = make_tiled_2d(&tmA, x, dtype, (uint64_t)M, (uint64_t)s->C, (uint64_t)lda, BLOCK_M, BLOCK_K)) return e;
+  } else {
+    if (int e = make_im2col_4d(&tmA, x, dtype, s->N, s->H, s->W, s->C, s->R, s->S, s->stride, s->pad, BLOCK_M)) return e;
+  }
+  const uint64_t ktot = (uint64_t)p.taps * s->C;
+  if (int e = make_tiled_2d(&tmB, w, dtype, (uint64_t)s->K, ktot, ktot, (uint32_t)bn, BLOCK_K)) return e;
+  if (int e = make_tiled_2d(&tmD, y, dtype, (uint64_t)M, (uint64_t)s->K, (uint64_t)ldd, BLOCK_M, 64)) return e;
+
+  cudaStream_t st = (cudaStream_t)stream;
+#define GO(BN)                                                              \
+  (dtype == PDB_BF16 ? launch_fprop<BN, true>(tmA, tmB, tmD, p, st) : launch_fprop<BN, false>(tmA, tmB, tmD, p, st))
+  if (bn == 64) return GO(64);
+  if (bn == 128) return GO(128);
+  return GO(256);
+#undef GO
+}
+
+extern "C" int pdb_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, const pdb_conv_shape* s, int64_t ldx,
+                              int64_t lddy, int64_t ldw, int64_t kvalid, int splits, int block_n, void* stream) {
+  PDB_CHECK_ARG(x && dy && dw && s, "pdb_conv_wgrad: null pointer");
+  PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16, "pdb_conv_wgrad: dtype must be PDB_BF16 or PDB_FP16");
+  if (int e = load_driver_fns()) return e;
+  const int P = (s->H + 2 * s->pad - s->R) / s->stride + 1, Q = (s->W + 2 * s->pad - s->S) / s->stride + 1;
+  const int64_t M = (int64_t)s->N * P * Q;
+  const bool plain = s->R == 1 && s->S == 1 && s->stride == 1 && s->pad == 0;
+  PDB_CHECK_ARG(M > 0 && M < (1ll << 31) && s->K > 0 && s->C > 0, "pdb_conv_wgrad: bad shape");
+  PDB_CHECK_ARG(s->C % 8 == 0 && s->K % 8 == 0, "pdb_conv_wgrad: C and K must be multiples of 8");
+  PDB_CHECK_ARG(plain || s->C % 64 == 0, "pdb_conv_wgrad: im2col path needs C %% 64 == 0 (C=%d)", s->C);
+  if (ldx <= 0) ldx = s->C;
+  if (lddy <= 0) lddy = s->K;
+  const int ktot = s->R * s->S * s->C;
+  if (ldw <= 0) ldw = ktot;
+  int bn = block_n;
+  if (bn <= 0) bn = ktot <= 64 ? 64 : (ktot <= 128 ? 128 : 256);
+  PDB_CHECK_ARG(bn == 64 || bn == 128 || bn == 256, "pdb_conv_wgrad: block_n must be 64, 128 or 256");
+
+  WgradParams p{};
+  p.Mpix = (int)M, p.Cout = s->K, p.Ktot = ktot, p.ldw = (int)ldw;
+  p.Kvalid = kvalid > 0 && kvalid < ktot ? (int)kvalid : ktot;
+  p.num_m_blocks = (s->K + BLOCK_M - 1) / BLOCK_M;
+  p.num_n_blocks = (ktot + bn - 1) / bn;
+  p.num_kb = (int)((M + 63) / 64);
+  const int tiles = p.num_m_blocks * p.num_n_blocks;
+  if (splits <= 0) {
+    // enough work items for ~2 waves of persistent CTAs, but keep at least 8 k-blocks per item
+    splits = (2 * num_sms() + tiles - 1) / tiles;
+    const int max_splits = (p.num_kb + 7) / 8;
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+  }
+  p.kb_per_split = (p.num_kb + splits - 1) / splits;
+  p.num_splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.cin_blocks = (s->C + 63) / 64, p.S = s->S;
+  p.P = P, p.Q = Q, p.stride = s->stride, p.pad = s->pad;
+  p.b_im2col = plain ? 0 : 1;
+  p.dw = dw;
+
+  CUtensorMap tmA, tmB;
+  if (int e = make_tiled_2d(&tmA, dy, dtype, (uint64_t)M, (uint64_t)s->K, (uint64_t)lddy, 64, 64)) return e;
+  if (plain) {
+    if (int e = make_tiled_2d(&tmB, x, dtype, (uint64_t)M, (uint64_t)s->C, (uint64_t)ldx, 64, 64)) return e;
+  } else {
+    if (int e = make_im2col_4d(&tmB, x, dtype, s->N, s->H, s->W, s->C, s->R, s->S, s->stride, s->pad, 64)) return e;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+#define GO(BN) (dtype == PDB_BF16 ? launch_wgrad<BN, true>(tmA, tmB, p, st) : launch_wgrad<BN, false>(tmA, tmB, p, st))
+  if (bn == 64) return GO(64);
+  if (bn == 128) return GO(128);
+  return GO(256);
+#undef GO
+}

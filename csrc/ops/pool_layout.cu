@@ -1,0 +1,377 @@
+// K12 pooling and the layout / elementwise helpers, NHWC 16-bit, 8 channels per thread (128-bit).
+#include "common.cuh"
+
+namespace pdb {
+
+static int ew_grid(int64_t n, int threads = 256) {
+  int64_t want = (n + threads - 1) / threads;
+  int64_t cap = (int64_t)num_sms() * 8;
+  return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
+// ---- MaxPool 3x3 / stride 2 / pad 1 -------------------------------------------------------------
+// argmax stores the window position 0..8 (kh*3+kw) of the first maximum, like cuDNN/ATen, so the
+// backward pass routes the gradient to exactly one input even when 16-bit values tie.
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y,
+                                                          uint8_t* __restrict__ argmax, int N, int H, int W, int C,
+                                                          int Ho, int Wo) {
+  const int cvec = C / 8;
+  const int64_t total = (int64_t)N * Ho * Wo * cvec, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cg = (int)(i % cvec);
+    int64_t t = i / cvec;
+    const int wo = (int)(t % Wo);
+    t /= Wo;
+    const int ho = (int)(t % Ho);
+    const int n = (int)(t / Ho);
+    float best[8];
+    int idx[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) best[k] = -INFINITY, idx[k] = 0;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int h = 2 * ho - 1 + kh;
+      if (h < 0 || h >= H) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int w = 2 * wo - 1 + kw;
+        if (w < 0 || w >= W) continue;
+        float f[8];
+        unpack8<T>(ldg128(x + (((int64_t)n * H + h) * W + w) * C + cg * 8), f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (f[k] > best[k]) best[k] = f[k], idx[k] = kh * 3 + kw;
+      }
+    }
+    stg128(y + i * 8, pack8<T>(best));
+    uint2 packed;
+    packed.x = idx[0] | (idx[1] << 8) | (idx[2] << 16) | (idx[3] << 24);
+    packed.y = idx[4] | (idx[5] << 8) | (idx[6] << 16) | (idx[7] << 24);
+    *reinterpret_cast<uint2*>(argmax + i * 8) = packed;
+  }
+}
+
+// Gather form: every input pixel collects from the (at most 2x2) windows that contain it — no atomics.
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ argmax,
+                                                          T* __restrict__ dx, int N, int H, int W, int C, int Ho,
+                                                          int Wo) {
+  const int cvec = C / 8;
+  const int64_t total = (int64_t)N * H * W * cvec, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cg = (int)(i % cvec);
+    int64_t t = i / cvec;
+    const int w = (int)(t % W);
+    t /= W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    float acc[8] = {0};
+    // windows with 2*ho-1 <= h <= 2*ho+1  <=>  ho in [(h-1)/2 .. (h+1)/2]
+    const int ho0 = h > 0 ? (h - 1) / 2 : 0, ho1 = min((h + 1) / 2, Ho - 1);
+    const int wo0 = w > 0 ? (w - 1) / 2 : 0, wo1 = min((w + 1) / 2, Wo - 1);
+    for (int ho = ho0; ho <= ho1; ++ho)
+      for (int wo = wo0; wo <= wo1; ++wo) {
+        const int pos = (h - (2 * ho - 1)) * 3 + (w - (2 * wo - 1));
+        const int64_t o = (((int64_t)n * Ho + ho) * Wo + wo) * C + cg * 8;
+        const uint2 a = *reinterpret_cast<const uint2*>(argmax + o);
+        float g[8];
+        unpack8<T>(ldg128(dy + o), g);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int id = ((k < 4 ? a.x : a.y) >> (8 * (k & 3))) & 0xff;
+          acc[k] += id == pos ? g[k] : 0.f;
+        }
+      }
+    stg128(dx + i * 8, pack8<T>(acc));
+  }
+}
+
+// ---- global average pool [N, HW, C] -> [N, C] ---------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int HW,
+                                                          int C) {
+  const int cvec = C / 8;
+  const int64_t total = (int64_t)N * cvec, stride = (int64_t)gridDim.x * blockDim.x;
+  const float inv = 1.0f / HW;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cg = (int)(i % cvec);
+    const int n = (int)(i / cvec);
+    float acc[8] = {0};
+    for (int p = 0; p < HW; ++p) {
+      float f[8];
+      unpack8<T>(ldg128(x + ((int64_t)n * HW + p) * C + cg * 8), f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] *= inv;
+    stg128(y + i * 8, pack8<T>(acc));
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int N, int HW,
+                                                          int C) {
+  const int cvec = C / 8;
+  const int64_t total = (int64_t)N * HW * cvec, stride = (int64_t)gridDim.x * blockDim.x;
+  const float inv = 1.0f / HW;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cg = (int)(i % cvec);
+    const int n = (int)(i / ((int64_t)HW * cvec));
+    float f[8];
+    unpack8<T>(ldg128(dy + ((int64_t)n * C + cg * 8)), f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] *= inv;
+    stg128(dx + i * 8, pack8<T>(f));
+  }
+}
+
+// ---- NCHW fp32 -> NHWC 16-bit (C small, e.g. 3): one thread per pixel ---------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__ y, int N, int C,
+                                                           int HW) {
+  const int64_t total = (int64_t)N * HW, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int64_t n = i / HW, p = i % HW;
+    for (int c = 0; c < C; ++c) y[i * C + c] = Elem<T>::from_f(__ldg(x + (n * C + c) * HW + p));
+  }
+}
+
+// ---- stem im2col: [N,3,H,W] fp32 -> [N*Ho*Wo, Kpad] 16-bit, column = (kh*7 + kw)*3 + c -----------
+// A block handles a run of output pixels of one output row; the needed input rows are read through
+// L1/L2 (each input element is reused by up to 16 patches).  One thread writes 8 columns (128 bit).
+template <typename T>
+__global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restrict__ x, T* __restrict__ col, int N,
+                                                          int H, int W, int Ho, int Wo, int Kpad) {
+  const int kvec = Kpad / 8;
+  const int64_t total = (int64_t)N * Ho * Wo * kvec, stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t HW = (int64_t)H * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int kv = (int)(i % kvec);
+    int64_t t = i / kvec;
+    const int wo = (int)(t % Wo);
+    t /= Wo;
+    const int ho = (int)(t % Ho);
+    const int n = (int)(t / Ho);
+    float f[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int kk = kv * 8 + k;
+      float v = 0.f;
+      if (kk < 147) {
+        const int c = kk % 3, tap = kk / 3, kw = tap % 7, kh = tap / 7;
+        const int h = 2 * ho - 3 + kh, w = 2 * wo - 3 + kw;
+        if (h >= 0 && h < H && w >= 0 && w < W) v = __ldg(x + ((int64_t)n * 3 + c) * HW + (int64_t)h * W + w);
+      }
+      f[k] = v;
+    }
+    stg128(col + i * 8, pack8<T>(f));
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) add16_kernel(const T* __restrict__ a, const T* __restrict__ b,
+                                                    T* __restrict__ o, int64_t nvec) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    float fa[8], fb[8];
+    unpack8<T>(ldg128_stream(a + i * 8), fa);
+    unpack8<T>(ldg128_stream(b + i * 8), fb);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) fa[k] += fb[k];
+    stg128(o + i * 8, pack8<T>(fa));
+  }
+}
+
+// dst[n, 2ho, 2wo] = src[n, ho, wo]; everything else zero.  One thread per destination vector.
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2_kernel(const T* __restrict__ src, T* __restrict__ dst, int N, int Ho,
+                                                        int Wo, int C) {
+  const int cvec = C / 8, H = 2 * Ho, W = 2 * Wo;
+  const int64_t total = (int64_t)N * H * W * cvec, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cg = (int)(i % cvec);
+    int64_t t = i / cvec;
+    const int w = (int)(t % W);
+    t /= W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (((h | w) & 1) == 0) v = ldg128_stream(src + (((int64_t)n * Ho + h / 2) * Wo + w / 2) * C + cg * 8);
+    stg128(dst + i * 8, v);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) add_strided2_kernel(const T* __restrict__ a, const T* __restrict__ b,
+                                                           T* __restrict__ o, int N, int H, int W, int C) {
+  const int cvec = C / 8, Ho = H / 2, Wo = W / 2;
+  const int64_t total = (int64_t)N * H * W * cvec, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int cg = (int)(i % cvec);
+    int64_t t = i / cvec;
+    const int w = (int)(t % W);
+    t /= W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    uint4 va = ldg128_stream(a + i * 8);
+    if (((h | w) & 1) == 0) {
+      float fa[8], fb[8];
+      unpack8<T>(va, fa);
+      unpack8<T>(ldg128_stream(b + (((int64_t)n * Ho + h / 2) * Wo + w / 2) * C + cg * 8), fb);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) fa[k] += fb[k];
+      va = pack8<T>(fa);
+    }
+    stg128(o + i * 8, va);
+  }
+}
+
+}  // namespace pdb
+using namespace pdb;
+
+#define ST ((cudaStream_t)stream)
+
+extern "C" int pdb_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int dtype, int N, int H, int W, int C,
+                                    void* stream) {
+  PDB_CHECK_ARG(x && y && argmax && N > 0 && H > 0 && W > 0 && C % 8 == 0, "pdb_maxpool3x3s2_fwd: bad arguments");
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const int64_t total = (int64_t)N * Ho * Wo * (C / 8);
+  PDB_DISPATCH_16(dtype, T, (maxpool_fwd_kernel<T><<<ew_grid(total), 256, 0, ST>>>((const T*)x, (T*)y, argmax, N, H, W,
+                                                                                    C, Ho, Wo)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int dtype, int N, int H, int W,
+                                    int C, void* stream) {
+  PDB_CHECK_ARG(dy && dx && argmax && N > 0 && H > 0 && W > 0 && C % 8 == 0, "pdb_maxpool3x3s2_bwd: bad arguments");
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const int64_t total = (int64_t)N * H * W * (C / 8);
+  PDB_DISPATCH_16(dtype, T, (maxpool_bwd_kernel<T><<<ew_grid(total), 256, 0, ST>>>((const T*)dy, argmax, (T*)dx, N, H,
+                                                                                    W, C, Ho, Wo)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW, int C, void* stream) {
+  PDB_CHECK_ARG(x && y && N > 0 && HW > 0 && C % 8 == 0, "pdb_avgpool_fwd: bad arguments");
+  PDB_DISPATCH_16(dtype, T, (avgpool_fwd_kernel<T><<<ew_grid((int64_t)N * C / 8, 128), 128, 0, ST>>>((const T*)x, (T*)y,
+                                                                                                      N, HW, C)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, void* stream) {
+  PDB_CHECK_ARG(dy && dx && N > 0 && HW > 0 && C % 8 == 0, "pdb_avgpool_bwd: bad arguments");
+  PDB_DISPATCH_16(dtype, T, (avgpool_bwd_kernel<T><<<ew_grid((int64_t)N * HW * C / 8), 256, 0, ST>>>((const T*)dy,
+                                                                                                      (T*)dx, N, HW, C)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_nchw_f32_to_nhwc16(const float* x, void* y, int dtype, int N, int C, int H, int W, void* stream) {
+  PDB_CHECK_ARG(x && y && N > 0 && C > 0 && H > 0 && W > 0, "pdb_nchw_f32_to_nhwc16: bad arguments");
+  PDB_DISPATCH_16(dtype, T, (nchw_to_nhwc_kernel<T><<<ew_grid((int64_t)N * H * W), 256, 0, ST>>>(x, (T*)y, N, C, H * W)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_stem_im2col(const float* x, void* col, int dtype, int N, int H, int W, int Kpad, void* stream) {
+  PDB_CHECK_ARG(x && col && N > 0 && H > 0 && W > 0 && Kpad >= 147 && Kpad % 8 == 0, "pdb_stem_im2col: bad arguments");
+  const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
+  const int64_t total = (int64_t)N * Ho * Wo * (Kpad / 8);
+  PDB_DISPATCH_16(dtype, T, (stem_im2col_kernel<T><<<ew_grid(total), 256, 0, ST>>>(x, (T*)col, N, H, W, Ho, Wo, Kpad)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_add16(const void* a, const void* b, void* out, int dtype, int64_t n, void* stream) {
+  PDB_CHECK_ARG(a && b && out && n > 0 && n % 8 == 0, "pdb_add16: bad arguments");
+  PDB_DISPATCH_16(dtype, T, (add16_kernel<T><<<ew_grid(n / 8), 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out, n / 8)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_upsample2_zero(const void* src, void* dst, int dtype, int N, int Ho, int Wo, int C, void* stream) {
+  PDB_CHECK_ARG(src && dst && N > 0 && Ho > 0 && Wo > 0 && C % 8 == 0, "pdb_upsample2_zero: bad arguments");
+  const int64_t total = (int64_t)N * Ho * Wo * 4 * (C / 8);
+  PDB_DISPATCH_16(dtype, T, (upsample2_kernel<T><<<ew_grid(total), 256, 0, ST>>>((const T*)src, (T*)dst, N, Ho, Wo, C)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_add_strided2(const void* a, const void* b, void* out, int dtype, int N, int H, int W, int C,
+                                void* stream) {
+  PDB_CHECK_ARG(a && b && out && N > 0 && H % 2 == 0 && W % 2 == 0 && C % 8 == 0, "pdb_add_strided2: bad arguments");
+  const int64_t total = (int64_t)N * H * W * (C / 8);
+  PDB_DISPATCH_16(dtype, T, (add_strided2_kernel<T><<<ew_grid(total), 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out,
+                                                                                     N, H, W, C)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---- weight layout helpers --------------------------------------------------------------------
+namespace pdb {
+template <typename T>
+__global__ void __launch_bounds__(256) weight_dgrad_kernel(const T* __restrict__ w, T* __restrict__ wt, int K, int R,
+                                                           int S, int C) {
+  // one thread per destination element; destination [C][R][S][K] is written coalesced along K
+  const int64_t total = (int64_t)C * R * S * K, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int k = (int)(i % K);
+    int64_t t = i / K;
+    const int s = (int)(t % S);
+    t /= S;
+    const int r = (int)(t % R);
+    const int c = (int)(t / R);
+    wt[i] = w[(((int64_t)k * R + (R - 1 - r)) * S + (S - 1 - s)) * C + c];
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) pad_rows_kernel(const T* __restrict__ src, T* __restrict__ dst, int rows,
+                                                       int cs, int cd) {
+  const int64_t total = (int64_t)rows * cd, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c = (int)(i % cd);
+    const int64_t r = i / cd;
+    dst[i] = c < cs ? src[r * cs + c] : Elem<T>::from_f(0.f);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ a, float* __restrict__ out, int rows,
+                                                     int cols) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float acc = 0.f;
+  for (int r = 0; r < rows; ++r) acc += Elem<T>::to_f(a[(int64_t)r * cols + c]);
+  out[c] += acc;
+}
+}  // namespace pdb
+
+extern "C" int pdb_weight_dgrad_layout(const void* w, void* wt, int dtype, int K, int R, int S, int C, void* stream) {
+  PDB_CHECK_ARG(w && wt && K > 0 && R > 0 && S > 0 && C > 0, "pdb_weight_dgrad_layout: bad arguments");
+  PDB_DISPATCH_16(dtype, T, (weight_dgrad_kernel<T><<<ew_grid((int64_t)K * R * S * C), 256, 0, ST>>>((const T*)w, (T*)wt,
+                                                                                                      K, R, S, C)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_pad_rows16(const void* src, void* dst, int dtype, int rows, int cols_src, int cols_dst,
+                              void* stream) {
+  PDB_CHECK_ARG(src && dst && rows > 0 && cols_src > 0 && cols_dst >= cols_src, "pdb_pad_rows16: bad arguments");
+  PDB_DISPATCH_16(dtype, T, (pad_rows_kernel<T><<<ew_grid((int64_t)rows * cols_dst), 256, 0, ST>>>(
+                                (const T*)src, (T*)dst, rows, cols_src, cols_dst)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_colsum16(const void* a, float* out, int dtype, int rows, int cols, void* stream) {
+  PDB_CHECK_ARG(a && out && rows > 0 && cols > 0, "pdb_colsum16: bad arguments");
+  PDB_DISPATCH_16(dtype, T, (colsum_kernel<T><<<(cols + 255) / 256, 256, 0, ST>>>((const T*)a, out, rows, cols)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,160 @@
+/* pdb200.h — C ABI of the sm_100a kernel library of pytorch_distributed_b200 (lib/libpdb200.so).
+ *
+ * Conventions
+ *   - every entry point returns 0 on success, non-zero on failure; pdb_last_error() then gives a
+ *     human-readable message (thread-local);
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises;
+ *   - activations are NHWC ("channels last") 16-bit, `dtype` selects the 16-bit format
+ *     (PDB_BF16 / PDB_FP16); statistics, master weights, gradients and the loss are fp32;
+ *   - "ref:" cites the reference script that causes the delegate kernel to run, "torch:" the
+ *     delegate whose behaviour is reproduced (see SURVEY.md §2.4 for the K-numbers).
+ */
+#ifndef PDB200_H_
+#define PDB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PDB_BF16 0
+#define PDB_FP16 1
+
+const char* pdb_last_error(void);
+int pdb_version(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * K9 — fused SGD step over flat arenas (ref:restnet_ddp.py:30 optimizer.step();
+ * torch:optim/sgd.py:322-380).  g' = (inv_scale? g*inv_scale : g) + wd*p;
+ * buf = first_step ? g' : momentum*buf + (1-dampening)*g';  p -= lr * (nesterov ? g'+momentum*buf : buf).
+ * If found_inf (device float) is non-null and non-zero the update is skipped on the device (no host
+ * sync; torch:amp/grad_scaler.py:363-373 does a .item()).  Optionally writes the 16-bit weight
+ * shadow and zeroes the gradient.  buf may be null when momentum == 0. */
+int pdb_sgd_step(float* p, float* g, float* buf, void* shadow16, int shadow_dtype, int64_t n, float lr,
+                 float momentum, float dampening, float weight_decay, int nesterov, int maximize,
+                 int first_step, const float* inv_scale, const float* found_inf, int zero_grad,
+                 void* stream);
+
+/* K13 — non-finite check of a flat fp32 range: *found_inf = 1.0f if any element is inf/nan
+ * (torch:amp/grad_scaler.py:349-361 _amp_foreach_non_finite_check_and_unscale_; the un-scale itself
+ * is folded into pdb_sgd_step / the all-reduce epilogue). */
+int pdb_check_finite(const float* g, int64_t n, float* found_inf, void* stream);
+
+/* fp32 -> 16-bit copy of a flat range (weight shadow refresh after load_state_dict). */
+int pdb_cast_f32_to_16(const float* src, void* dst, int dtype, int64_t n, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K10 — fused cross-entropy forward + backward (ref:restnet_ddp.py:28; torch:nn/functional.py:3421).
+ * logits [rows, classes] 16-bit; labels int64.  loss_sum += sum_i -log softmax(x_i)[y_i] / rows
+ * (caller zeroes *loss beforehand); dlogits = (softmax - onehot) * grad_scale / rows, same dtype.
+ * grad_scale may be null (1.0) or a device float (amp loss scale). */
+int pdb_xent_fwd_bwd(const void* logits, int dtype, const int64_t* labels, int rows, int classes,
+                     float* loss, void* dlogits, const float* grad_scale, void* stream);
+
+/* K14 — top-k hit counters (ref:restnet_ddp.py:58-60).  out[j] += #rows whose label ranks < ks[j].
+ * Ties are broken by index like torch.topk(sorted=True). */
+int pdb_topk_correct(const void* logits, int dtype, const int64_t* labels, int rows, int classes,
+                     const int* ks, int nk, float* out, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K8 — BatchNorm (+ReLU, +residual) on NHWC 16-bit activations, fp32 statistics
+ * (torch:nn/modules/batchnorm.py:144-210; eps 1e-5, momentum 0.1, unbiased running variance). */
+
+/* Per-channel sum and sum of squares of x[rows, C] into sums[2*C] (sum | sumsq).  Two-stage:
+ * per-block partials go to `scratch` (>= pdb_bn_stats_scratch_bytes(C) bytes, any contents) and the
+ * last block to finish folds them, in a fixed order, into sums — deterministic, no atomics on
+ * the data path.  The convolution epilogue normally produces these sums itself; this entry point is
+ * for layers whose producer is not one of our GEMMs and for tests. */
+size_t pdb_bn_stats_scratch_bytes(int C);
+int pdb_bn_stats(const void* x, int dtype, int64_t rows, int C, float* sums, void* scratch,
+                 size_t scratch_bytes, void* stream);
+
+/* y = [relu]( (x - mean) * rstd * gamma + beta [+ residual] ).  mean/rstd are derived from
+ * sums[2*C] over `count` elements per channel (count may exceed rows under SyncBN) inside the
+ * kernel; block 0 stores save_mean/save_rstd and updates running_mean/var/num_batches_tracked when
+ * given.  x and y may alias. */
+int pdb_bn_apply(const void* x, const void* residual, void* y, int dtype, int64_t rows, int C,
+                 const float* sums, double count, const float* gamma, const float* beta, float eps,
+                 float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
+                 float* save_mean, float* save_rstd, int relu, void* stream);
+
+/* Inference-mode BN: uses running statistics. */
+int pdb_bn_apply_eval(const void* x, const void* residual, void* y, int dtype, int64_t rows, int C,
+                      const float* running_mean, const float* running_var, const float* gamma,
+                      const float* beta, float eps, int relu, void* stream);
+
+/* Backward reductions: with g = dz * (z > 0 if z given), dsums[0:C] += sum g,
+ * dsums[C:2C] += sum g * (x - mean) * rstd.  dsums must be zeroed by the caller. */
+int pdb_bn_bwd_reduce(const void* dz, const void* z, const void* x, int dtype, int64_t rows, int C,
+                      const float* mean, const float* rstd, float* dsums, void* stream);
+
+/* dx = gamma*rstd * (g - dsums[c]/count - xhat * dsums[C+c]/count);  optionally also writes
+ * dres = g (gradient of the residual branch).  Block 0 accumulates dgamma += dsums[C:], dbeta +=
+ * dsums[:C] (fp32 gradient arena views; may be null). */
+int pdb_bn_bwd_apply(const void* dz, const void* z, const void* x, void* dx, void* dres, int dtype,
+                     int64_t rows, int C, const float* mean, const float* rstd, const float* gamma,
+                     const float* dsums, double count, float* dgamma, float* dbeta, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K12 — pooling on NHWC 16-bit. */
+int pdb_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int dtype, int N, int H, int W, int C,
+                         void* stream);
+int pdb_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int dtype, int N, int H, int W,
+                         int C, void* stream);
+int pdb_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW, int C, void* stream);
+int pdb_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Layout / elementwise helpers. */
+/* NCHW fp32 -> NHWC 16-bit (the loader yields NCHW fp32, ref:restnet_ddp.py:25). */
+int pdb_nchw_f32_to_nhwc16(const float* x, void* y, int dtype, int N, int C, int H, int W, void* stream);
+/* Stem im2col: NCHW fp32 [N,3,H,W] -> [N*Ho*Wo, Kpad] 16-bit patches for the 7x7/2 pad-3 stem conv
+ * (K = 147, columns ordered (kh, kw, c), zero padded to Kpad). */
+int pdb_stem_im2col(const float* x, void* col, int dtype, int N, int H, int W, int Kpad, void* stream);
+/* out = a + b (16-bit), used where a residual sum is not fused into a producer. */
+int pdb_add16(const void* a, const void* b, void* out, int dtype, int64_t n, void* stream);
+/* dst[n, 2h, 2w, :] = src[n, h, w, :], zeros elsewhere: zero-upsample by 2 (stride-2 dgrad input). */
+int pdb_upsample2_zero(const void* src, void* dst, int dtype, int N, int Ho, int Wo, int C, void* stream);
+/* out[n,h,w,:] = a[n,h,w,:] + (h,w even ? b[n,h/2,w/2,:] : 0): merges the stride-2 1x1 dgrad. */
+int pdb_add_strided2(const void* a, const void* b, void* out, int dtype, int N, int H, int W, int C,
+                     void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K7 / K11 — convolutions and the fc layer as tcgen05 implicit GEMMs (ref:restnet_ddp.py:26,29
+ * model(samples) / loss.backward(); delegates: cuDNN 9.22 conv fwd/dgrad/wgrad, cuBLASLt linear). */
+typedef struct {
+  int N, H, W, C;     /* input activation, NHWC; a plain GEMM is H = W = 1, N = rows */
+  int K;              /* output channels */
+  int R, S;           /* filter height / width */
+  int stride, pad;
+} pdb_conv_shape;
+
+/* y[N*P*Q, K] = conv(x, w).  w is [K, R, S, C] 16-bit (K-major rows of length R*S*C).  lda / ldd:
+ * row pitch in elements of x (plain 1x1 path only) and y; <= 0 means dense.  stats (nullable):
+ * fp32 [2K], per-channel sum | sum of squares of the rounded outputs are ADDED to it (zero it
+ * first) — the BatchNorm statistics pass fused into the epilogue.  bias (nullable): fp32 [K].
+ * block_n: 64 / 128 / 256, or 0 for the default heuristic.  dgrad is the same call on dY with the
+ * weights rearranged by pdb_weight_dgrad_layout. */
+int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, const pdb_conv_shape* s, int64_t lda,
+                   int64_t ldd, float* stats, const float* bias, int block_n, void* stream);
+
+/* dw[K, R*S*C] (fp32, row pitch ldw) += dy[N*P*Q, K]^T * im2col(x).  The pixel range is split over
+ * CTAs (`splits`, 0 = heuristic) and partial tiles are added with fp32 vector reductions, so dw
+ * must hold the running gradient (zero for a fresh step).  Only columns < kvalid are written
+ * (<= 0: all R*S*C). */
+int pdb_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, const pdb_conv_shape* s, int64_t ldx,
+                   int64_t lddy, int64_t ldw, int64_t kvalid, int splits, int block_n, void* stream);
+
+/* wt[C, R, S, K] = w[K, R-1-r, S-1-s, C]: weight layout for running dgrad through pdb_conv_fprop. */
+int pdb_weight_dgrad_layout(const void* w, void* wt, int dtype, int K, int R, int S, int C, void* stream);
+/* dst[rows, cols_dst] = src[rows, cols_src] zero-padded on the right (16-bit). */
+int pdb_pad_rows16(const void* src, void* dst, int dtype, int rows, int cols_src, int cols_dst, void* stream);
+/* out[c] += sum_r a[r, c] (16-bit in, fp32 out): fc bias gradient. */
+int pdb_colsum16(const void* a, float* out, int dtype, int rows, int cols, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDB200_H_ */

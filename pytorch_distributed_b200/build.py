@@ -105,7 +105,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
     if jobs or not out.exists() or force:
         objs = [str(OBJ / (s.stem + ".o")) for s in srcs]
         cuda_lib = str(Path(nvcc).resolve().parent.parent / "lib64")
-        cmd = [nvcc, "-shared", *NVCC_ARCH, "-o", str(out), *objs, f"-L{cuda_lib}", "-lcudart", "-lcuda"]
+        cmd = [nvcc, "-shared", *NVCC_ARCH, "-o", str(out), *objs, f"-L{cuda_lib}", "-lcudart"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -1,2 +1,51 @@
+"""ctypes signatures of include/pdb200.h."""
+import ctypes
+from ctypes import POINTER, Structure, c_char_p, c_double, c_float, c_int, c_int64, c_size_t, c_void_p
+
+P = c_void_p
+
+
+class ConvShape(Structure):
+    _fields_ = [("N", c_int), ("H", c_int), ("W", c_int), ("C", c_int), ("K", c_int), ("R", c_int), ("S", c_int),
+                ("stride", c_int), ("pad", c_int)]
+
+
 def declare(L):
-    pass
+    def sig(name, args, res=c_int):
+        f = getattr(L, name)
+        f.argtypes, f.restype = args, res
+
+    sig("pdb_last_error", [], c_char_p)
+    sig("pdb_version", [])
+    sig("pdb_sgd_step", [P, P, P, P, c_int, c_int64, c_float, c_float, c_float, c_float, c_int, c_int, c_int, P, P,
+                         c_int, P])
+    sig("pdb_check_finite", [P, c_int64, P, P])
+    sig("pdb_cast_f32_to_16", [P, P, c_int, c_int64, P])
+    sig("pdb_xent_fwd_bwd", [P, c_int, P, c_int, c_int, P, P, P, P])
+    sig("pdb_topk_correct", [P, c_int, P, c_int, c_int, P, c_int, P, P])
+    sig("pdb_bn_stats_scratch_bytes", [c_int], c_size_t)
+    sig("pdb_bn_stats", [P, c_int, c_int64, c_int, P, P, c_size_t, P])
+    sig("pdb_bn_apply", [P, P, P, c_int, c_int64, c_int, P, c_double, P, P, c_float, c_float, P, P, P, P, P, c_int, P])
+    sig("pdb_bn_apply_eval", [P, P, P, c_int, c_int64, c_int, P, P, P, P, c_float, c_int, P])
+    sig("pdb_bn_bwd_reduce", [P, P, P, c_int, c_int64, c_int, P, P, P, P])
+    sig("pdb_bn_bwd_apply", [P, P, P, P, P, c_int, c_int64, c_int, P, P, P, P, c_double, P, P, P])
+    sig("pdb_maxpool3x3s2_fwd", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])
+    sig("pdb_maxpool3x3s2_bwd", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])
+    sig("pdb_avgpool_fwd", [P, P, c_int, c_int, c_int, c_int, P])
+    sig("pdb_avgpool_bwd", [P, P, c_int, c_int, c_int, c_int, P])
+    sig("pdb_nchw_f32_to_nhwc16", [P, P, c_int, c_int, c_int, c_int, c_int, P])
+    sig("pdb_stem_im2col", [P, P, c_int, c_int, c_int, c_int, c_int, P])
+    sig("pdb_add16", [P, P, P, c_int, c_int64, P])
+    sig("pdb_upsample2_zero", [P, P, c_int, c_int, c_int, c_int, c_int, P])
+    sig("pdb_add_strided2", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])
+    sig("pdb_conv_fprop", [P, P, P, c_int, POINTER(ConvShape), c_int64, c_int64, P, P, c_int, P])
+    sig("pdb_conv_wgrad", [P, P, P, c_int, POINTER(ConvShape), c_int64, c_int64, c_int64, c_int64, c_int, c_int, P])
+    sig("pdb_weight_dgrad_layout", [P, P, c_int, c_int, c_int, c_int, c_int, P])
+    sig("pdb_pad_rows16", [P, P, c_int, c_int, c_int, c_int, P])
+    sig("pdb_colsum16", [P, P, c_int, c_int, c_int, P])
+    for name, args in OPTIONAL.items():
+        if hasattr(L, name):
+            sig(name, args)
+
+
+OPTIONAL = {}

@@ -1,1 +1,269 @@
-__all__ = []
+"""Tensor-level wrappers of the sm_100a kernels.  All launches go to the current CUDA stream."""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import check, count_launch, ptr, require, stream_ptr
+from ._sigs import ConvShape
+
+__all__ = ["dtype_tag", "sgd_step", "check_finite", "cast_to_16", "xent_fwd_bwd", "topk_correct", "bn_stats",
+           "bn_apply", "bn_apply_eval", "bn_bwd_reduce", "bn_bwd_apply", "maxpool_fwd", "maxpool_bwd",
+           "avgpool_fwd", "avgpool_bwd", "nchw_to_nhwc16", "stem_im2col", "add16", "upsample2_zero",
+           "add_strided2", "conv_fprop", "conv_wgrad", "weight_dgrad_layout", "pad_rows16", "colsum16",
+           "peer_copy", "peer_copy_", "reduce_to_root", "ConvShape"]
+
+_TAG = {torch.bfloat16: 0, torch.float16: 1}
+
+
+def dtype_tag(dt: torch.dtype) -> int:
+    try:
+        return _TAG[dt]
+    except KeyError:
+        raise TypeError(f"native kernels take bf16/fp16 activations, got {dt}") from None
+
+
+def _st(t: torch.Tensor):
+    return stream_ptr(t.device)
+
+
+def sgd_step(p, g, buf, shadow, *, lr, momentum, dampening, weight_decay, nesterov, maximize, first_step,
+             inv_scale=None, found_inf=None, zero_grad=False) -> None:
+    L = require()
+    with torch.cuda.device(p.device):
+        check(L.pdb_sgd_step(ptr(p), ptr(g), ptr(buf), ptr(shadow), dtype_tag(shadow.dtype) if shadow is not None else 0,
+                             p.numel(), lr, momentum, dampening, weight_decay, int(nesterov), int(maximize),
+                             int(first_step), ptr(inv_scale), ptr(found_inf), int(zero_grad), _st(p)), "pdb_sgd_step")
+    count_launch()
+
+
+def check_finite(g: torch.Tensor, found_inf: torch.Tensor) -> None:
+    check(require().pdb_check_finite(ptr(g), g.numel(), ptr(found_inf), _st(g)), "pdb_check_finite")
+    count_launch()
+
+
+def cast_to_16(src: torch.Tensor, dst: torch.Tensor) -> None:
+    check(require().pdb_cast_f32_to_16(ptr(src), ptr(dst), dtype_tag(dst.dtype), src.numel(), _st(src)),
+          "pdb_cast_f32_to_16")
+    count_launch()
+
+
+def xent_fwd_bwd(logits: torch.Tensor, labels: torch.Tensor, grad_scale: Optional[torch.Tensor] = None,
+                 need_grad: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    logits = logits.contiguous()
+    rows, classes = logits.shape
+    loss = torch.zeros((), dtype=torch.float32, device=logits.device)
+    dl = torch.empty_like(logits) if need_grad else None
+    check(require().pdb_xent_fwd_bwd(ptr(logits), dtype_tag(logits.dtype), ptr(labels), rows, classes, ptr(loss),
+                                     ptr(dl), ptr(grad_scale), _st(logits)), "pdb_xent_fwd_bwd")
+    count_launch()
+    return loss, dl
+
+
+_ks_cache = {}
+
+
+def topk_correct(logits: torch.Tensor, labels: torch.Tensor, ks: Sequence[int] = (1, 5)) -> torch.Tensor:
+    logits = logits.contiguous()
+    if logits.dtype not in _TAG:
+        logits = logits.to(torch.bfloat16)
+    key = (tuple(ks), logits.device)
+    if key not in _ks_cache:
+        _ks_cache[key] = torch.tensor(list(ks), dtype=torch.int32, device=logits.device)
+    out = torch.zeros(len(ks), dtype=torch.float32, device=logits.device)
+    check(require().pdb_topk_correct(ptr(logits), dtype_tag(logits.dtype), ptr(labels), logits.shape[0],
+                                     logits.shape[1], ptr(_ks_cache[key]), len(ks), ptr(out), _st(logits)),
+          "pdb_topk_correct")
+    count_launch()
+    return out
+
+
+_scratch = {}
+
+
+def bn_stats_scratch(C: int, device) -> torch.Tensor:
+    n = require().pdb_bn_stats_scratch_bytes(C)
+    key = (torch.device(device), torch.cuda.current_stream(device).cuda_stream)
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < n:
+        buf = torch.zeros(n, dtype=torch.uint8, device=device)      # ticket must start at 0
+        _scratch[key] = buf
+    return buf
+
+
+def bn_stats(x2d: torch.Tensor, sums: torch.Tensor, scratch: Optional[torch.Tensor] = None) -> None:
+    rows, C = x2d.shape
+    scratch = scratch if scratch is not None else bn_stats_scratch(C, x2d.device)
+    check(require().pdb_bn_stats(ptr(x2d), dtype_tag(x2d.dtype), rows, C, ptr(sums), ptr(scratch), scratch.numel(),
+                                 _st(x2d)), "pdb_bn_stats")
+    count_launch()
+
+
+def bn_apply(x, residual, y, sums, count, gamma, beta, eps, momentum, running_mean, running_var, nbt, save_mean,
+             save_rstd, relu: bool) -> None:
+    rows, C = x.shape
+    check(require().pdb_bn_apply(ptr(x), ptr(residual), ptr(y), dtype_tag(x.dtype), rows, C, ptr(sums), float(count),
+                                 ptr(gamma), ptr(beta), eps, momentum, ptr(running_mean), ptr(running_var), ptr(nbt),
+                                 ptr(save_mean), ptr(save_rstd), int(relu), _st(x)), "pdb_bn_apply")
+    count_launch()
+
+
+def bn_apply_eval(x, residual, y, running_mean, running_var, gamma, beta, eps, relu: bool) -> None:
+    rows, C = x.shape
+    check(require().pdb_bn_apply_eval(ptr(x), ptr(residual), ptr(y), dtype_tag(x.dtype), rows, C, ptr(running_mean),
+                                      ptr(running_var), ptr(gamma), ptr(beta), eps, int(relu), _st(x)),
+          "pdb_bn_apply_eval")
+    count_launch()
+
+
+def bn_bwd_reduce(dz, z, x, mean, rstd, dsums) -> None:
+    rows, C = x.shape
+    check(require().pdb_bn_bwd_reduce(ptr(dz), ptr(z), ptr(x), dtype_tag(x.dtype), rows, C, ptr(mean), ptr(rstd),
+                                      ptr(dsums), _st(x)), "pdb_bn_bwd_reduce")
+    count_launch()
+
+
+def bn_bwd_apply(dz, z, x, dx, dres, mean, rstd, gamma, dsums, count, dgamma, dbeta) -> None:
+    rows, C = x.shape
+    check(require().pdb_bn_bwd_apply(ptr(dz), ptr(z), ptr(x), ptr(dx), ptr(dres), dtype_tag(x.dtype), rows, C,
+                                     ptr(mean), ptr(rstd), ptr(gamma), ptr(dsums), float(count), ptr(dgamma),
+                                     ptr(dbeta), _st(x)), "pdb_bn_bwd_apply")
+    count_launch()
+
+
+def maxpool_fwd(x, y, argmax) -> None:
+    N, H, W, C = x.shape
+    check(require().pdb_maxpool3x3s2_fwd(ptr(x), ptr(y), ptr(argmax), dtype_tag(x.dtype), N, H, W, C, _st(x)),
+          "pdb_maxpool3x3s2_fwd")
+    count_launch()
+
+
+def maxpool_bwd(dy, argmax, dx) -> None:
+    N, H, W, C = dx.shape
+    check(require().pdb_maxpool3x3s2_bwd(ptr(dy), ptr(argmax), ptr(dx), dtype_tag(dx.dtype), N, H, W, C, _st(dx)),
+          "pdb_maxpool3x3s2_bwd")
+    count_launch()
+
+
+def avgpool_fwd(x, y) -> None:
+    N, H, W, C = x.shape
+    check(require().pdb_avgpool_fwd(ptr(x), ptr(y), dtype_tag(x.dtype), N, H * W, C, _st(x)), "pdb_avgpool_fwd")
+    count_launch()
+
+
+def avgpool_bwd(dy, dx) -> None:
+    N, H, W, C = dx.shape
+    check(require().pdb_avgpool_bwd(ptr(dy), ptr(dx), dtype_tag(dx.dtype), N, H * W, C, _st(dx)), "pdb_avgpool_bwd")
+    count_launch()
+
+
+def nchw_to_nhwc16(x: torch.Tensor, y: torch.Tensor) -> None:
+    N, C, H, W = x.shape
+    check(require().pdb_nchw_f32_to_nhwc16(ptr(x), ptr(y), dtype_tag(y.dtype), N, C, H, W, _st(x)),
+          "pdb_nchw_f32_to_nhwc16")
+    count_launch()
+
+
+def stem_im2col(x: torch.Tensor, col: torch.Tensor) -> None:
+    N, C, H, W = x.shape
+    assert C == 3 and x.dtype == torch.float32 and x.is_contiguous()
+    check(require().pdb_stem_im2col(ptr(x), ptr(col), dtype_tag(col.dtype), N, H, W, col.shape[-1], _st(x)),
+          "pdb_stem_im2col")
+    count_launch()
+
+
+def add16(a, b, out) -> None:
+    check(require().pdb_add16(ptr(a), ptr(b), ptr(out), dtype_tag(a.dtype), a.numel(), _st(a)), "pdb_add16")
+    count_launch()
+
+
+def upsample2_zero(src, dst) -> None:
+    N, Ho, Wo, C = src.shape
+    check(require().pdb_upsample2_zero(ptr(src), ptr(dst), dtype_tag(src.dtype), N, Ho, Wo, C, _st(src)),
+          "pdb_upsample2_zero")
+    count_launch()
+
+
+def add_strided2(a, b, out) -> None:
+    N, H, W, C = a.shape
+    check(require().pdb_add_strided2(ptr(a), ptr(b), ptr(out), dtype_tag(a.dtype), N, H, W, C, _st(a)),
+          "pdb_add_strided2")
+    count_launch()
+
+
+def conv_fprop(x, w, y, shape: ConvShape, *, lda: int = 0, ldd: int = 0, stats=None, bias=None, block_n: int = 0) -> None:
+    check(require().pdb_conv_fprop(ptr(x), ptr(w), ptr(y), dtype_tag(x.dtype), ctypes.byref(shape), lda, ldd,
+                                   ptr(stats), ptr(bias), block_n, _st(x)), "pdb_conv_fprop")
+    count_launch()
+
+
+def conv_wgrad(x, dy, dw, shape: ConvShape, *, ldx: int = 0, lddy: int = 0, ldw: int = 0, kvalid: int = 0,
+               splits: int = 0, block_n: int = 0) -> None:
+    check(require().pdb_conv_wgrad(ptr(x), ptr(dy), ptr(dw), dtype_tag(x.dtype), ctypes.byref(shape), ldx, lddy, ldw,
+                                   kvalid, splits, block_n, _st(x)), "pdb_conv_wgrad")
+    count_launch()
+
+
+def weight_dgrad_layout(w, wt, K, R, S, C) -> None:
+    check(require().pdb_weight_dgrad_layout(ptr(w), ptr(wt), dtype_tag(w.dtype), K, R, S, C, _st(w)),
+          "pdb_weight_dgrad_layout")
+    count_launch()
+
+
+def pad_rows16(src, dst, rows, cols_src, cols_dst) -> None:
+    check(require().pdb_pad_rows16(ptr(src), ptr(dst), dtype_tag(src.dtype), rows, cols_src, cols_dst, _st(src)),
+          "pdb_pad_rows16")
+    count_launch()
+
+
+def colsum16(a, out) -> None:
+    rows, cols = a.shape
+    check(require().pdb_colsum16(ptr(a), ptr(out), dtype_tag(a.dtype), rows, cols, _st(a)), "pdb_colsum16")
+    count_launch()
+
+
+# ---- peer-memory helpers (single-process DP mode); kernels land in csrc/comm/p2p.cu ----------------
+def _has(name: str) -> bool:
+    return hasattr(require(), name)
+
+
+def peer_copy_(dst: torch.Tensor, src: torch.Tensor) -> None:
+    """dst (on its own GPU) pulls src's bytes over NVLink (K4a/K4b/K4c)."""
+    if not _has("pdb_peer_pull"):
+        dst.copy_(src, non_blocking=True)
+        return
+    assert dst.is_contiguous() and src.is_contiguous() and dst.numel() * dst.element_size() == src.numel() * src.element_size()
+    src_ev = torch.cuda.Event()
+    src_ev.record(torch.cuda.current_stream(src.device))
+    with torch.cuda.device(dst.device):
+        torch.cuda.current_stream(dst.device).wait_event(src_ev)
+        check(require().pdb_peer_pull(ptr(dst), ptr(src), dst.numel() * dst.element_size(), _st(dst)), "pdb_peer_pull")
+    count_launch()
+
+
+def peer_copy(src: torch.Tensor, device: torch.device) -> torch.Tensor:
+    dst = torch.empty(src.shape, dtype=src.dtype, device=device)
+    peer_copy_(dst, src.contiguous())
+    return dst
+
+
+def reduce_to_root(root: torch.Tensor, peers) -> None:
+    """root += sum(peers): GPU 0 reads every replica's gradient arena over NVLink (K4d)."""
+    if not _has("pdb_reduce_to_root"):
+        for g in peers:
+            root.add_(g.to(root.device))
+        return
+    evs = []
+    for g in peers:
+        e = torch.cuda.Event()
+        e.record(torch.cuda.current_stream(g.device))
+        evs.append(e)
+    with torch.cuda.device(root.device):
+        for e in evs:
+            torch.cuda.current_stream(root.device).wait_event(e)
+        arr = (ctypes.c_void_p * len(peers))(*[g.data_ptr() for g in peers])
+        check(require().pdb_reduce_to_root(ptr(root), arr, len(peers), root.numel(), _st(root)), "pdb_reduce_to_root")
+    count_launch()

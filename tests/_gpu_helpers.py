@@ -1,0 +1,66 @@
+"""fp32 PyTorch oracles for the sm_100a kernels + small runners shared by tests and probes."""
+import torch
+import torch.nn.functional as F
+
+from pytorch_distributed_b200 import ops
+from pytorch_distributed_b200.ops import ConvShape
+
+
+def rel_err(a: torch.Tensor, b: torch.Tensor) -> float:
+    a, b = a.float(), b.float()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-12))
+
+
+def conv_case(N, H, W, C, K, R, S, stride, pad, dtype=torch.bfloat16, block_n=0, stats=True, seed=0):
+    """Runs pdb_conv_fprop and returns (rel_err_y, rel_err_stats)."""
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    x = torch.randn(N, H, W, C, device="cuda", generator=g).to(dtype)
+    w = (torch.randn(K, R, S, C, device="cuda", generator=g) / (R * S * C) ** 0.5).to(dtype)
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+    y = torch.full((N, P, Q, K), float("nan"), device="cuda", dtype=dtype)
+    st = torch.zeros(2 * K, device="cuda") if stats else None
+    ops.conv_fprop(x, w, y, ConvShape(N, H, W, C, K, R, S, stride, pad), stats=st, block_n=block_n)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), stride=stride, padding=pad)
+    ref = ref.permute(0, 2, 3, 1)
+    e_y = rel_err(y, ref)
+    e_s = 0.0
+    if stats:
+        yf = y.float().reshape(-1, K)
+        e_s = max(rel_err(st[:K], yf.sum(0)), rel_err(st[K:], (yf * yf).sum(0)))
+    return e_y, e_s
+
+
+def wgrad_case(N, H, W, C, K, R, S, stride, pad, dtype=torch.bfloat16, block_n=0, splits=0, seed=0):
+    torch.backends.cudnn.allow_tf32 = False
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    x = torch.randn(N, H, W, C, device="cuda", generator=g).to(dtype)
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+    dy = torch.randn(N, P, Q, K, device="cuda", generator=g).to(dtype)
+    dw = torch.zeros(K, R, S, C, device="cuda")
+    ops.conv_wgrad(x, dy, dw, ConvShape(N, H, W, C, K, R, S, stride, pad), splits=splits, block_n=block_n)
+    torch.cuda.synchronize()
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(False)
+    wr = torch.zeros(K, C, R, S, device="cuda", requires_grad=True)
+    out = F.conv2d(xr, wr, stride=stride, padding=pad)
+    out.backward(dy.float().permute(0, 3, 1, 2))
+    return rel_err(dw, wr.grad.permute(0, 2, 3, 1))
+
+
+def dgrad_case(N, H, W, C, K, R, S, pad, dtype=torch.bfloat16, seed=0):
+    """stride-1 dgrad through conv_fprop with the flipped/transposed weights."""
+    torch.backends.cudnn.allow_tf32 = False
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    w = (torch.randn(K, R, S, C, device="cuda", generator=g) / (R * S * C) ** 0.5).to(dtype)
+    P, Q = H + 2 * pad - R + 1, W + 2 * pad - S + 1
+    dy = torch.randn(N, P, Q, K, device="cuda", generator=g).to(dtype)
+    wt = torch.empty(C, R, S, K, device="cuda", dtype=dtype)
+    ops.weight_dgrad_layout(w, wt, K, R, S, C)
+    dx = torch.full((N, H, W, C), float("nan"), device="cuda", dtype=dtype)
+    ops.conv_fprop(dy, wt, dx, ConvShape(N, P, Q, K, C, R, S, 1, R - 1 - pad))
+    torch.cuda.synchronize()
+    xr = torch.zeros(N, C, H, W, device="cuda", requires_grad=True)
+    F.conv2d(xr, w.float().permute(0, 3, 1, 2), padding=pad).backward(dy.float().permute(0, 3, 1, 2))
+    return rel_err(dx, xr.grad.permute(0, 2, 3, 1))

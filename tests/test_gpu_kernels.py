@@ -1,0 +1,196 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 reference of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from pytorch_distributed_b200 import ops  # noqa: E402
+from pytorch_distributed_b200.optim.sgd import _flat_sgd  # noqa: E402
+
+from ._gpu_helpers import rel_err  # noqa: E402
+
+DT = [torch.bfloat16, torch.float16]
+
+
+def test_library_loaded():
+    assert ops.available(), "libpdb200.so must load on a GPU box (no silent fallback)"
+
+
+@pytest.mark.parametrize("first", [True, False])
+@pytest.mark.parametrize("nesterov", [False, True])
+def test_sgd_step(first, nesterov):
+    n = 1 << 20
+    g = torch.Generator(device="cuda").manual_seed(0)
+    p = torch.randn(n, device="cuda", generator=g)
+    gr = torch.randn(n, device="cuda", generator=g) * 64
+    buf = torch.randn(n, device="cuda", generator=g)
+    inv = torch.tensor(1 / 64.0, device="cuda")
+    rp, rb = p.clone(), buf.clone()
+    _flat_sgd(rp, gr, rb, lr=0.1, momentum=0.9, dampening=0.0, weight_decay=1e-4, nesterov=nesterov,
+              maximize=False, first_step=first, inv_scale=inv)
+    shadow = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    g2 = gr.clone()
+    ops.sgd_step(p, g2, buf, shadow, lr=0.1, momentum=0.9, dampening=0.0, weight_decay=1e-4, nesterov=nesterov,
+                 maximize=False, first_step=first, inv_scale=inv, found_inf=torch.zeros((), device="cuda"),
+                 zero_grad=True)
+    assert torch.allclose(p, rp, rtol=1e-5, atol=1e-6) and torch.allclose(buf, rb, rtol=1e-5, atol=1e-6)
+    assert torch.equal(shadow, p.to(torch.bfloat16)) and float(g2.abs().max()) == 0.0
+
+
+def test_sgd_skips_on_found_inf_and_check_finite():
+    n = 4096
+    p = torch.randn(n, device="cuda")
+    g = torch.randn(n, device="cuda")
+    buf = torch.randn(n, device="cuda")
+    g[77] = float("inf")
+    flag = torch.zeros((), device="cuda")
+    ops.check_finite(g, flag)
+    assert float(flag) == 1.0
+    p0, b0 = p.clone(), buf.clone()
+    ops.sgd_step(p, g, buf, None, lr=0.1, momentum=0.9, dampening=0.0, weight_decay=0.0, nesterov=False,
+                 maximize=False, first_step=False, found_inf=flag)
+    assert torch.equal(p, p0) and torch.equal(buf, b0)
+    ok = torch.zeros((), device="cuda")
+    ops.check_finite(torch.randn(n, device="cuda"), ok)
+    assert float(ok) == 0.0
+
+
+@pytest.mark.parametrize("dt", DT)
+def test_xent_and_topk(dt):
+    g = torch.Generator(device="cuda").manual_seed(1)
+    logits = (torch.randn(400, 1000, device="cuda", generator=g) * 3).to(dt)
+    labels = torch.randint(0, 1000, (400,), device="cuda", generator=g)
+    scale = torch.tensor(128.0, device="cuda")
+    loss, dl = ops.xent_fwd_bwd(logits, labels, grad_scale=scale)
+    ref_in = logits.float().requires_grad_(True)
+    ref = F.cross_entropy(ref_in, labels)
+    ref.backward()
+    assert abs(float(loss) - float(ref)) < 1e-3 * abs(float(ref))
+    assert rel_err(dl, ref_in.grad * 128.0) < (1e-2 if dt == torch.bfloat16 else 2e-3)
+    hits = ops.topk_correct(logits, labels, (1, 5))
+    _, pred = logits.float().topk(5, -1, True, True)
+    eq = pred.eq(labels[:, None])
+    assert hits.tolist() == [float(eq[:, :1].sum()), float(eq.sum())]
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("rows,C", [(4 * 56 * 56, 64), (3 * 14 * 14, 1024), (5 * 49, 2048), (1000, 24)])
+def test_bn_forward(dt, rows, C):
+    g = torch.Generator(device="cuda").manual_seed(2)
+    x = (torch.randn(rows, C, device="cuda", generator=g) * 2 + 0.5).to(dt)
+    res = torch.randn(rows, C, device="cuda", generator=g).to(dt)
+    gamma = torch.rand(C, device="cuda", generator=g) + 0.5
+    beta = torch.randn(C, device="cuda", generator=g)
+    sums = torch.empty(2 * C, device="cuda")
+    ops.bn_stats(x, sums)
+    ops.bn_stats(x, sums)                       # scratch ticket must have been reset by the first call
+    xf = x.float()
+    assert rel_err(sums[:C], xf.sum(0)) < 1e-4 and rel_err(sums[C:], (xf * xf).sum(0)) < 1e-4
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    nbt = torch.zeros((), dtype=torch.int64, device="cuda")
+    mean, rstd = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
+    y = torch.empty_like(x)
+    ops.bn_apply(x, res, y, sums, rows, gamma, beta, 1e-5, 0.1, rm, rv, nbt, mean, rstd, True)
+    rrm, rrv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    ref = F.batch_norm(xf, rrm, rrv, gamma, beta, True, 0.1, 1e-5)
+    ref = F.relu(ref + res.float())
+    assert rel_err(y, ref) < (1.5e-2 if dt == torch.bfloat16 else 2e-3)
+    assert torch.allclose(rm, rrm, rtol=1e-3, atol=1e-4) and torch.allclose(rv, rrv, rtol=1e-3, atol=1e-4)
+    assert int(nbt) == 1
+    assert torch.allclose(mean, xf.mean(0), rtol=1e-3, atol=1e-4)
+    ye = torch.empty_like(x)
+    ops.bn_apply_eval(x, None, ye, rm, rv, gamma, beta, 1e-5, False)
+    assert rel_err(ye, F.batch_norm(xf, rm, rv, gamma, beta, False, 0.0, 1e-5)) < 1.5e-2
+
+
+@pytest.mark.parametrize("dt", DT)
+@pytest.mark.parametrize("rows,C,with_z", [(4 * 28 * 28, 128, True), (2 * 49, 2048, True), (3000, 256, False)])
+def test_bn_backward(dt, rows, C, with_z):
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = (torch.randn(rows, C, device="cuda", generator=g) * 1.5 + 0.3).to(dt)
+    gamma = torch.rand(C, device="cuda", generator=g) + 0.5
+    beta = torch.randn(C, device="cuda", generator=g) * 0.1
+    dz = torch.randn(rows, C, device="cuda", generator=g).to(dt)
+    xr = x.float().requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    pre = F.batch_norm(xr, None, None, gr, br, True, 0.1, 1e-5)
+    z = F.relu(pre) if with_z else pre
+    z.backward(dz.float())
+    xf = x.float()
+    mean, var = xf.mean(0), xf.var(0, unbiased=False)
+    rstd = torch.rsqrt(var + 1e-5)
+    zt = z.detach().to(dt) if with_z else None
+    dsums = torch.zeros(2 * C, device="cuda")
+    ops.bn_bwd_reduce(dz, zt, x, mean, rstd, dsums)
+    dx, dres = torch.empty_like(x), torch.empty_like(x)
+    dgamma, dbeta = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+    ops.bn_bwd_apply(dz, zt, x, dx, dres, mean, rstd, gamma, dsums, rows, dgamma, dbeta)
+    tol = 2e-2 if dt == torch.bfloat16 else 4e-3
+    assert rel_err(dgamma, gr.grad) < tol and rel_err(dbeta, br.grad) < tol
+    assert rel_err(dx, xr.grad) < tol
+    mask = (z.detach() > 0).float() if with_z else 1.0
+    assert rel_err(dres, dz.float() * mask) < 1e-6
+
+
+@pytest.mark.parametrize("dt", DT)
+def test_pools(dt):
+    g = torch.Generator(device="cuda").manual_seed(4)
+    x = torch.randn(3, 20, 20, 64, device="cuda", generator=g).to(dt)
+    x[0, :4, :4] = 0                                          # ties (post-ReLU zeros)
+    y = torch.empty(3, 10, 10, 64, device="cuda", dtype=dt)
+    am = torch.empty(3, 10, 10, 64, device="cuda", dtype=torch.uint8)
+    ops.maxpool_fwd(x, y, am)
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    ref = F.max_pool2d(xr, 3, 2, 1)
+    assert torch.equal(y.float(), ref.permute(0, 2, 3, 1))
+    dy = torch.randn(3, 10, 10, 64, device="cuda", generator=g).to(dt)
+    ref.backward(dy.float().permute(0, 3, 1, 2))
+    dx = torch.empty_like(x)
+    ops.maxpool_bwd(dy, am, dx)
+    assert rel_err(dx, xr.grad.permute(0, 2, 3, 1)) < 1e-2
+    a = torch.randn(5, 7, 7, 128, device="cuda", generator=g).to(dt)
+    o = torch.empty(5, 128, device="cuda", dtype=dt)
+    ops.avgpool_fwd(a, o)
+    assert rel_err(o, a.float().mean((1, 2))) < 1e-2
+    do = torch.randn(5, 128, device="cuda", generator=g).to(dt)
+    da = torch.empty_like(a)
+    ops.avgpool_bwd(do, da)
+    assert rel_err(da, (do.float() / 49)[:, None, None, :].expand(5, 7, 7, 128)) < 1e-2
+
+
+@pytest.mark.parametrize("dt", DT)
+def test_layout_helpers(dt):
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(2, 3, 32, 32, device="cuda", generator=g)
+    y = torch.empty(2, 32, 32, 3, device="cuda", dtype=dt)
+    ops.nchw_to_nhwc16(x, y)
+    assert torch.equal(y, x.permute(0, 2, 3, 1).to(dt))
+    col = torch.empty(2 * 16 * 16, 152, device="cuda", dtype=dt)
+    ops.stem_im2col(x, col)
+    ref = F.unfold(x, 7, padding=3, stride=2)                  # [N, C*49, L], rows ordered (c, kh, kw)
+    ref = ref.view(2, 3, 49, 256).permute(0, 3, 2, 1).reshape(512, 147)   # -> (kh*7+kw)*3 + c
+    assert torch.equal(col[:, :147], ref.to(dt)) and float(col[:, 147:].abs().max()) == 0.0
+    a = torch.randn(2, 8, 8, 16, device="cuda", generator=g).to(dt)
+    b = torch.randn(2, 8, 8, 16, device="cuda", generator=g).to(dt)
+    o = torch.empty_like(a)
+    ops.add16(a, b, o)
+    assert torch.equal(o, (a.float() + b.float()).to(dt))
+    s = torch.randn(2, 4, 4, 16, device="cuda", generator=g).to(dt)
+    up = torch.empty(2, 8, 8, 16, device="cuda", dtype=dt)
+    ops.upsample2_zero(s, up)
+    ref_up = torch.zeros(2, 8, 8, 16, device="cuda", dtype=dt)
+    ref_up[:, ::2, ::2] = s
+    assert torch.equal(up, ref_up)
+    ops.add_strided2(a, s, o)
+    assert torch.equal(o, (a.float() + ref_up.float()).to(dt))
+    w = torch.randn(8, 3, 3, 16, device="cuda", generator=g).to(dt)
+    wt = torch.empty(16, 3, 3, 8, device="cuda", dtype=dt)
+    ops.weight_dgrad_layout(w, wt, 8, 3, 3, 16)
+    assert torch.equal(wt, w.flip(1, 2).permute(3, 1, 2, 0).contiguous())
+    pd = torch.empty(8, 152, device="cuda", dtype=dt)
+    ops.pad_rows16(w.reshape(8, 144), pd, 8, 144, 152)
+    assert torch.equal(pd[:, :144], w.reshape(8, 144)) and float(pd[:, 144:].abs().max()) == 0
+    cs = torch.zeros(16, device="cuda")
+    ops.colsum16(a.reshape(-1, 16), cs)
+    assert rel_err(cs, a.float().reshape(-1, 16).sum(0)) < 1e-5
