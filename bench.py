@@ -192,7 +192,6 @@ def run_ours(args):
     from pytorch_distributed_b200.nn import CrossEntropyLoss
     from pytorch_distributed_b200.optim import SGD, StepLR
     from pytorch_distributed_b200.parallel import DistributedDataParallel
-    from pytorch_distributed_b200.utils import BufferArena, ParamArena
 
     cfg = TrainConfig(mode=args.mode, batch_size=args.batch, dtype=args.dtype, engine=args.engine,
                       backend=args.backend, sync_bn=args.sync_bn, device="cuda", seed=rank)
@@ -205,7 +204,7 @@ def run_ours(args):
     if args.mode in ("ddp", "ddp_amp"):
         wrapped = DistributedDataParallel(model, device_ids=[local], backend=args.backend)
     else:
-        ParamArena(model, device), BufferArena(model, device)
+        harness.ensure_arenas(model, device)
         wrapped = model
     criterion = CrossEntropyLoss()
     optimizer = SGD(wrapped.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)

@@ -1,0 +1,99 @@
+"""Per-kernel-class device time of one native training step (CUDA events around every launch).
+
+Serialises the step (an event pair per kernel), so compare SHARES, not the absolute total.
+  python bench_tools/layer_times.py [--batch 400] [--out gpurun_out/layer_times.json]
+"""
+import argparse
+import collections
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+from pytorch_distributed_b200 import amp, harness, ops  # noqa: E402
+from pytorch_distributed_b200.config import TrainConfig  # noqa: E402
+from pytorch_distributed_b200.nn import CrossEntropyLoss  # noqa: E402
+from pytorch_distributed_b200.ops import elementwise as E  # noqa: E402
+from pytorch_distributed_b200.optim import SGD  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=400)
+    ap.add_argument("--out", default="gpurun_out/layer_times.json")
+    args = ap.parse_args()
+    dev = torch.device("cuda", 0)
+    cfg = TrainConfig(mode="ddp_amp", batch_size=args.batch, dtype="bf16", device="cuda")
+    model = harness.build_model(cfg, dev)
+    model.enable_native(batch_size=args.batch, dtype=torch.bfloat16)
+    opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    sc = amp.GradScaler(device=dev)
+    crit = CrossEntropyLoss()
+    x = torch.randn(args.batch, 3, 224, 224, device=dev)
+    y = torch.randint(0, 1000, (args.batch,), device=dev)
+    model.train()
+    for _ in range(3):
+        harness.train_step(model, crit, opt, x, y, cfg, dev, sc, stock_autocast=False)
+    torch.cuda.synchronize()
+
+    records = []
+    names = [n for n in E.__all__ if callable(getattr(ops, n, None)) and n not in ("dtype_tag", "ConvShape")]
+    originals = {}
+
+    def wrap(name, fn):
+        def inner(*a, **k):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            r = fn(*a, **k)
+            e1.record()
+            tag = name
+            if name in ("conv_fprop", "conv_wgrad"):
+                s = a[3]
+                tag = f"{name} {s.C}->{s.K} {s.R}x{s.S}/{s.stride} M={s.N * ((s.H + 2 * s.pad - s.R) // s.stride + 1) * ((s.W + 2 * s.pad - s.S) // s.stride + 1)}"
+                flops = 2.0 * s.N * ((s.H + 2 * s.pad - s.R) // s.stride + 1) * ((s.W + 2 * s.pad - s.S) // s.stride + 1) * s.K * s.C * s.R * s.S
+            else:
+                flops = 0.0
+            records.append((name, tag, e0, e1, flops))
+            return r
+        return inner
+
+    import pytorch_distributed_b200.models.native_resnet as NR
+    import pytorch_distributed_b200.optim.sgd as SG
+    for n in names:
+        originals[n] = getattr(ops, n)
+        setattr(ops, n, wrap(n, originals[n]))
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record()
+    harness.train_step(model, crit, opt, x, y, cfg, dev, sc, stock_autocast=False)
+    a1.record()
+    torch.cuda.synchronize()
+    for n in names:
+        setattr(ops, n, originals[n])
+    by_class = collections.OrderedDict()
+    by_tag = collections.OrderedDict()
+    for name, tag, e0, e1, flops in records:
+        ms = e0.elapsed_time(e1)
+        c = by_class.setdefault(name, [0, 0.0, 0.0])
+        c[0] += 1; c[1] += ms; c[2] += flops
+        t = by_tag.setdefault(tag, [0, 0.0, 0.0])
+        t[0] += 1; t[1] += ms; t[2] += flops
+    total = a0.elapsed_time(a1)
+    out = {"batch": args.batch, "step_ms_serialised": total, "launches": len(records),
+           "by_class": {k: {"n": v[0], "ms": round(v[1], 3), "tflops": round(v[2] / v[1] / 1e9, 1) if v[1] > 0 and v[2] else None}
+                        for k, v in sorted(by_class.items(), key=lambda kv: -kv[1][1])},
+           "by_shape": {k: {"n": v[0], "ms": round(v[1], 3), "tflops": round(v[2] / v[1] / 1e9, 1) if v[1] > 0 and v[2] else None}
+                        for k, v in sorted(by_tag.items(), key=lambda kv: -kv[1][1])[:60]}}
+    os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
+    with open(args.out, "w") as f:
+        json.dump(out, f, indent=1)
+    print(json.dumps({"step_ms_serialised": total, "launches": len(records)}))
+    for k, v in list(out["by_class"].items())[:14]:
+        print(f"{k:22s} n={v['n']:4d} ms={v['ms']:9.3f} tflops={v['tflops']}")
+
+
+if __name__ == "__main__":
+    main()

@@ -67,9 +67,9 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ 
     const int h = (int)(t % H);
     const int n = (int)(t / H);
     float acc[8] = {0};
-    // windows with 2*ho-1 <= h <= 2*ho+1  <=>  ho in [(h-1)/2 .. (h+1)/2]
-    const int ho0 = h > 0 ? (h - 1) / 2 : 0, ho1 = min((h + 1) / 2, Ho - 1);
-    const int wo0 = w > 0 ? (w - 1) / 2 : 0, wo1 = min((w + 1) / 2, Wo - 1);
+    // windows with 2*ho-1 <= h <= 2*ho+1  <=>  ho in [ceil((h-1)/2) .. floor((h+1)/2)] = [h/2 .. (h+1)/2]
+    const int ho0 = h / 2, ho1 = min((h + 1) / 2, Ho - 1);
+    const int wo0 = w / 2, wo1 = min((w + 1) / 2, Wo - 1);
     for (int ho = ho0; ho <= ho1; ++ho)
       for (int wo = wo0; wo <= wo1; ++wo) {
         const int pos = (h - (2 * ho - 1)) * 3 + (w - (2 * wo - 1));

@@ -141,10 +141,20 @@ class GradScaler:
             if not self._unscaled:
                 arena = getattr(optimizer, "arena", None)
                 grads = [arena.grads] if arena is not None else [p.grad for p in params if p.grad is not None]
-                if not (grads and grads[0].is_cuda):
+                if grads and grads[0].is_cuda:
+                    from . import ops
+                    if ops.available():
+                        for g in grads:
+                            if g.numel() % 4 == 0 and g.is_contiguous():
+                                ops.check_finite(g, self._found_inf)        # K13, one read of the arena
+                            else:
+                                self._found_inf.add_((~torch.isfinite(g)).any().to(torch.float32)).clamp_(max=1.0)
+                    else:
+                        for g in grads:
+                            self._found_inf.add_((~torch.isfinite(g)).any().to(torch.float32)).clamp_(max=1.0)
+                else:
                     for g in grads:
                         self._found_inf.add_((~torch.isfinite(g)).any().to(torch.float32)).clamp_(max=1.0)
-                # on CUDA the inf check is part of ops.sgd_step (reads grads once)
             self._unscaled = True
             return optimizer.step(*args, inv_scale=inv, found_inf=self._found_inf, **kwargs)
         # Foreign optimizer: torch semantics, host sync included.

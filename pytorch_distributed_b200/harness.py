@@ -172,6 +172,17 @@ def validate(dataloader, model, criterion, epoch: int, cfg: TrainConfig, device:
     return c1 / total
 
 
+def ensure_arenas(model, device: torch.device):
+    """Re-home parameters / buffers into arenas unless that has been done already (the native engine
+    and the parallel wrappers do it themselves; doing it twice would orphan their views)."""
+    from .utils import BufferArena, ParamArena
+    if getattr(model, "_pdb200_arena", None) is None:
+        ParamArena(model, device)
+    if getattr(model, "_pdb200_buffer_arena", None) is None:
+        BufferArena(model, device)
+    return model._pdb200_arena
+
+
 def build_model(cfg: TrainConfig, device: torch.device) -> ResNet:
     torch.manual_seed(cfg.seed)
     model = ResNet(cfg.layers, num_classes=cfg.num_classes, width=cfg.width)
@@ -222,9 +233,7 @@ def main(cfg: TrainConfig, local_rank: int = 0) -> float:
                                           backend=cfg.backend)
         loader_batch = cfg.batch_size
     else:
-        from .utils import BufferArena, ParamArena
-        ParamArena(model, device)
-        BufferArena(model, device)
+        ensure_arenas(model, device)
         wrapped = model
         loader_batch = cfg.batch_size
 

@@ -1,0 +1,362 @@
+"""Native sm_100a step graph for ResNet-50: the whole forward/backward as a fixed kernel sequence.
+
+The reference's delegates execute ResNet-50 op by op through the dispatcher: ~160 forward and ~320
+backward launches of cuDNN / ATen kernels per step, NCHW tensors, autograd bookkeeping per op
+(SURVEY.md §3.2).  Here the network is a *static plan* over NHWC 16-bit buffers:
+
+  conv  : tcgen05/TMA implicit GEMM (csrc/ops/conv_gemm.cu); its epilogue also produces the
+          per-channel sum / sum-of-squares the following BatchNorm needs;
+  BN    : one fused normalise(+residual)+ReLU pass forward, one reduce + one apply pass backward
+          (csrc/ops/batchnorm.cu);
+  dgrad : the same GEMM kernel on dY with flipped/transposed weights (stride-2 layers run on a
+          zero-upsampled dY); wgrad: the MN-major split-K GEMM, accumulating straight into the fp32
+          gradient arena (no per-parameter gradient tensors, nothing for DDP to flatten).
+
+PyTorch sees ONE autograd node (``_NativeStep``).  Gradients are written into the ``ParamArena`` in
+place; when the model is wrapped in our DistributedDataParallel the engine tells it, at statically
+known points of the backward sequence, which parameters are complete so the bucket all-reduce can
+start while earlier layers are still running — the role of the per-parameter autograd hooks in the
+delegate's reducer (reducer.hpp:74,276-286), without the hooks.
+
+Layer semantics follow tv:models/resnet.py:108-163,266-282 and torch:nn/modules/batchnorm.py:144-210.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+from torch import nn
+
+from .. import ops
+from ..ops import ConvShape
+from ..utils.arena import BufferArena, ParamArena
+
+STEM_KPAD = 152          # 7*7*3 = 147 columns padded to a multiple of 8 (16-byte rows for TMA)
+
+
+class _ConvPlan:
+    """Static description of one convolution: where its weights live and its geometry."""
+
+    def __init__(self, name: str, conv: nn.Conv2d, eng: "NativeResNetEngine"):
+        self.name = name
+        self.K, self.C = conv.out_channels, conv.in_channels
+        self.R, self.S = conv.kernel_size
+        self.stride, self.pad = conv.stride[0], conv.padding[0]
+        self.pindex = eng.pindex[name + ".weight"]
+        self.w16 = eng.arena.shadow_view(name + ".weight")                  # [K, R, S, C] 16-bit
+        self.dw = eng.arena.grads[eng.arena.by_name[name + ".weight"].offset:][: self.K * self.R * self.S * self.C]
+        self.wt16 = torch.empty(self.C * self.R * self.S * self.K, dtype=eng.dtype, device=eng.device)
+
+    def shape(self, N: int, H: int, W: int) -> ConvShape:
+        return ConvShape(N, H, W, self.C, self.K, self.R, self.S, self.stride, self.pad)
+
+    def out_hw(self, H: int, W: int) -> Tuple[int, int]:
+        return ((H + 2 * self.pad - self.R) // self.stride + 1, (W + 2 * self.pad - self.S) // self.stride + 1)
+
+
+class _BNPlan:
+    def __init__(self, name: str, bn: nn.BatchNorm2d, eng: "NativeResNetEngine", slot: int):
+        self.name, self.C = name, bn.num_features
+        self.eps = float(bn.eps)
+        self.momentum = 0.1 if bn.momentum is None else float(bn.momentum)
+        self.gamma = eng.arena.param_view(name + ".weight")
+        self.beta = eng.arena.param_view(name + ".bias")
+        self.dgamma = eng.arena.grad_view(name + ".weight")
+        self.dbeta = eng.arena.grad_view(name + ".bias")
+        self.pindex = (eng.pindex[name + ".weight"], eng.pindex[name + ".bias"])
+        self.running_mean, self.running_var = bn.running_mean, bn.running_var
+        self.nbt = bn.num_batches_tracked
+        self.slot = slot                 # offset (floats) of this layer's [2C] block in the stats buffers
+        self.mean = torch.empty(self.C, dtype=torch.float32, device=eng.device)
+        self.rstd = torch.empty(self.C, dtype=torch.float32, device=eng.device)
+
+
+class _BlockPlan:
+    def __init__(self, prefix: str, block, eng: "NativeResNetEngine"):
+        self.conv1, self.bn1 = eng._conv(prefix + ".conv1", block.conv1), eng._bn(prefix + ".bn1", block.bn1)
+        self.conv2, self.bn2 = eng._conv(prefix + ".conv2", block.conv2), eng._bn(prefix + ".bn2", block.bn2)
+        self.conv3, self.bn3 = eng._conv(prefix + ".conv3", block.conv3), eng._bn(prefix + ".bn3", block.bn3)
+        self.convd = self.bnd = None
+        if block.downsample is not None:
+            self.convd = eng._conv(prefix + ".downsample.0", block.downsample[0])
+            self.bnd = eng._bn(prefix + ".downsample.1", block.downsample[1])
+
+
+class _NativeStep(torch.autograd.Function):
+    """One autograd node for the whole network.  ``anchor`` is a parameter that requires grad; it
+    only exists so that autograd schedules ``backward`` — real gradients go to the arena."""
+
+    @staticmethod
+    def forward(ctx, x, anchor, engine):
+        logits, saved = engine._forward_train(x)
+        ctx.engine, ctx.saved = engine, saved
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        ctx.engine._backward(ctx.saved, dlogits)
+        ctx.saved = None
+        return None, None, None
+
+
+class NativeResNetEngine:
+    def __init__(self, model, batch_size: int, dtype: torch.dtype = torch.bfloat16, sync_bn: bool = False):
+        ops.require()
+        p0 = next(model.parameters())
+        if not p0.is_cuda:
+            raise RuntimeError("the native engine needs the model on a CUDA device")
+        if model.width % 64 != 0:
+            raise RuntimeError(f"the tcgen05 conv path needs channel counts that are multiples of 64 (width={model.width})")
+        if dtype not in (torch.bfloat16, torch.float16):
+            raise RuntimeError("native engine compute dtype must be bf16 or fp16")
+        self.model, self.batch_size, self.dtype, self.sync_bn = model, batch_size, dtype, sync_bn
+        self.device = p0.device
+        self.arena: ParamArena = getattr(model, "_pdb200_arena", None) or ParamArena(model, self.device)
+        self.buffers: BufferArena = getattr(model, "_pdb200_buffer_arena", None) or BufferArena(model, self.device)
+        self.arena.ensure_shadow(dtype)
+        self.pindex: Dict[str, int] = {e.name: i for i, e in enumerate(self.arena.entries)}
+        self._stat_floats = 0
+        self.ddp = None
+
+        self.stem_conv = self._conv("conv1", model.conv1)
+        self.stem_bn = self._bn("bn1", model.bn1)
+        self.stem_w16 = torch.zeros(model.conv1.out_channels, STEM_KPAD, dtype=dtype, device=self.device)
+        self.blocks: List[_BlockPlan] = []
+        for li in range(1, 5):
+            layer = getattr(model, f"layer{li}")
+            for bi, block in enumerate(layer):
+                self.blocks.append(_BlockPlan(f"layer{li}.{bi}", block, self))
+        fc = model.fc
+        self.fc_K, self.fc_C = fc.out_features, fc.in_features
+        self.fc_w16 = self.arena.shadow_view("fc.weight")
+        self.fc_wt16 = torch.empty(self.fc_C * self.fc_K, dtype=dtype, device=self.device)
+        self.fc_bias = self.arena.param_view("fc.bias")
+        e = self.arena.by_name["fc.weight"]
+        self.fc_dw = self.arena.grads[e.offset: e.offset + e.numel]
+        self.fc_db = self.arena.grad_view("fc.bias")
+        self.fc_pindex = (self.pindex["fc.weight"], self.pindex["fc.bias"])
+        self.stats = torch.zeros(self._stat_floats, dtype=torch.float32, device=self.device)
+        self.dstats = torch.zeros(self._stat_floats, dtype=torch.float32, device=self.device)
+        self._anchor = model.fc.bias
+        self._convs: List[_ConvPlan] = [self.stem_conv] + [c for b in self.blocks for c in
+                                                           (b.conv1, b.conv2, b.conv3, b.convd) if c is not None]
+
+    # -- plan construction -------------------------------------------------------------------------
+    def _conv(self, name: str, conv: nn.Conv2d) -> _ConvPlan:
+        return _ConvPlan(name, conv, self)
+
+    def _bn(self, name: str, bn: nn.BatchNorm2d) -> _BNPlan:
+        plan = _BNPlan(name, bn, self, self._stat_floats)
+        self._stat_floats += 2 * bn.num_features
+        return plan
+
+    def attach_ddp(self, ddp) -> None:
+        self.ddp = ddp
+
+    def _ready(self, *indices: int) -> None:
+        if self.ddp is not None:
+            for i in indices:
+                self.ddp.mark_param_ready(i)
+
+    # -- helpers -------------------------------------------------------------------------------------
+    def _new(self, *shape) -> torch.Tensor:
+        return torch.empty(shape, dtype=self.dtype, device=self.device)
+
+    def _refresh_weights(self, need_dgrad: bool) -> None:
+        """16-bit operand copies derived from the weight shadow: padded stem rows and, for training,
+        the flipped/transposed layouts dgrad runs on."""
+        c = self.stem_conv
+        ops.pad_rows16(c.w16, self.stem_w16, c.K, c.R * c.S * c.C, STEM_KPAD)
+        if need_dgrad:
+            for cv in self._convs[1:]:
+                ops.weight_dgrad_layout(cv.w16, cv.wt16, cv.K, cv.R, cv.S, cv.C)
+            ops.weight_dgrad_layout(self.fc_w16, self.fc_wt16, self.fc_K, 1, 1, self.fc_C)
+
+    def _sync_stats(self, buf: torch.Tensor) -> float:
+        """SyncBatchNorm: sums are additive, so one all-reduce of [2C] per layer and direction."""
+        if not self.sync_bn:
+            return 1.0
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(buf)
+            return float(dist.get_world_size())
+        return 1.0
+
+    def _conv_bn(self, cv: _ConvPlan, bn: _BNPlan, x: torch.Tensor, *, residual=None, relu=True, train=True,
+                 x2d_lda: int = 0):
+        N, H, W, _ = x.shape
+        P, Q = cv.out_hw(H, W)
+        y = self._new(N, P, Q, cv.K)
+        sums = self.stats[bn.slot: bn.slot + 2 * bn.C] if train else None
+        ops.conv_fprop(x, cv.w16, y, cv.shape(N, H, W), stats=sums)
+        z = self._new(N, P, Q, cv.K)
+        rows = N * P * Q
+        if train:
+            world = self._sync_stats(sums)
+            ops.bn_apply(y.view(rows, cv.K), None if residual is None else residual.view(rows, cv.K),
+                         z.view(rows, cv.K), sums, rows * world, bn.gamma, bn.beta, bn.eps, bn.momentum,
+                         bn.running_mean, bn.running_var, bn.nbt, bn.mean, bn.rstd, relu)
+        else:
+            ops.bn_apply_eval(y.view(rows, cv.K), None if residual is None else residual.view(rows, cv.K),
+                              z.view(rows, cv.K), bn.running_mean, bn.running_var, bn.gamma, bn.beta, bn.eps, relu)
+        return y, z
+
+    # -- forward -----------------------------------------------------------------------------------------
+    def _stem(self, x: torch.Tensor, train: bool):
+        N, _, H, W = x.shape
+        cv, bn = self.stem_conv, self.stem_bn
+        P, Q = cv.out_hw(H, W)
+        rows = N * P * Q
+        col = self._new(rows, STEM_KPAD)
+        ops.stem_im2col(x.contiguous().float(), col)
+        y = self._new(N, P, Q, cv.K)
+        sums = self.stats[bn.slot: bn.slot + 2 * bn.C] if train else None
+        ops.conv_fprop(col, self.stem_w16, y, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0), stats=sums)
+        z = self._new(N, P, Q, cv.K)
+        if train:
+            world = self._sync_stats(sums)
+            ops.bn_apply(y.view(rows, cv.K), None, z.view(rows, cv.K), sums, rows * world, bn.gamma, bn.beta, bn.eps,
+                         bn.momentum, bn.running_mean, bn.running_var, bn.nbt, bn.mean, bn.rstd, True)
+        else:
+            ops.bn_apply_eval(y.view(rows, cv.K), None, z.view(rows, cv.K), bn.running_mean, bn.running_var, bn.gamma,
+                              bn.beta, bn.eps, True)
+        Hp, Wp = (P + 2 - 3) // 2 + 1, (Q + 2 - 3) // 2 + 1
+        pooled = self._new(N, Hp, Wp, cv.K)
+        argmax = torch.empty(N, Hp, Wp, cv.K, dtype=torch.uint8, device=self.device)
+        ops.maxpool_fwd(z, pooled, argmax)
+        return col, y, z, argmax, pooled
+
+    def _block_fwd(self, b: _BlockPlan, x: torch.Tensor, train: bool):
+        y1, z1 = self._conv_bn(b.conv1, b.bn1, x, train=train)
+        y2, z2 = self._conv_bn(b.conv2, b.bn2, z1, train=train)
+        if b.convd is not None:
+            yd, sc = self._conv_bn(b.convd, b.bnd, x, relu=False, train=train)
+        else:
+            yd, sc = None, x
+        y3, out = self._conv_bn(b.conv3, b.bn3, z2, residual=sc, relu=True, train=train)
+        return (x, y1, z1, y2, z2, y3, yd, out), out
+
+    def _head(self, feat: torch.Tensor):
+        N, H, W, C = feat.shape
+        pooled = self._new(N, C)
+        ops.avgpool_fwd(feat, pooled)
+        logits = self._new(N, self.fc_K)
+        ops.conv_fprop(pooled, self.fc_w16, logits, ConvShape(N, 1, 1, C, self.fc_K, 1, 1, 1, 0), bias=self.fc_bias,
+                       block_n=128)
+        return pooled, logits
+
+    def _forward_train(self, x: torch.Tensor):
+        self.stats.zero_()
+        self._refresh_weights(need_dgrad=True)
+        stem = self._stem(x, True)
+        cur, saved_blocks = stem[-1], []
+        for b in self.blocks:
+            sv, cur = self._block_fwd(b, cur, True)
+            saved_blocks.append(sv)
+        pooled, logits = self._head(cur)
+        return logits, (stem, saved_blocks, pooled, tuple(cur.shape))
+
+    @torch.no_grad()
+    def forward_eval(self, x: torch.Tensor, train_stats: bool = False) -> torch.Tensor:
+        if train_stats:
+            self.stats.zero_()
+        self._refresh_weights(need_dgrad=False)
+        cur = self._stem(x, train_stats)[-1]
+        for b in self.blocks:
+            _, cur = self._block_fwd(b, cur, train_stats)
+        return self._head(cur)[1]
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        if self.model.training and torch.is_grad_enabled():
+            return _NativeStep.apply(x, self._anchor, self)
+        return self.forward_eval(x, train_stats=self.model.training)
+
+    # -- backward ----------------------------------------------------------------------------------------
+    def _bn_bwd(self, bn: _BNPlan, dz, z, y, *, want_dres: bool):
+        """Returns (dy, dres).  dres = dz * relu_mask (gradient of the residual branch)."""
+        rows = y.numel() // bn.C
+        ds = self.dstats[bn.slot: bn.slot + 2 * bn.C]
+        v = lambda t: None if t is None else t.view(rows, bn.C)    # noqa: E731
+        ops.bn_bwd_reduce(v(dz), v(z), v(y), bn.mean, bn.rstd, ds)
+        world = self._sync_stats(ds)
+        dy = torch.empty_like(y)
+        dres = torch.empty_like(y) if want_dres else None
+        ops.bn_bwd_apply(v(dz), v(z), v(y), v(dy), v(dres), bn.mean, bn.rstd, bn.gamma, ds, rows * world, bn.dgamma,
+                         bn.dbeta)
+        return dy, dres
+
+    def _conv_bwd(self, cv: _ConvPlan, x: torch.Tensor, dy: torch.Tensor, need_dx: bool = True):
+        """wgrad into the arena; returns dx (same spatial size as x) when requested."""
+        N, H, W, _ = x.shape
+        ops.conv_wgrad(x, dy, cv.dw, cv.shape(N, H, W))
+        if not need_dx:
+            return None
+        _, P, Q, _ = dy.shape
+        if cv.R == 1:
+            # 1x1: plain GEMM on the (possibly strided-compact) pixel set
+            dx = self._new(N, P, Q, cv.C)
+            ops.conv_fprop(dy, cv.wt16, dx, ConvShape(N, P, Q, cv.K, cv.C, 1, 1, 1, 0))
+            return dx            # compact [N, P, Q, C]; the caller scatters it if stride == 2
+        if cv.stride == 2:
+            up = self._new(N, H, W, cv.K)
+            ops.upsample2_zero(dy, up)
+            dy, P, Q = up, H, W
+        dx = self._new(N, H, W, cv.C)
+        ops.conv_fprop(dy, cv.wt16, dx, ConvShape(N, P, Q, cv.K, cv.C, cv.R, cv.S, 1, cv.R - 1 - cv.pad))
+        return dx
+
+    def _block_bwd(self, b: _BlockPlan, sv, dout: torch.Tensor) -> torch.Tensor:
+        x, y1, z1, y2, z2, y3, yd, out = sv
+        dy3, dres = self._bn_bwd(b.bn3, dout, out, y3, want_dres=True)
+        self._ready(*b.bn3.pindex)
+        dz2 = self._conv_bwd(b.conv3, z2, dy3)
+        self._ready(b.conv3.pindex)
+        dy2, _ = self._bn_bwd(b.bn2, dz2, z2, y2, want_dres=False)
+        self._ready(*b.bn2.pindex)
+        dz1 = self._conv_bwd(b.conv2, z1, dy2)
+        self._ready(b.conv2.pindex)
+        dy1, _ = self._bn_bwd(b.bn1, dz1, z1, y1, want_dres=False)
+        self._ready(*b.bn1.pindex)
+        dxa = self._conv_bwd(b.conv1, x, dy1)
+        self._ready(b.conv1.pindex)
+        dx = torch.empty_like(dxa)
+        if b.convd is None:
+            ops.add16(dxa, dres, dx)
+        else:
+            dyd, _ = self._bn_bwd(b.bnd, dres, None, yd, want_dres=False)
+            self._ready(*b.bnd.pindex)
+            dxd = self._conv_bwd(b.convd, x, dyd)
+            self._ready(b.convd.pindex)
+            if b.convd.stride == 2:
+                ops.add_strided2(dxa, dxd, dx)
+            else:
+                ops.add16(dxa, dxd, dx)
+        return dx
+
+    def _backward(self, saved, dlogits: torch.Tensor) -> None:
+        stem, saved_blocks, pooled, feat_shape = saved
+        dlogits = dlogits.contiguous()
+        if dlogits.dtype != self.dtype:
+            dlogits = dlogits.to(self.dtype)
+        self.dstats.zero_()
+        N = dlogits.shape[0]
+        # fc: wgrad, bias grad, dgrad
+        ops.conv_wgrad(pooled, dlogits, self.fc_dw, ConvShape(N, 1, 1, self.fc_C, self.fc_K, 1, 1, 1, 0))
+        ops.colsum16(dlogits, self.fc_db)
+        self._ready(*self.fc_pindex[::-1])
+        dpooled = self._new(N, self.fc_C)
+        ops.conv_fprop(dlogits, self.fc_wt16, dpooled, ConvShape(N, 1, 1, self.fc_K, self.fc_C, 1, 1, 1, 0))
+        d = self._new(*feat_shape)
+        ops.avgpool_bwd(dpooled, d)
+        for b, sv in zip(reversed(self.blocks), reversed(saved_blocks)):
+            d = self._block_bwd(b, sv, d)
+        col, y0, z0, argmax, _ = stem
+        dz0 = torch.empty_like(z0)
+        ops.maxpool_bwd(d, argmax, dz0)
+        dy0, _ = self._bn_bwd(self.stem_bn, dz0, z0, y0, want_dres=False)
+        self._ready(*self.stem_bn.pindex)
+        cv = self.stem_conv
+        rows = col.shape[0]
+        ops.conv_wgrad(col, dy0.view(rows, cv.K), cv.dw, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0),
+                       ldw=cv.R * cv.S * cv.C, kvalid=cv.R * cv.S * cv.C)
+        self._ready(cv.pindex)

@@ -1,0 +1,90 @@
+"""Native step graph vs the stock fp32 model: logits, loss, every parameter gradient, BN buffers."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from pytorch_distributed_b200 import amp, harness  # noqa: E402
+from pytorch_distributed_b200.config import TrainConfig  # noqa: E402
+from pytorch_distributed_b200.models import resnet50  # noqa: E402
+from pytorch_distributed_b200.nn import CrossEntropyLoss  # noqa: E402
+from pytorch_distributed_b200.optim import SGD  # noqa: E402
+
+
+def _cos(a, b):
+    a, b = a.float().flatten(), b.float().flatten()
+    return float(F.cosine_similarity(a, b, dim=0))
+
+
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])
+def test_forward_backward_matches_fp32_model(dt):
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    ref = resnet50().to(dev)
+    ours = copy.deepcopy(ref)
+    ours.enable_native(batch_size=16, dtype=dt)
+    x = torch.randn(16, 3, 96, 96, device=dev)
+    y = torch.randint(0, 1000, (16,), device=dev)
+
+    ref.train()
+    out_ref = ref(x)
+    loss_ref = F.cross_entropy(out_ref, y)
+    loss_ref.backward()
+
+    ours.train()
+    out = ours(x)
+    assert out.dtype == dt and out.shape == (16, 1000)
+    loss = CrossEntropyLoss()(out, y)
+    loss.backward()
+    torch.cuda.synchronize()
+
+    assert _cos(out, out_ref) > 0.995, _cos(out, out_ref)
+    assert abs(float(loss) - float(loss_ref)) < 0.05 * abs(float(loss_ref))
+    worst = (1.0, None)
+    for (n, p), q in zip(ours.named_parameters(), ref.parameters()):
+        assert p.grad.data_ptr() == ours._pdb200_arena.grad_view(n).data_ptr()
+        c = _cos(p.grad, q.grad)
+        if c < worst[0]:
+            worst = (c, n)
+        rel = float(p.grad.float().norm() / (q.grad.norm() + 1e-20))
+        assert 0.8 < rel < 1.25, (n, rel)
+    assert worst[0] > 0.97, worst
+    # BN running statistics were updated like torch's
+    for (n, b), c in zip(ours.named_buffers(), ref.buffers()):
+        if b.is_floating_point():
+            assert torch.allclose(b, c, rtol=5e-2, atol=5e-3), n
+        else:
+            assert int(b) == int(c) == 1, n
+    # eval forward uses running stats
+    ours.eval(), ref.eval()
+    with torch.no_grad():
+        assert _cos(ours(x), ref(x)) > 0.99
+
+
+def test_training_steps_reduce_loss_and_match_torch_engine():
+    """A few optimisation steps through the public harness step: native vs stock-op engine."""
+    torch.manual_seed(1)
+    dev = torch.device("cuda")
+    cfg = TrainConfig(mode="ddp_amp", batch_size=32, dtype="bf16", device="cuda")
+    a = harness.build_model(cfg, dev)
+    b = copy.deepcopy(a)
+    a.enable_native(batch_size=32, dtype=torch.bfloat16)
+    harness.ensure_arenas(a, dev), harness.ensure_arenas(b, dev)
+    x = torch.randn(32, 3, 64, 64, device=dev)
+    y = torch.randint(0, 1000, (32,), device=dev)
+    losses = []
+    for m, stock in ((a, False), (b, True)):
+        opt = SGD(m.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+        sc = amp.GradScaler(device=dev)
+        crit = CrossEntropyLoss()
+        m.train()
+        ls = [float(harness.train_step(m, crit, opt, x, y, cfg, dev, sc, stock_autocast=stock)) for _ in range(6)]
+        losses.append(ls)
+    assert losses[0][-1] < losses[0][0]                      # it learns the fixed batch
+    assert abs(losses[0][0] - losses[1][0]) < 0.05 * losses[1][0]
+    assert abs(losses[0][-1] - losses[1][-1]) < 0.35 * max(losses[1][-1], 0.5), losses
