@@ -122,7 +122,10 @@ class DistributedDataParallel(nn.Module):
     # -- gradient path -----------------------------------------------------------------
     def _make_hook(self, index: int):
         def hook(param: torch.Tensor) -> None:
-            self._on_grad_ready(index, param)
+            # With the native step graph the engine reports readiness itself (mark_param_ready);
+            # autograd still fires this hook for the graph's anchor parameter — ignore it.
+            if getattr(self.module, "_engine", None) is None:
+                self._on_grad_ready(index, param)
         return hook
 
     def _on_grad_ready(self, index: int, param=None) -> None:
