@@ -436,3 +436,70 @@ extern "C" int pdb_bn_bwd_apply(const void* dz, const void* z, const void* x, vo
   PDB_LAUNCH_CHECK();
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// pdb_bn_stats_noalloc — the same statistics kernel for callers that cannot allocate device memory.
+//
+// pdb_bn_stats needs a caller-provided scratch buffer for the per-block partial sums.  Some users of
+// this library have no way to produce one at the point of the call: a C/C++ host that gave all of
+// the GPU's memory to its own pre-planned pools at start-up and has no allocator left to ask; code
+// that runs in the middle of a training step, where cudaMalloc/cudaFree would synchronise the whole
+// device and break the overlap between the compute and communication streams; embedders that are
+// simply not allowed to call the CUDA allocator (the memory budget is owned by somebody else).
+// For them the scratch lives here, in a fixed array in the library's device image: every GPU that
+// loads libpdb200.so carries these kNoAllocScratchBytes (~512 KB) until the process exits, whether
+// or not this entry point is ever called.
+//
+// Limits and rules, all consequences of the fixed array:
+//   * C <= kNoAllocMaxC (512); larger layers are rejected with an error — use pdb_bn_stats;
+//   * at most kNoAllocMaxBlocks (128) CTAs fold partials, whatever `rows` is;
+//   * the array is shared by every call on the device and still holds the previous call's partials:
+//     the block ticket is cleared on the stream before each launch, partials are fully overwritten
+//     before they are read; two calls that run concurrently on one GPU (different streams) race on
+//     it and produce garbage — serialise them;
+//   * the first call on each device resolves the array's device address (cudaGetSymbolAddress; the
+//     name of a __device__ array is only a host-side handle, not something a kernel can
+//     dereference) — make that first call outside of any stream capture.
+// Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+namespace pdb {
+constexpr int kNoAllocMaxC = 512;
+constexpr int kNoAllocMaxBlocks = 128;
+constexpr size_t kNoAllocScratchBytes =
+    sizeof(StatsScratch) + (size_t)kNoAllocMaxBlocks * 2 * kNoAllocMaxC * sizeof(float);
+static __device__ __align__(256) unsigned char g_bn_stats_scratch[kNoAllocScratchBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_noalloc_ptr[kMaxDevices] = {};      // per-device address of g_bn_stats_scratch
+}  // namespace pdb
+
+extern "C" int pdb_bn_stats_noalloc(const void* x, int dtype, int64_t rows, int C, float* sums, void* stream) {
+  PDB_CHECK_ARG(x && sums, "pdb_bn_stats_noalloc: null pointer");
+  PDB_CHECK_ARG(C > 0 && C % 8 == 0, "pdb_bn_stats_noalloc: C=%d must be a positive multiple of 8", C);
+  PDB_CHECK_ARG(C <= kNoAllocMaxC,
+                "pdb_bn_stats_noalloc: C=%d exceeds the built-in scratch limit of %d channels; "
+                "use pdb_bn_stats with a caller-provided scratch buffer", C, kNoAllocMaxC);
+  PDB_CHECK_ARG(rows > 0, "pdb_bn_stats_noalloc: rows must be positive");
+  int dev = -1;
+  PDB_CUDA(cudaGetDevice(&dev));
+  PDB_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "pdb_bn_stats_noalloc: device index %d out of range", dev);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    // one-time set-up for this device (it is the current one): symbol -> device address
+    void* p = nullptr;
+    PDB_CUDA(cudaGetSymbolAddress(&p, g_bn_stats_scratch));
+    PDB_CHECK_ARG(p != nullptr, "pdb_bn_stats_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = p;
+  }
+  StatsScratch* scratch = static_cast<StatsScratch*>(g_noalloc_ptr[dev]);
+  int cx, ry;
+  reduce_geometry(C, &cx, &ry);
+  int grid = reduce_grid(rows, ry);
+  if (grid > kNoAllocMaxBlocks) grid = kNoAllocMaxBlocks;
+  cudaStream_t st = (cudaStream_t)stream;
+  // The ticket counter is the only state that must start at zero; an earlier launch that was
+  // aborted (or a racing one) could have left it non-zero.
+  PDB_CUDA(cudaMemsetAsync(scratch, 0, sizeof(StatsScratch), st));
+  const size_t smem = (size_t)kThreads * 16 * sizeof(float);
+  PDB_DISPATCH_16(dtype, T, (bn_stats_kernel<T><<<grid, kThreads, smem, st>>>((const T*)x, rows, C, cx, ry, sums, scratch)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}

@@ -71,6 +71,16 @@ size_t pdb_bn_stats_scratch_bytes(int C);
 int pdb_bn_stats(const void* x, int dtype, int64_t rows, int C, float* sums, void* scratch,
                  size_t scratch_bytes, void* stream);
 
+/* Same result as pdb_bn_stats for callers that cannot obtain device memory for the scratch buffer
+ * (hosts whose GPU memory is fully committed to their own pools, code in the middle of a step where
+ * cudaMalloc/cudaFree would synchronise the device, embedders that may not call the CUDA allocator).
+ * This entry point has no counterpart in the reference.  The partial sums go to a fixed ~512 KB
+ * array inside the library's device image, resident on every GPU that loads the library until exit.
+ * Limit: C <= 512 (a multiple of 8); larger C returns an error.  The first call on each device
+ * looks up the array's device address (do it before any stream capture); calls that overlap on one
+ * GPU share the array and race — run them one after another.  Allocates nothing. */
+int pdb_bn_stats_noalloc(const void* x, int dtype, int64_t rows, int C, float* sums, void* stream);
+
 /* y = [relu]( (x - mean) * rstd * gamma + beta [+ residual] ).  mean/rstd are derived from
  * sums[2*C] over `count` elements per channel (count may exceed rows under SyncBN) inside the
  * kernel; block 0 stores save_mean/save_rstd and updates running_mean/var/num_batches_tracked when
