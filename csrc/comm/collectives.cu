@@ -1,0 +1,315 @@
+// K1-K6: collectives as kernels over NVLink peer memory (symmetric arenas + signal pads).
+//
+// The delegates go through NCCL (ProcessGroupNCCL for DDP, torch.cuda.nccl for DataParallel) and wrap
+// every collective in extra passes: copy+divide into a flat bucket, all-reduce, copy out, then a separate
+// un-scale/inf-check kernel for amp (reducer.hpp:276-286, torch:amp/grad_scaler.py:349-361).  Here every
+// rank's gradient arena is mapped into every other rank's address space (torch symmetric memory does the
+// allocation and handle exchange; the kernels are ours) and one kernel does, per bucket:
+//
+//     barrier  ->  reduce-scatter by P2P loads (rank r sums shard r of all ranks)
+//              ->  x 1/world, x 1/loss_scale, non-finite check          (fused epilogue)
+//              ->  all-gather by P2P stores (or NVLS multimem.st)        ->  barrier
+//
+// in place on the gradients, so DDP needs no bucket copies at all.  With a multicast mapping the
+// reduce-scatter is a single `multimem.ld_reduce` per 16 bytes: the NVSwitch adds the eight copies.
+//
+// Cross-GPU synchronisation: one 32-bit slot per (block, peer) in the symmetric signal pad; release/acquire
+// CAS at system scope (the protocol of torch's CUDASymmetricMemory sync_remote_blocks, re-implemented).
+// Every spin is bounded by the global timer and traps instead of hanging the box.
+#include "common.cuh"
+
+namespace pdb {
+
+constexpr int kMaxWorld = 16;
+constexpr int kCommThreads = 512;
+constexpr unsigned long long kSpinTimeoutNs = 20ull * 1000 * 1000 * 1000;     // 20 s
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+__device__ __forceinline__ uint32_t cas_release_sys(uint32_t* addr, uint32_t cmp, uint32_t val) {
+  uint32_t old;
+  asm volatile("atom.global.release.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
+  return old;
+}
+__device__ __forceinline__ uint32_t cas_acquire_sys(uint32_t* addr, uint32_t cmp, uint32_t val) {
+  uint32_t old;
+  asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
+  return old;
+}
+
+// Block-level barrier across ranks: block b of every rank meets block b of every other rank.
+// Slot layout in each rank's pad: pad[b * world + src_rank].
+__device__ __forceinline__ void cross_rank_barrier(uint32_t* const* pads, int rank, int world) {
+  __syncthreads();
+  if (threadIdx.x < world && (int)threadIdx.x != rank) {
+    const int peer = threadIdx.x;
+    uint32_t* remote = pads[peer] + blockIdx.x * world + rank;        // my flag in the peer's pad
+    uint32_t* local = pads[rank] + blockIdx.x * world + peer;         // the peer's flag in my pad
+    const unsigned long long t0 = globaltimer_ns();
+    while (cas_release_sys(remote, 0u, 1u) != 0u)
+      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
+    while (cas_acquire_sys(local, 1u, 0u) != 1u)
+      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
+  }
+  __syncthreads();
+}
+
+struct PeerPtrs {
+  float* buf[kMaxWorld];
+  uint32_t* pad[kMaxWorld];
+  float* flag[kMaxWorld];       // per-rank non-finite flag (symmetric); may be null
+};
+
+__device__ __forceinline__ float4 ld_peer(const float* p) {
+  float4 v;
+  // peer data is produced by another GPU: bypass L1 (.cg) so a stale line can never be observed
+  asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_peer(float* p, const float4& v) {
+  asm volatile("st.global.cg.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 multimem_ld_reduce(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(float* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+// Two-shot in-place all-reduce of elements [start, start + n) of every rank's buffer.
+// kMulticast: reduce and broadcast through the NVLS multicast address `mc` instead of per-peer loads/stores.
+template <bool kMulticast>
+__global__ void __launch_bounds__(kCommThreads) allreduce_kernel(PeerPtrs pp, float* mc, int rank, int world,
+                                                                 int64_t start, int64_t n, float scale,
+                                                                 const float* __restrict__ inv_scale) {
+  cross_rank_barrier(pp.pad, rank, world);            // everybody's gradients for this range are final
+  const float s = scale * (inv_scale ? *inv_scale : 1.0f);
+  // shard r = [lo, hi) in units of float4, split evenly
+  const int64_t n4 = n / 4;
+  const int64_t per = (n4 + world - 1) / world;
+  const int64_t lo = min(per * rank, n4), hi = min(lo + per, n4);
+  bool bad = false;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+    const int64_t off = start + i * 4;
+    float4 acc;
+    if (kMulticast) {
+      acc = multimem_ld_reduce(mc + off);
+    } else {
+      acc = ld_peer(pp.buf[rank] + off);
+#pragma unroll 1
+      for (int k = 1; k < world; ++k) {
+        const int p = rank + k < world ? rank + k : rank + k - world;     // stagger peers across ranks
+        const float4 v = ld_peer(pp.buf[p] + off);
+        acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+      }
+    }
+    acc.x *= s, acc.y *= s, acc.z *= s, acc.w *= s;
+    bad |= !(isfinite(acc.x) && isfinite(acc.y) && isfinite(acc.z) && isfinite(acc.w));
+    if (kMulticast) {
+      multimem_st(mc + off, acc);
+    } else {
+#pragma unroll 1
+      for (int k = 0; k < world; ++k) {
+        const int p = rank + k < world ? rank + k : rank + k - world;
+        st_peer(pp.buf[p] + off, acc);
+      }
+    }
+  }
+  if (pp.flag[0] != nullptr && __syncthreads_or(bad) && threadIdx.x < world) {
+    // the non-finite verdict must be identical on all ranks: raise it everywhere
+    *reinterpret_cast<volatile float*>(pp.flag[threadIdx.x]) = 1.0f;
+  }
+  __threadfence_system();
+  cross_rank_barrier(pp.pad, rank, world);            // all shards have landed everywhere
+}
+
+// Broadcast of [start, start+n) from `root` to every rank: non-root ranks pull over NVLink.
+__global__ void __launch_bounds__(kCommThreads) broadcast_kernel(PeerPtrs pp, int rank, int world, int root,
+                                                                 int64_t start, int64_t n) {
+  cross_rank_barrier(pp.pad, rank, world);
+  if (rank != root) {
+    const int64_t n4 = n / 4, stride = (int64_t)gridDim.x * blockDim.x;
+    const float* src = pp.buf[root] + start;
+    float* dst = pp.buf[rank] + start;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride)
+      reinterpret_cast<float4*>(dst)[i] = ld_peer(src + i * 4);
+  }
+  cross_rank_barrier(pp.pad, rank, world);            // root may overwrite its copy only after everyone has read it
+}
+
+// One-shot all-reduce for tiny payloads (SyncBN statistics, metric vectors): every rank pushes its n floats
+// into slot [rank] of every peer's staging buffer, then sums the `world` slots locally.  Single block.
+// staging layout per rank: float[world][n_max].
+__global__ void __launch_bounds__(1024) small_allreduce_kernel(PeerPtrs pp, int rank, int world, float* __restrict__ data,
+                                                               int n, int slot_stride) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float v = data[i];
+    for (int p = 0; p < world; ++p) pp.buf[p][(int64_t)rank * slot_stride + i] = v;
+  }
+  __threadfence_system();
+  cross_rank_barrier(pp.pad, rank, world);
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    float acc = 0.f;
+    for (int p = 0; p < world; ++p) acc += __ldcg(pp.buf[rank] + (int64_t)p * slot_stride + i);
+    data[i] = acc;
+  }
+  cross_rank_barrier(pp.pad, rank, world);            // slots may be reused by the next call
+}
+
+// ---- single-process DataParallel helpers (all GPUs in one address space, peer access enabled) ----------
+__global__ void __launch_bounds__(256) peer_pull_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src, int64_t n16) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
+    uint4 v;
+    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(src + i));
+    dst[i] = v;
+  }
+}
+
+struct PeerList {
+  const float* p[kMaxWorld];
+};
+
+__global__ void __launch_bounds__(256) reduce_to_root_kernel(float* __restrict__ root, PeerList peers, int n_peers,
+                                                             int64_t n4) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 acc = reinterpret_cast<float4*>(root)[i];
+    for (int k = 0; k < n_peers; ++k) {
+      const float4 v = ld_peer(peers.p[k] + i * 4);
+      acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+    }
+    reinterpret_cast<float4*>(root)[i] = acc;
+  }
+}
+
+static int fill_peers(PeerPtrs* pp, void* const* bufs, void* const* pads, void* const* flags, int world) {
+  PDB_CHECK_ARG(world >= 1 && world <= kMaxWorld, "world size %d not supported (max %d)", world, kMaxWorld);
+  for (int i = 0; i < kMaxWorld; ++i) pp->buf[i] = nullptr, pp->pad[i] = nullptr, pp->flag[i] = nullptr;
+  for (int i = 0; i < world; ++i) {
+    pp->buf[i] = static_cast<float*>(bufs[i]);
+    pp->pad[i] = static_cast<uint32_t*>(pads[i]);
+    pp->flag[i] = flags ? static_cast<float*>(flags[i]) : nullptr;
+  }
+  return 0;
+}
+
+}  // namespace pdb
+using namespace pdb;
+
+extern "C" int pdb_comm_max_blocks(int world, size_t signal_pad_bytes) {
+  const size_t slots = signal_pad_bytes / sizeof(uint32_t);
+  int b = (int)(slots / (size_t)(world > 0 ? world : 1));
+  return b > 32 ? 32 : b;
+}
+
+extern "C" int pdb_allreduce_inplace(void* const* bufs, void* const* pads, void* const* flags, void* multicast, int rank,
+                                     int world, int64_t start, int64_t n, float scale, const float* inv_scale,
+                                     int blocks, void* stream) {
+  PDB_CHECK_ARG(bufs && pads && n >= 0 && start >= 0, "pdb_allreduce_inplace: bad arguments");
+  PDB_CHECK_ARG(n % 4 == 0 && start % 4 == 0, "pdb_allreduce_inplace: range must be 16-byte aligned (start=%lld n=%lld)",
+                (long long)start, (long long)n);
+  PDB_CHECK_ARG(rank >= 0 && rank < world, "pdb_allreduce_inplace: rank %d out of range", rank);
+  PDB_CHECK_ARG(blocks >= 1 && blocks <= 32, "pdb_allreduce_inplace: blocks must be in [1, 32]");
+  if (n == 0) return 0;
+  PeerPtrs pp;
+  if (int e = fill_peers(&pp, bufs, pads, flags, world)) return e;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (multicast)
+    allreduce_kernel<true><<<blocks, kCommThreads, 0, st>>>(pp, static_cast<float*>(multicast), rank, world, start, n, scale, inv_scale);
+  else
+    allreduce_kernel<false><<<blocks, kCommThreads, 0, st>>>(pp, nullptr, rank, world, start, n, scale, inv_scale);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_broadcast_inplace(void* const* bufs, void* const* pads, int rank, int world, int root, int64_t start,
+                                     int64_t n, int blocks, void* stream) {
+  PDB_CHECK_ARG(bufs && pads && n >= 0 && n % 4 == 0 && start % 4 == 0, "pdb_broadcast_inplace: bad arguments");
+  PDB_CHECK_ARG(rank >= 0 && rank < world && root >= 0 && root < world, "pdb_broadcast_inplace: bad rank/root");
+  PDB_CHECK_ARG(blocks >= 1 && blocks <= 32, "pdb_broadcast_inplace: blocks must be in [1, 32]");
+  if (n == 0) return 0;
+  PeerPtrs pp;
+  if (int e = fill_peers(&pp, bufs, pads, nullptr, world)) return e;
+  broadcast_kernel<<<blocks, kCommThreads, 0, (cudaStream_t)stream>>>(pp, rank, world, root, start, n);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_small_allreduce(void* const* staging, void* const* pads, int rank, int world, float* data, int n,
+                                   int slot_stride, void* stream) {
+  PDB_CHECK_ARG(staging && pads && data && n > 0 && n <= slot_stride, "pdb_small_allreduce: bad arguments");
+  PeerPtrs pp;
+  if (int e = fill_peers(&pp, staging, pads, nullptr, world)) return e;
+  small_allreduce_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(pp, rank, world, data, n, slot_stride);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+static int enable_peer(int dst_dev, int src_dev) {
+  if (dst_dev == src_dev) return 0;
+  int can = 0;
+  PDB_CUDA(cudaDeviceCanAccessPeer(&can, dst_dev, src_dev));
+  PDB_CHECK_ARG(can, "GPU %d cannot access GPU %d over P2P", dst_dev, src_dev);
+  cudaError_t e = cudaDeviceEnablePeerAccess(src_dev, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) {
+    cudaGetLastError();
+    return 0;
+  }
+  PDB_CUDA(e);
+  return 0;
+}
+
+static int device_of(const void* p, int* dev) {
+  cudaPointerAttributes a;
+  PDB_CUDA(cudaPointerGetAttributes(&a, p));
+  *dev = a.device;
+  return 0;
+}
+
+extern "C" int pdb_peer_pull(void* dst, const void* src, int64_t bytes, void* stream) {
+  PDB_CHECK_ARG(dst && src && bytes > 0 && bytes % 16 == 0, "pdb_peer_pull: bytes (%lld) must be a positive multiple of 16",
+                (long long)bytes);
+  PDB_CHECK_ARG((((uintptr_t)dst | (uintptr_t)src) & 15) == 0, "pdb_peer_pull: pointers must be 16-byte aligned");
+  int cur = 0, sdev = 0;
+  PDB_CUDA(cudaGetDevice(&cur));
+  if (int e = device_of(src, &sdev)) return e;
+  if (int e = enable_peer(cur, sdev)) return e;
+  const int64_t n16 = bytes / 16;
+  int64_t want = (n16 + 255) / 256;
+  const int grid = (int)(want < 64 ? want : 64);          // a few dozen CTAs saturate an NVLink direction
+  peer_pull_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((uint4*)dst, (const uint4*)src, n16);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_reduce_to_root(float* root, void* const* peers, int n_peers, int64_t n, void* stream) {
+  PDB_CHECK_ARG(root && peers && n_peers >= 1 && n_peers < kMaxWorld && n > 0 && n % 4 == 0,
+                "pdb_reduce_to_root: bad arguments");
+  int cur = 0;
+  PDB_CUDA(cudaGetDevice(&cur));
+  PeerList pl;
+  for (int i = 0; i < n_peers; ++i) {
+    int d = 0;
+    if (int e = device_of(peers[i], &d)) return e;
+    if (int e = enable_peer(cur, d)) return e;
+    pl.p[i] = static_cast<const float*>(peers[i]);
+  }
+  const int64_t n4 = n / 4;
+  int64_t want = (n4 + 255) / 256;
+  const int grid = (int)(want < 128 ? want : 128);
+  reduce_to_root_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(root, pl, n_peers, n4);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}

@@ -164,6 +164,37 @@ int pdb_pad_rows16(const void* src, void* dst, int dtype, int rows, int cols_src
 /* out[c] += sum_r a[r, c] (16-bit in, fp32 out): fc bias gradient. */
 int pdb_colsum16(const void* a, float* out, int dtype, int rows, int cols, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * K1-K6 — collectives over NVLink peer memory (csrc/comm/collectives.cu).  `bufs[r]` / `pads[r]` are
+ * rank r's symmetric buffer base and signal pad as mapped in THIS process (torch symmetric memory
+ * provides allocation and handle exchange only).  Every rank must call with the same arguments and the
+ * same `blocks` (<= pdb_comm_max_blocks); kernels of different ranks wait for each other, so each rank
+ * needs its own GPU.  Spins are bounded (20 s) and trap. */
+int pdb_comm_max_blocks(int world, size_t signal_pad_bytes);
+
+/* K1 (ref:restnet_ddp.py:29 loss.backward() -> Reducer all_reduce_bucket -> ncclAllReduce): in-place
+ * all-reduce of fp32 elements [start, start+n) of every rank's buffer: reduce-scatter by P2P loads (or
+ * one multimem.ld_reduce per 16 B when `multicast` is the NVLS address of the same buffer), multiply
+ * by scale (1/world) and *inv_scale (device float, nullable: amp un-scale), raise flags[r][0] = 1 on
+ * every rank if the result is non-finite (nullable), all-gather by P2P stores / multimem.st. */
+int pdb_allreduce_inplace(void* const* bufs, void* const* pads, void* const* flags, void* multicast, int rank,
+                          int world, int64_t start, int64_t n, float scale, const float* inv_scale, int blocks,
+                          void* stream);
+/* K2/K3 (DDP _sync_module_states / per-iteration buffer broadcast): every rank != root pulls
+ * [start, start+n) from root's buffer. */
+int pdb_broadcast_inplace(void* const* bufs, void* const* pads, int rank, int world, int root, int64_t start,
+                          int64_t n, int blocks, void* stream);
+/* K5/K6 (ref:restnet_ddp.py:63-64 metric reduce; SyncBatchNorm statistics): one-shot in-place sum over
+ * ranks of data[0:n] through a symmetric staging area float[world][slot_stride]. */
+int pdb_small_allreduce(void* const* staging, void* const* pads, int rank, int world, float* data, int n,
+                        int slot_stride, void* stream);
+/* K4a-K4c (ref:resnet_dp.py:21 DataParallel scatter / replicate / gather): the current GPU pulls
+ * `bytes` from another GPU's memory (single process, peer access is enabled on demand). */
+int pdb_peer_pull(void* dst, const void* src, int64_t bytes, void* stream);
+/* K4d (ref:resnet_dp.py:24 backward -> ReduceAddCoalesced -> nccl.reduce): root[0:n] += sum of the
+ * peers' arrays, read over NVLink by the root GPU. */
+int pdb_reduce_to_root(float* root, void* const* peers, int n_peers, int64_t n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

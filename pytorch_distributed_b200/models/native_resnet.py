@@ -178,7 +178,11 @@ class NativeResNetEngine:
             return 1.0
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-            dist.all_reduce(buf)
+            comm = getattr(self.ddp, "comm", None)
+            if comm is not None and hasattr(comm, "allreduce_small_"):
+                comm.allreduce_small_(buf)        # K6: peer-memory exchange, no NCCL call per BN layer
+            else:
+                dist.all_reduce(buf)
             return float(dist.get_world_size())
         return 1.0
 

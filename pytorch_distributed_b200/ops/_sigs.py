@@ -48,4 +48,11 @@ def declare(L):
             sig(name, args)
 
 
-OPTIONAL = {}
+OPTIONAL = {
+    "pdb_allreduce_inplace": [P, P, P, P, c_int, c_int, c_int64, c_int64, c_float, P, c_int, P],
+    "pdb_broadcast_inplace": [P, P, c_int, c_int, c_int, c_int64, c_int64, c_int, P],
+    "pdb_small_allreduce": [P, P, c_int, c_int, P, c_int, c_int, P],
+    "pdb_peer_pull": [P, P, c_int64, P],
+    "pdb_reduce_to_root": [P, P, c_int, c_int64, P],
+    "pdb_comm_max_blocks": [c_int, c_size_t],
+}

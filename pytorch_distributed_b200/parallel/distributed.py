@@ -116,8 +116,7 @@ class DistributedDataParallel(nn.Module):
         self._sync_buffers()
 
     def _sync_buffers(self) -> None:                         # K3
-        self.comm.broadcast_(self.buffer_arena.floats, 0)
-        self.comm.broadcast_(self.buffer_arena.ints, 0)
+        self.comm.broadcast_(self.buffer_arena.storage, 0)     # fp32 stats + int64 counters, one transfer
 
     # -- gradient path -----------------------------------------------------------------
     def _make_hook(self, index: int):

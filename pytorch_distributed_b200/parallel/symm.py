@@ -1,0 +1,170 @@
+"""NativeComm — arena collectives as our own sm_100a kernels over NVLink peer memory.
+
+torch's symmetric-memory allocator is used for exactly two things: allocating buffers that can be mapped by
+peers, and exchanging the handles (``rendezvous``; bootstrap over the NCCL group's store).  Everything that
+moves or reduces data is ``csrc/comm/collectives.cu``: in-place two-shot all-reduce with fused
+1/world · 1/loss-scale · non-finite check (K1), pull broadcast (K2/K3), one-shot small all-reduce for SyncBN
+statistics and metric vectors (K5/K6).  Kernels run on a high-priority side stream so that a bucket's
+all-reduce overlaps the rest of backward.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .. import ops
+from ..ops._lib import check, count_launch, ptr, require
+
+
+class _Mapped:
+    """A symmetric tensor after rendezvous: per-rank base pointers, signal pads, multicast address."""
+
+    def __init__(self, tensor: torch.Tensor, group):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.tensor = tensor
+        self.handle = symm_mem.rendezvous(tensor, group if group is not None else dist.group.WORLD)
+        h = self.handle
+        self.world, self.rank = h.world_size, h.rank
+        self.bufs = (ctypes.c_void_p * self.world)(*[int(p) for p in h.buffer_ptrs])
+        self.pads = (ctypes.c_void_p * self.world)(*[int(p) for p in h.signal_pad_ptrs])
+        mc = 0
+        try:
+            mc = int(h.multicast_ptr) if h.has_multicast_support else 0
+        except Exception:
+            mc = 0
+        self.multicast = mc
+        self.pad_bytes = int(getattr(h, "signal_pad_size", 2048))
+
+
+class NativeComm:
+    name = "native"
+    fuses_unscale = True
+
+    def __init__(self, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        require()
+        L = require()
+        if not hasattr(L, "pdb_allreduce_inplace"):
+            raise RuntimeError("libpdb200.so was built without csrc/comm")
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        try:
+            gname = (group if group is not None else dist.group.WORLD).group_name
+            symm_mem.enable_symm_mem_for_group(gname)
+        except Exception:
+            pass
+        self.stream = torch.cuda.Stream(self.device, priority=-1)
+        self._mapped: Dict[int, _Mapped] = {}
+        # symmetric scratch: [0:64) non-finite flags, then the staging area of the small all-reduce
+        self.slot = 8192
+        self._aux_t = symm_mem.empty(64 + self.world * self.slot, dtype=torch.float32, device=self.device)
+        self._aux_t.zero_()
+        self._aux = _Mapped(self._aux_t, group)
+        self.flag = self._aux_t[:1]
+        fl = [int(p) for p in self._aux.handle.buffer_ptrs]
+        self._flag_ptrs = (ctypes.c_void_p * self.world)(*fl)
+        self._staging_ptrs = (ctypes.c_void_p * self.world)(*[p + 64 * 4 for p in fl])
+        self.use_multicast = os.environ.get("PDB200_NVLS", "1") != "0"
+        self.blocks = int(os.environ.get("PDB200_COMM_BLOCKS", "24"))
+        self._events: List[torch.cuda.Event] = []
+        self._pass_started = False
+        self._found_inf: Optional[torch.Tensor] = None
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group)
+
+    # -- registration -----------------------------------------------------------------------------------
+    def _map(self, t: torch.Tensor) -> _Mapped:
+        key = t.untyped_storage().data_ptr()
+        m = self._mapped.get(key)
+        if m is None:
+            m = _Mapped(t, self.group)
+            self._mapped[key] = m
+        return m
+
+    def register_arena(self, arena) -> None:
+        if not (getattr(arena, "grads_symmetric", False) and getattr(arena, "params_symmetric", False)):
+            raise RuntimeError("NativeComm needs arenas in symmetric memory: create the process group before "
+                               "the model's arenas (ParamArena allocates symmetric memory when it is initialised)")
+        self._map(arena.grads)
+        self._map(arena.params)
+
+    def _blocks(self, m: _Mapped, n: int) -> int:
+        cap = require().pdb_comm_max_blocks(self.world, m.pad_bytes)
+        want = max(1, min(self.blocks, cap, (n // 4 + 511) // 512))
+        return want
+
+    # -- collectives ------------------------------------------------------------------------------------
+    def broadcast_(self, flat: torch.Tensor, src: int = 0) -> None:
+        if self.world == 1:
+            return
+        sym = flat.untyped_storage().data_ptr() in self._mapped or getattr(flat, "_pdb200_symmetric", False)
+        if not sym:
+            try:
+                m = self._map(flat)
+            except Exception:
+                dist.broadcast(flat, src, group=self.group)
+                return
+        m = self._map(flat)
+        start = (flat.data_ptr() - m.tensor.data_ptr()) // 4
+        n = flat.numel() * flat.element_size() // 4
+        if n % 4 or start % 4:
+            dist.broadcast(flat, src, group=self.group)
+            return
+        check(require().pdb_broadcast_inplace(m.bufs, m.pads, self.rank, self.world, src, start, n,
+                                              self._blocks(m, n), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)),
+              "pdb_broadcast_inplace")
+        count_launch()
+
+    def allreduce_range(self, flat: torch.Tensor, start: int, end: int, *, average: bool = True,
+                        wire_dtype=None, inv_scale=None, found_inf=None) -> None:
+        if self.world == 1:
+            return
+        m = self._map(flat)
+        cur = torch.cuda.current_stream(self.device)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.stream.wait_event(ev)
+        with torch.cuda.stream(self.stream):
+            if not self._pass_started:
+                self._pass_started = True
+                self.flag.zero_()
+            self._found_inf = found_inf
+            n = end - start
+            check(require().pdb_allreduce_inplace(
+                m.bufs, m.pads, self._flag_ptrs if found_inf is not None else None,
+                ctypes.c_void_p(m.multicast if self.use_multicast else 0), self.rank, self.world, start, n,
+                (1.0 / self.world) if average else 1.0, ptr(inv_scale), self._blocks(m, n),
+                ctypes.c_void_p(self.stream.cuda_stream)), "pdb_allreduce_inplace")
+            count_launch()
+            done = torch.cuda.Event()
+            done.record(self.stream)
+        self._events.append(done)
+
+    def wait_all(self) -> None:
+        cur = torch.cuda.current_stream(self.device)
+        if self._events:
+            cur.wait_event(self._events[-1])          # stream order on the comm stream covers the earlier ones
+            self._events.clear()
+        if self._found_inf is not None:
+            torch.maximum(self._found_inf, self.flag[0], out=self._found_inf)
+            self._found_inf = None
+        self._pass_started = False
+
+    def allreduce_small_(self, data: torch.Tensor) -> None:
+        """In-place sum over ranks of a small fp32 vector (SyncBN statistics, metric accumulators)."""
+        if self.world == 1:
+            return
+        n = data.numel()
+        if n > self.slot or data.dtype != torch.float32 or not data.is_contiguous():
+            dist.all_reduce(data, group=self.group)
+            return
+        check(require().pdb_small_allreduce(self._staging_ptrs, self._aux.pads, self.rank, self.world, ptr(data), n,
+                                            self.slot, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)),
+              "pdb_small_allreduce")
+        count_launch()

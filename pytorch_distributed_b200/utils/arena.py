@@ -39,6 +39,33 @@ def _round_up(n: int, a: int) -> int:
     return (n + a - 1) // a * a
 
 
+def want_symmetric(device: torch.device) -> bool:
+    """Arenas are placed in NVLink-symmetric memory when they will take part in peer-memory collectives:
+    CUDA device, NCCL process group (used only for the handle exchange), more than one rank."""
+    import os
+    if os.environ.get("PDB200_SYMM", "1") == "0" or torch.device(device).type != "cuda":
+        return False
+    try:
+        import torch.distributed as dist
+        return dist.is_available() and dist.is_initialized() and dist.get_backend() == "nccl" and dist.get_world_size() > 1
+    except Exception:
+        return False
+
+
+def alloc_flat(n: int, dtype: torch.dtype, device: torch.device, symmetric: bool):
+    """Zero-initialised flat buffer; returns (tensor, is_symmetric).  Symmetric allocations must happen in
+    the same order on every rank (they do: every rank builds the same model)."""
+    if symmetric:
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            t = symm_mem.empty(n, dtype=dtype, device=device)
+            t.zero_()
+            return t, True
+        except Exception:
+            pass
+    return torch.zeros(n, dtype=dtype, device=device), False
+
+
 def _view(flat: torch.Tensor, e: ArenaEntry) -> torch.Tensor:
     seg = flat[e.offset: e.offset + e.numel]
     if e.channels_last:
@@ -62,8 +89,9 @@ class ParamArena:
             self.entries.append(ArenaEntry(n, off, p.numel(), p.shape, cl))
             off = _round_up(off + p.numel(), ALIGN_ELEMS)
         self.numel = off
-        self.params = torch.zeros(off, dtype=torch.float32, device=device)
-        self.grads = torch.zeros(off, dtype=torch.float32, device=device)
+        symmetric = want_symmetric(device)
+        self.params, self.params_symmetric = alloc_flat(off, torch.float32, device, symmetric)
+        self.grads, self.grads_symmetric = alloc_flat(off, torch.float32, device, symmetric)
         self.momentum: Optional[torch.Tensor] = None
         self.shadow: Optional[torch.Tensor] = None     # 16-bit copy of the weights for the MMA path
         self.by_name: Dict[str, ArenaEntry] = {e.name: e for e in self.entries}
@@ -150,13 +178,25 @@ class BufferArena:
         for n, b in f:
             self.float_entries.append(ArenaEntry(n, off, b.numel(), b.shape, False))
             off = _round_up(off + b.numel(), 4)
-        self.floats = torch.zeros(max(off, 1), dtype=torch.float32, device=device)
+        n_float = _round_up(max(off, 1), 4)
         self.int_entries: List[ArenaEntry] = []
-        off = 0
+        ioff = 0
         for n, b in i:
-            self.int_entries.append(ArenaEntry(n, off, b.numel(), b.shape, False))
-            off += b.numel()
-        self.ints = torch.zeros(max(off, 1), dtype=torch.int64, device=device)
+            self.int_entries.append(ArenaEntry(n, ioff, b.numel(), b.shape, False))
+            ioff += b.numel()
+        n_int = max(ioff, 1)
+        # one allocation: fp32 statistics followed by the int64 counters (viewed through the same bytes),
+        # so the per-iteration DDP buffer broadcast is a single transfer
+        total = _round_up(n_float + 2 * n_int, 4)
+        self.storage, self.symmetric = alloc_flat(total, torch.float32, device, want_symmetric(device))
+        self.floats = self.storage[:n_float]
+        # The counters are updated with real in-place ops (num_batches_tracked += 1).  A plain view would
+        # share the storage's autograd version counter with running_mean/var, which BN saves for backward,
+        # and every later layer's increment would look like an illegal in-place modification.  A DLPack
+        # round trip aliases the same bytes with an independent version counter.
+        from torch.utils import dlpack
+        ints_alias = dlpack.from_dlpack(dlpack.to_dlpack(self.storage[n_float: n_float + 2 * n_int]))
+        self.ints = ints_alias.view(torch.int64)
         owners = {}
         for mod_name, mod in module.named_modules():
             for bn, _ in mod.named_buffers(recurse=False):

@@ -1,0 +1,90 @@
+"""Peer-memory collectives and the DDP / DP engines on >= 2 GPUs, against NCCL as the oracle."""
+import json
+
+import pytest
+import torch
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+from pytorch_distributed_b200 import launcher, ops  # noqa: E402
+
+from . import _mp_gpu as W  # noqa: E402
+
+
+def _world():
+    return min(torch.cuda.device_count(), 8)
+
+
+@pytest.mark.timeout(600)
+def test_collectives_match_nccl(tmp_path, free_port):
+    world = _world()
+    launcher.spawn(W.comm_worker, args=(world, free_port, str(tmp_path)), nprocs=world)
+    for r in range(world):
+        res = json.load(open(tmp_path / f"comm_{r}.json"))
+        for k, v in res.items():
+            if k.startswith("allreduce_err"):
+                assert v < 1e-5, (k, v, res)          # fp32 sums in a fixed order: only association differs
+            elif k.startswith("found_inf_clean"):
+                assert v == 0.0, res
+            elif k.startswith("found_inf_injected"):
+                assert v == 1.0, res                  # ... on every rank, not only the one that saw the inf
+        assert res["broadcast_ok"] and res["small_allreduce_ok"] and res["soak_ok"], res
+
+
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("sync_bn", [False, True])
+def test_ddp_native_comm_matches_nccl_backend(tmp_path, free_port, sync_bn):
+    world = _world()
+    for i, backend in enumerate(("native", "nccl")):
+        launcher.spawn(W.ddp_native_worker, args=(world, free_port + i, str(tmp_path), backend, sync_bn), nprocs=world)
+    nat = [torch.load(tmp_path / f"ddp_native_{int(sync_bn)}_{r}.pt") for r in range(world)]
+    ref = [torch.load(tmp_path / f"ddp_nccl_{int(sync_bn)}_{r}.pt") for r in range(world)]
+    assert nat[0]["comm"] == "native" and ref[0]["comm"] == "torch"
+    for r in range(1, world):
+        assert torch.equal(nat[0]["params"], nat[r]["params"])        # replicas stay bit-identical
+    for r in range(world):
+        assert nat[r]["losses"] == pytest.approx(ref[r]["losses"], rel=2e-2)
+        assert nat[r]["scale"] == 65536.0
+    cos = torch.nn.functional.cosine_similarity(nat[0]["params"] - ref[0]["params"].mean() * 0, ref[0]["params"], dim=0)
+    assert float(cos) > 0.9999
+
+
+def test_dp_peer_kernels():
+    d0, d1 = torch.device("cuda", 0), torch.device("cuda", 1)
+    src = torch.randn(1 << 20, device=d0)
+    dst = ops.peer_copy(src, d1)
+    torch.cuda.synchronize(d1)
+    assert torch.equal(dst.cpu(), src.cpu())
+    root = torch.randn(1 << 20, device=d0)
+    peers = [torch.randn(1 << 20, device=torch.device("cuda", i)) for i in range(1, torch.cuda.device_count())]
+    want = root.cpu() + sum(p.cpu() for p in peers)
+    ops.reduce_to_root(root, peers)
+    torch.cuda.synchronize(d0)
+    assert torch.allclose(root.cpu(), want, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.timeout(600)
+def test_data_parallel_native_two_gpus():
+    """DP mode with the native engine per replica: gradients are the SUM over replicas on GPU 0."""
+    import copy
+    from pytorch_distributed_b200.models import resnet50
+    from pytorch_distributed_b200.nn import CrossEntropyLoss
+    from pytorch_distributed_b200.parallel import DataParallel
+    torch.manual_seed(0)
+    base = resnet50().cuda(0)
+    ref = copy.deepcopy(base)
+    base.enable_native(batch_size=8, dtype=torch.bfloat16)
+    ref.enable_native(batch_size=8, dtype=torch.bfloat16)
+    dp = DataParallel(base, device_ids=[0, 1], output_device=0)
+    x = torch.randn(16, 3, 64, 64, device="cuda:0")
+    y = torch.randint(0, 1000, (16,), device="cuda:0")
+    out = dp(x)
+    assert out.shape == (16, 1000) and out.device.index == 0
+    (CrossEntropyLoss()(out, y) * 2).backward()          # mean over 16 rows
+    torch.cuda.synchronize()
+    for cx, cy in zip(x.chunk(2), y.chunk(2)):
+        CrossEntropyLoss()(ref(cx), cy).backward()       # mean over 8 rows each -> same total scale
+    torch.cuda.synchronize()
+    a, b = base._pdb200_arena.grads, ref._pdb200_arena.grads
+    assert float(torch.nn.functional.cosine_similarity(a, b, dim=0)) > 0.98
+    assert 0.9 < float(a.norm() / b.norm()) < 1.1
