@@ -99,30 +99,60 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_kernel(PeerPtrs pp, fl
   const int64_t per = (n4 + world - 1) / world;
   const int64_t lo = min(per * rank, n4), hi = min(lo + per, n4);
   bool bad = false;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
-    const int64_t off = start + i * 4;
-    float4 acc;
+  // Latency-bound over NVLink (~2 us per remote access): keep kUnroll independent 16-byte requests in
+  // flight per thread (32 CTAs x 512 threads x 8 x 16 B = 2 MB, the bandwidth-delay product of one
+  // NVLink direction), issue all loads of a batch before the first add.
+  constexpr int kUnroll = 8;
+  const int64_t tile = (int64_t)blockDim.x * kUnroll;
+  for (int64_t base = lo + (int64_t)blockIdx.x * tile; base < hi; base += (int64_t)gridDim.x * tile) {
+    float4 acc[kUnroll];
+    int64_t off[kUnroll];
+    bool live[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+      live[u] = i < hi;
+      off[u] = start + (live[u] ? i : lo) * 4;
+    }
     if (kMulticast) {
-      acc = multimem_ld_reduce(mc + off);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u)
+        if (live[u]) acc[u] = multimem_ld_reduce(mc + off[u]);
     } else {
-      acc = ld_peer(pp.buf[rank] + off);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u)
+        if (live[u]) acc[u] = ld_peer(pp.buf[rank] + off[u]);
 #pragma unroll 1
       for (int k = 1; k < world; ++k) {
         const int p = rank + k < world ? rank + k : rank + k - world;     // stagger peers across ranks
-        const float4 v = ld_peer(pp.buf[p] + off);
-        acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+        const float* src = pp.buf[p];
+        float4 v[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+          if (live[u]) v[u] = ld_peer(src + off[u]);
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+          if (live[u]) acc[u].x += v[u].x, acc[u].y += v[u].y, acc[u].z += v[u].z, acc[u].w += v[u].w;
       }
     }
-    acc.x *= s, acc.y *= s, acc.z *= s, acc.w *= s;
-    bad |= !(isfinite(acc.x) && isfinite(acc.y) && isfinite(acc.z) && isfinite(acc.w));
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      if (!live[u]) continue;
+      acc[u].x *= s, acc[u].y *= s, acc[u].z *= s, acc[u].w *= s;
+      bad |= !(isfinite(acc[u].x) && isfinite(acc[u].y) && isfinite(acc[u].z) && isfinite(acc[u].w));
+    }
     if (kMulticast) {
-      multimem_st(mc + off, acc);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u)
+        if (live[u]) multimem_st(mc + off[u], acc[u]);
     } else {
 #pragma unroll 1
       for (int k = 0; k < world; ++k) {
         const int p = rank + k < world ? rank + k : rank + k - world;
-        st_peer(pp.buf[p] + off, acc);
+        float* dst = pp.buf[p];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+          if (live[u]) st_peer(dst + off[u], acc[u]);
       }
     }
   }
@@ -142,8 +172,22 @@ __global__ void __launch_bounds__(kCommThreads) broadcast_kernel(PeerPtrs pp, in
     const int64_t n4 = n / 4, stride = (int64_t)gridDim.x * blockDim.x;
     const float* src = pp.buf[root] + start;
     float* dst = pp.buf[rank] + start;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride)
-      reinterpret_cast<float4*>(dst)[i] = ld_peer(src + i * 4);
+    constexpr int kUnroll = 8;
+    const int64_t tile = (int64_t)blockDim.x * kUnroll;
+    (void)stride;
+    for (int64_t base = (int64_t)blockIdx.x * tile; base < n4; base += (int64_t)gridDim.x * tile) {
+      float4 v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+        if (i < n4) v[u] = ld_peer(src + i * 4);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+        if (i < n4) reinterpret_cast<float4*>(dst)[i] = v[u];
+      }
+    }
   }
   cross_rank_barrier(pp.pad, rank, world);            // root may overwrite its copy only after everyone has read it
 }
@@ -169,11 +213,21 @@ __global__ void __launch_bounds__(1024) small_allreduce_kernel(PeerPtrs pp, int 
 
 // ---- single-process DataParallel helpers (all GPUs in one address space, peer access enabled) ----------
 __global__ void __launch_bounds__(256) peer_pull_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src, int64_t n16) {
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
-    uint4 v;
-    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(src + i));
-    dst[i] = v;
+  constexpr int kUnroll = 8;
+  const int64_t tile = (int64_t)blockDim.x * kUnroll;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < n16; base += (int64_t)gridDim.x * tile) {
+    uint4 v[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+      if (i < n16)
+        asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + i));
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+      if (i < n16) dst[i] = v[u];
+    }
   }
 }
 
@@ -211,7 +265,7 @@ using namespace pdb;
 extern "C" int pdb_comm_max_blocks(int world, size_t signal_pad_bytes) {
   const size_t slots = signal_pad_bytes / sizeof(uint32_t);
   int b = (int)(slots / (size_t)(world > 0 ? world : 1));
-  return b > 32 ? 32 : b;
+  return b > 64 ? 64 : b;
 }
 
 extern "C" int pdb_allreduce_inplace(void* const* bufs, void* const* pads, void* const* flags, void* multicast, int rank,
@@ -221,7 +275,7 @@ extern "C" int pdb_allreduce_inplace(void* const* bufs, void* const* pads, void*
   PDB_CHECK_ARG(n % 4 == 0 && start % 4 == 0, "pdb_allreduce_inplace: range must be 16-byte aligned (start=%lld n=%lld)",
                 (long long)start, (long long)n);
   PDB_CHECK_ARG(rank >= 0 && rank < world, "pdb_allreduce_inplace: rank %d out of range", rank);
-  PDB_CHECK_ARG(blocks >= 1 && blocks <= 32, "pdb_allreduce_inplace: blocks must be in [1, 32]");
+  PDB_CHECK_ARG(blocks >= 1 && blocks <= 64, "pdb_allreduce_inplace: blocks must be in [1, 64]");
   if (n == 0) return 0;
   PeerPtrs pp;
   if (int e = fill_peers(&pp, bufs, pads, flags, world)) return e;
@@ -238,7 +292,7 @@ extern "C" int pdb_broadcast_inplace(void* const* bufs, void* const* pads, int r
                                      int64_t n, int blocks, void* stream) {
   PDB_CHECK_ARG(bufs && pads && n >= 0 && n % 4 == 0 && start % 4 == 0, "pdb_broadcast_inplace: bad arguments");
   PDB_CHECK_ARG(rank >= 0 && rank < world && root >= 0 && root < world, "pdb_broadcast_inplace: bad rank/root");
-  PDB_CHECK_ARG(blocks >= 1 && blocks <= 32, "pdb_broadcast_inplace: blocks must be in [1, 32]");
+  PDB_CHECK_ARG(blocks >= 1 && blocks <= 64, "pdb_broadcast_inplace: blocks must be in [1, 64]");
   if (n == 0) return 0;
   PeerPtrs pp;
   if (int e = fill_peers(&pp, bufs, pads, nullptr, world)) return e;
@@ -288,7 +342,7 @@ extern "C" int pdb_peer_pull(void* dst, const void* src, int64_t bytes, void* st
   if (int e = enable_peer(cur, sdev)) return e;
   const int64_t n16 = bytes / 16;
   int64_t want = (n16 + 255) / 256;
-  const int grid = (int)(want < 64 ? want : 64);          // a few dozen CTAs saturate an NVLink direction
+  const int grid = (int)(want < 128 ? want : 128);        // ~2 MB in flight saturates an NVLink direction
   peer_pull_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((uint4*)dst, (const uint4*)src, n16);
   PDB_LAUNCH_CHECK();
   return 0;

@@ -33,29 +33,48 @@ __device__ __forceinline__ void reduce_rows(const T* __restrict__ a, const T* __
       rs[k] = rstd[cg * 8 + k];
     }
   }
-  for (int64_t r = (int64_t)blockIdx.x * ry + ty; r < rows; r += (int64_t)gridDim.x * ry) {
-    const int64_t off = r * C + (int64_t)cg * 8;
-    float fa[8];
-    unpack8<T>(ldg128_stream(a + off), fa);
-    if (MODE == 0) {
+  constexpr int U = 4;                     // rows in flight per thread
+  const int64_t rstride = (int64_t)gridDim.x * ry;
+  for (int64_t r0 = (int64_t)blockIdx.x * ry + ty; r0 < rows; r0 += rstride * U) {
+    uint4 va[U], vx[U], vz[U];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        s0[k] += fa[k];
-        s1[k] = fmaf(fa[k], fa[k], s1[k]);
+    for (int u = 0; u < U; ++u) {
+      const int64_t r = r0 + u * rstride;
+      if (r < rows) {
+        const int64_t off = r * C + (int64_t)cg * 8;
+        va[u] = ldg128_stream(a + off);
+        if (MODE == 1) {
+          vx[u] = ldg128_stream(x + off);
+          if (kHasZ) vz[u] = ldg128_stream(z + off);
+        }
       }
-    } else {
-      float fx[8];
-      unpack8<T>(ldg128_stream(x + off), fx);
-      if (kHasZ) {
-        float fz[8];
-        unpack8<T>(ldg128_stream(z + off), fz);
+    }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) fa[k] = fz[k] > 0.f ? fa[k] : 0.f;
-      }
+    for (int u = 0; u < U; ++u) {
+      const int64_t r = r0 + u * rstride;
+      if (r >= rows) continue;
+      float fa[8];
+      unpack8<T>(va[u], fa);
+      if (MODE == 0) {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        s0[k] += fa[k];
-        s1[k] = fmaf(fa[k], (fx[k] - mu[k]) * rs[k], s1[k]);
+        for (int k = 0; k < 8; ++k) {
+          s0[k] += fa[k];
+          s1[k] = fmaf(fa[k], fa[k], s1[k]);
+        }
+      } else {
+        float fx[8];
+        unpack8<T>(vx[u], fx);
+        if (kHasZ) {
+          float fz[8];
+          unpack8<T>(vz[u], fz);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) fa[k] = fz[k] > 0.f ? fa[k] : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          s0[k] += fa[k];
+          s1[k] = fmaf(fa[k], (fx[k] - mu[k]) * rs[k], s1[k]);
+        }
       }
     }
   }
@@ -186,25 +205,39 @@ __global__ void __launch_bounds__(kThreads) bn_apply_kernel(const T* __restrict_
   if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches_tracked) *num_batches_tracked += 1;
   __syncthreads();
   const int cvec = C / 8;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
-    const int c0 = (int)(i % cvec) * 8;
-    float f[8];
-    unpack8<T>(ldg128_stream(x + i * 8), f);
-    if (kRes) {
-      float r[8];
-      unpack8<T>(ldg128_stream(res + i * 8), r);
+  constexpr int U = 4;                     // independent 128-bit requests in flight per thread and stream
+  const int64_t tile = (int64_t)blockDim.x * U;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < nvec; base += (int64_t)gridDim.x * tile) {
+    uint4 vx[U], vr[U];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], scale[c0 + k], shift[c0 + k]) + r[k];
-    } else {
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+      if (i < nvec) {
+        vx[u] = ldg128_stream(x + i * 8);
+        if (kRes) vr[u] = ldg128_stream(res + i * 8);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+      if (i >= nvec) continue;
+      const int c0 = (int)(i % cvec) * 8;
+      float f[8];
+      unpack8<T>(vx[u], f);
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], scale[c0 + k], shift[c0 + k]);
-    }
-    if (kRelu) {
+      if (kRes) {
+        float r[8];
+        unpack8<T>(vr[u], r);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+        for (int k = 0; k < 8; ++k) f[k] += r[k];
+      }
+      if (kRelu) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+      }
+      stg128(y + i * 8, pack8<T>(f));
     }
-    stg128(y + i * 8, pack8<T>(f));
   }
 }
 
@@ -277,23 +310,39 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const T* __restr
   }
   __syncthreads();
   const int cvec = C / 8;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
-    const int c0 = (int)(i % cvec) * 8;
-    float g[8], fx[8];
-    unpack8<T>(ldg128_stream(dz + i * 8), g);
-    unpack8<T>(ldg128_stream(x + i * 8), fx);
-    if (kHasZ) {
-      float fz[8];
-      unpack8<T>(ldg128_stream(z + i * 8), fz);
+  constexpr int U = 2;
+  const int64_t tile = (int64_t)blockDim.x * U;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < nvec; base += (int64_t)gridDim.x * tile) {
+    uint4 vg[U], vx[U], vz[U];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] = fz[k] > 0.f ? g[k] : 0.f;
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+      if (i < nvec) {
+        vg[u] = ldg128_stream(dz + i * 8);
+        vx[u] = ldg128_stream(x + i * 8);
+        if (kHasZ) vz[u] = ldg128_stream(z + i * 8);
+      }
     }
-    if (kDres) stg128(dres + i * 8, pack8<T>(g));
-    float o[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) o[k] = fmaf(A[c0 + k], g[k], fmaf(B[c0 + k], fx[k], Cc[c0 + k]));
-    stg128(dx + i * 8, pack8<T>(o));
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+      if (i >= nvec) continue;
+      const int c0 = (int)(i % cvec) * 8;
+      float g[8], fx[8];
+      unpack8<T>(vg[u], g);
+      unpack8<T>(vx[u], fx);
+      if (kHasZ) {
+        float fz[8];
+        unpack8<T>(vz[u], fz);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] = fz[k] > 0.f ? g[k] : 0.f;
+      }
+      if (kDres) stg128(dres + i * 8, pack8<T>(g));
+      float o[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = fmaf(A[c0 + k], g[k], fmaf(B[c0 + k], fx[k], Cc[c0 + k]));
+      stg128(dx + i * 8, pack8<T>(o));
+    }
   }
 }
 

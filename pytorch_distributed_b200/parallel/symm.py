@@ -54,11 +54,6 @@ class NativeComm:
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.device = torch.device("cuda", torch.cuda.current_device())
-        try:
-            gname = (group if group is not None else dist.group.WORLD).group_name
-            symm_mem.enable_symm_mem_for_group(gname)
-        except Exception:
-            pass
         self.stream = torch.cuda.Stream(self.device, priority=-1)
         self._mapped: Dict[int, _Mapped] = {}
         # symmetric scratch: [0:64) non-finite flags, then the staging area of the small all-reduce
@@ -71,7 +66,7 @@ class NativeComm:
         self._flag_ptrs = (ctypes.c_void_p * self.world)(*fl)
         self._staging_ptrs = (ctypes.c_void_p * self.world)(*[p + 64 * 4 for p in fl])
         self.use_multicast = os.environ.get("PDB200_NVLS", "1") != "0"
-        self.blocks = int(os.environ.get("PDB200_COMM_BLOCKS", "24"))
+        self.blocks = int(os.environ.get("PDB200_COMM_BLOCKS", "32"))
         self._events: List[torch.cuda.Event] = []
         self._pass_started = False
         self._found_inf: Optional[torch.Tensor] = None
@@ -96,7 +91,7 @@ class NativeComm:
 
     def _blocks(self, m: _Mapped, n: int) -> int:
         cap = require().pdb_comm_max_blocks(self.world, m.pad_bytes)
-        want = max(1, min(self.blocks, cap, (n // 4 + 511) // 512))
+        want = max(1, min(self.blocks, cap, (n // 4 + 4095) // 4096))
         return want
 
     # -- collectives ------------------------------------------------------------------------------------
