@@ -205,6 +205,8 @@ __global__ void __launch_bounds__(kThreads) bn_apply_kernel(const T* __restrict_
   if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches_tracked) *num_batches_tracked += 1;
   __syncthreads();
   const int cvec = C / 8;
+  const bool fixed_c = (blockDim.x % cvec) == 0;
+  const int c_fixed = (int)(threadIdx.x % cvec) * 8;
   constexpr int U = 4;                     // independent 128-bit requests in flight per thread and stream
   const int64_t tile = (int64_t)blockDim.x * U;
   for (int64_t base = (int64_t)blockIdx.x * tile; base < nvec; base += (int64_t)gridDim.x * tile) {
@@ -221,7 +223,9 @@ __global__ void __launch_bounds__(kThreads) bn_apply_kernel(const T* __restrict_
     for (int u = 0; u < U; ++u) {
       const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
       if (i >= nvec) continue;
-      const int c0 = (int)(i % cvec) * 8;
+      // 64-bit modulo is ~50 instructions; every base is a multiple of blockDim, so when cvec divides
+      // blockDim (all power-of-two channel counts) the channel offset is a per-thread constant
+      const int c0 = fixed_c ? c_fixed : (int)(i % cvec) * 8;
       float f[8];
       unpack8<T>(vx[u], f);
 #pragma unroll
@@ -310,6 +314,8 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const T* __restr
   }
   __syncthreads();
   const int cvec = C / 8;
+  const bool fixed_c = (blockDim.x % cvec) == 0;
+  const int c_fixed = (int)(threadIdx.x % cvec) * 8;
   constexpr int U = 2;
   const int64_t tile = (int64_t)blockDim.x * U;
   for (int64_t base = (int64_t)blockIdx.x * tile; base < nvec; base += (int64_t)gridDim.x * tile) {
@@ -327,7 +333,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const T* __restr
     for (int u = 0; u < U; ++u) {
       const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
       if (i >= nvec) continue;
-      const int c0 = (int)(i % cvec) * 8;
+      const int c0 = fixed_c ? c_fixed : (int)(i % cvec) * 8;
       float g[8], fx[8];
       unpack8<T>(vg[u], g);
       unpack8<T>(vx[u], fx);

@@ -641,9 +641,11 @@ extern "C" int pdb_conv_wgrad(const void* x, const void* dy, float* dw, int dtyp
   p.num_kb = (int)((M + 63) / 64);
   const int tiles = p.num_m_blocks * p.num_n_blocks;
   if (splits <= 0) {
-    // enough work items for ~2 waves of persistent CTAs, but keep at least 8 k-blocks per item
-    splits = (2 * num_sms() + tiles - 1) / tiles;
-    const int max_splits = (p.num_kb + 7) / 8;
+    // One wave of persistent CTAs: items = tiles * splits must not spill over the SM count (a second,
+    // nearly empty wave doubles the time — measured with bench_tools/conv_tune.py), and every extra split
+    // costs a full tile of fp32 reductions; keep at least 4 k-blocks of work per item.
+    splits = num_sms() / tiles;
+    const int max_splits = (p.num_kb + 3) / 4;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
   }

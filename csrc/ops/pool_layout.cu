@@ -375,3 +375,35 @@ extern "C" int pdb_colsum16(const void* a, float* out, int dtype, int rows, int 
   PDB_LAUNCH_CHECK();
   return 0;
 }
+
+// Batched dgrad weight layout: one launch re-arranges every convolution of the network.
+// table[i] = {w_off, wt_off, K, R, S, C} (element offsets into w_base / wt_base), in device memory.
+namespace pdb {
+template <typename T>
+__global__ void __launch_bounds__(256) weight_dgrad_batched_kernel(const T* __restrict__ w_base, T* __restrict__ wt_base,
+                                                                   const int64_t* __restrict__ table) {
+  const int64_t* e = table + (int64_t)blockIdx.y * 6;
+  const T* w = w_base + e[0];
+  T* wt = wt_base + e[1];
+  const int K = (int)e[2], R = (int)e[3], S = (int)e[4], C = (int)e[5];
+  const int64_t total = (int64_t)C * R * S * K, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int k = (int)(i % K);
+    int64_t t = i / K;
+    const int s = (int)(t % S);
+    t /= S;
+    const int r = (int)(t % R);
+    const int c = (int)(t / R);
+    wt[i] = w[(((int64_t)k * R + (R - 1 - r)) * S + (S - 1 - s)) * C + c];
+  }
+}
+}  // namespace pdb
+
+extern "C" int pdb_weight_dgrad_layout_batched(const void* w_base, void* wt_base, const int64_t* table_dev, int n,
+                                               int dtype, void* stream) {
+  PDB_CHECK_ARG(w_base && wt_base && table_dev && n > 0 && n <= 65535, "pdb_weight_dgrad_layout_batched: bad arguments");
+  dim3 grid(64, n);
+  PDB_DISPATCH_16(dtype, T, (weight_dgrad_batched_kernel<T><<<grid, 256, 0, ST>>>((const T*)w_base, (T*)wt_base, table_dev)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}

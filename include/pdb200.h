@@ -159,6 +159,10 @@ int pdb_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, const pd
 
 /* wt[C, R, S, K] = w[K, R-1-r, S-1-s, C]: weight layout for running dgrad through pdb_conv_fprop. */
 int pdb_weight_dgrad_layout(const void* w, void* wt, int dtype, int K, int R, int S, int C, void* stream);
+/* The same for n convolutions in one launch: table_dev is a device array of n x {w_off, wt_off, K, R, S,
+ * C} (int64, element offsets into w_base / wt_base). */
+int pdb_weight_dgrad_layout_batched(const void* w_base, void* wt_base, const int64_t* table_dev, int n, int dtype,
+                                    void* stream);
 /* dst[rows, cols_dst] = src[rows, cols_src] zero-padded on the right (16-bit). */
 int pdb_pad_rows16(const void* src, void* dst, int dtype, int rows, int cols_src, int cols_dst, void* stream);
 /* out[c] += sum_r a[r, c] (16-bit in, fp32 out): fc bias gradient. */

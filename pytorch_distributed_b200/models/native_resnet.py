@@ -45,7 +45,8 @@ class _ConvPlan:
         self.pindex = eng.pindex[name + ".weight"]
         self.w16 = eng.arena.shadow_view(name + ".weight")                  # [K, R, S, C] 16-bit
         self.dw = eng.arena.grads[eng.arena.by_name[name + ".weight"].offset:][: self.K * self.R * self.S * self.C]
-        self.wt16 = torch.empty(self.C * self.R * self.S * self.K, dtype=eng.dtype, device=eng.device)
+        self.w_off = eng.arena.by_name[name + ".weight"].offset
+        self.wt16 = None                      # slice of the engine's flat dgrad-weight buffer (set later)
 
     def shape(self, N: int, H: int, W: int) -> ConvShape:
         return ConvShape(N, H, W, self.C, self.K, self.R, self.S, self.stride, self.pad)
@@ -129,7 +130,6 @@ class NativeResNetEngine:
         fc = model.fc
         self.fc_K, self.fc_C = fc.out_features, fc.in_features
         self.fc_w16 = self.arena.shadow_view("fc.weight")
-        self.fc_wt16 = torch.empty(self.fc_C * self.fc_K, dtype=dtype, device=self.device)
         self.fc_bias = self.arena.param_view("fc.bias")
         e = self.arena.by_name["fc.weight"]
         self.fc_dw = self.arena.grads[e.offset: e.offset + e.numel]
@@ -140,6 +140,21 @@ class NativeResNetEngine:
         self._anchor = model.fc.bias
         self._convs: List[_ConvPlan] = [self.stem_conv] + [c for b in self.blocks for c in
                                                            (b.conv1, b.conv2, b.conv3, b.convd) if c is not None]
+        # dgrad operand layouts [Cin, kh, kw(flipped), Cout] of every conv but the stem, plus fc, in ONE flat
+        # buffer so a single batched launch refreshes them all from the weight shadow
+        table, off = [], 0
+        for cv in self._convs[1:]:
+            n = cv.K * cv.R * cv.S * cv.C
+            table.append([cv.w_off, off, cv.K, cv.R, cv.S, cv.C])
+            off += (n + 63) // 64 * 64
+        fc_off = off
+        table.append([e.offset, fc_off, self.fc_K, 1, 1, self.fc_C])
+        off += (self.fc_K * self.fc_C + 63) // 64 * 64
+        self.wt_all = torch.empty(off, dtype=dtype, device=self.device)
+        for cv, row in zip(self._convs[1:], table):
+            cv.wt16 = self.wt_all[row[1]: row[1] + cv.K * cv.R * cv.S * cv.C]
+        self.fc_wt16 = self.wt_all[fc_off: fc_off + self.fc_K * self.fc_C]
+        self._wt_table = torch.tensor(table, dtype=torch.int64, device=self.device)
 
     # -- plan construction -------------------------------------------------------------------------
     def _conv(self, name: str, conv: nn.Conv2d) -> _ConvPlan:
@@ -168,9 +183,7 @@ class NativeResNetEngine:
         c = self.stem_conv
         ops.pad_rows16(c.w16, self.stem_w16, c.K, c.R * c.S * c.C, STEM_KPAD)
         if need_dgrad:
-            for cv in self._convs[1:]:
-                ops.weight_dgrad_layout(cv.w16, cv.wt16, cv.K, cv.R, cv.S, cv.C)
-            ops.weight_dgrad_layout(self.fc_w16, self.fc_wt16, self.fc_K, 1, 1, self.fc_C)
+            ops.weight_dgrad_layout_batched(self.arena.shadow, self.wt_all, self._wt_table, self._wt_table.shape[0])
 
     def _sync_stats(self, buf: torch.Tensor) -> float:
         """SyncBatchNorm: sums are additive, so one all-reduce of [2C] per layer and direction."""

@@ -13,7 +13,7 @@ from ._sigs import ConvShape
 __all__ = ["dtype_tag", "sgd_step", "check_finite", "cast_to_16", "xent_fwd_bwd", "topk_correct", "bn_stats",
            "bn_apply", "bn_apply_eval", "bn_bwd_reduce", "bn_bwd_apply", "maxpool_fwd", "maxpool_bwd",
            "avgpool_fwd", "avgpool_bwd", "nchw_to_nhwc16", "stem_im2col", "add16", "upsample2_zero",
-           "add_strided2", "conv_fprop", "conv_wgrad", "weight_dgrad_layout", "pad_rows16", "colsum16",
+           "add_strided2", "conv_fprop", "conv_wgrad", "weight_dgrad_layout", "weight_dgrad_layout_batched", "pad_rows16", "colsum16",
            "peer_copy", "peer_copy_", "reduce_to_root", "ConvShape"]
 
 _TAG = {torch.bfloat16: 0, torch.float16: 1}
@@ -210,6 +210,13 @@ def conv_wgrad(x, dy, dw, shape: ConvShape, *, ldx: int = 0, lddy: int = 0, ldw:
 def weight_dgrad_layout(w, wt, K, R, S, C) -> None:
     check(require().pdb_weight_dgrad_layout(ptr(w), ptr(wt), dtype_tag(w.dtype), K, R, S, C, _st(w)),
           "pdb_weight_dgrad_layout")
+    count_launch()
+
+
+def weight_dgrad_layout_batched(w_base, wt_base, table_dev, n: int) -> None:
+    check(require().pdb_weight_dgrad_layout_batched(ptr(w_base), ptr(wt_base), ptr(table_dev), n,
+                                                    dtype_tag(w_base.dtype), _st(w_base)),
+          "pdb_weight_dgrad_layout_batched")
     count_launch()
 
 
