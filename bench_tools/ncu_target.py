@@ -1,0 +1,70 @@
+"""Short single-GPU program for ncu captures: runs one kernel family a few times on a real ResNet-50 shape
+at batch 400.   python bench_tools/ncu_target.py {fprop|wgrad|bn|step}"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+from pytorch_distributed_b200 import ops  # noqa: E402
+from pytorch_distributed_b200.ops import ConvShape  # noqa: E402
+
+
+def main():
+    what = sys.argv[1] if len(sys.argv) > 1 else "fprop"
+    N, dt = 400, torch.bfloat16
+    if what in ("fprop", "wgrad"):
+        H, C, K, R = 14, 256, 256, 3
+        x = torch.randn(N, H, H, C, device="cuda", dtype=dt)
+        sh = ConvShape(N, H, H, C, K, R, R, 1, 1)
+        if what == "fprop":
+            w = torch.randn(K, R, R, C, device="cuda", dtype=dt) * 0.02
+            y = torch.empty(N, H, H, K, device="cuda", dtype=dt)
+            st = torch.zeros(2 * K, device="cuda")
+            for _ in range(6):
+                ops.conv_fprop(x, w, y, sh, stats=st)
+        else:
+            dy = torch.randn(N, H, H, K, device="cuda", dtype=dt)
+            dw = torch.zeros(K, R, R, C, device="cuda")
+            for _ in range(6):
+                ops.conv_wgrad(x, dy, dw, sh)
+    elif what == "bn":
+        rows, C = N * 56 * 56, 256
+        x = torch.randn(rows, C, device="cuda", dtype=dt)
+        z = torch.relu(x)
+        dz = torch.randn(rows, C, device="cuda", dtype=dt)
+        mean, rstd = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+        gamma = torch.ones(C, device="cuda")
+        ds = torch.zeros(2 * C, device="cuda")
+        dx, dres = torch.empty_like(x), torch.empty_like(x)
+        sums = torch.zeros(2 * C, device="cuda")
+        y = torch.empty_like(x)
+        for _ in range(4):
+            ops.bn_bwd_reduce(dz, z, x, mean, rstd, ds)
+            ops.bn_bwd_apply(dz, z, x, dx, dres, mean, rstd, gamma, ds, rows, None, None)
+            ops.bn_apply(x, z, y, sums + 1.0, rows, gamma, mean, 1e-5, 0.1, None, None, None, None, None, True)
+    else:
+        from pytorch_distributed_b200 import amp, harness
+        from pytorch_distributed_b200.config import TrainConfig
+        from pytorch_distributed_b200.nn import CrossEntropyLoss
+        from pytorch_distributed_b200.optim import SGD
+        dev = torch.device("cuda", 0)
+        cfg = TrainConfig(mode="ddp_amp", batch_size=N, dtype="bf16", device="cuda")
+        model = harness.build_model(cfg, dev)
+        model.enable_native(batch_size=N, dtype=dt)
+        opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+        sc = amp.GradScaler(device=dev)
+        crit = CrossEntropyLoss()
+        xb = torch.randn(N, 3, 224, 224, device=dev)
+        yb = torch.randint(0, 1000, (N,), device=dev)
+        model.train()
+        for _ in range(3):
+            harness.train_step(model, crit, opt, xb, yb, cfg, dev, sc, stock_autocast=False)
+    torch.cuda.synchronize()
+    print("ok", what)
+
+
+if __name__ == "__main__":
+    main()

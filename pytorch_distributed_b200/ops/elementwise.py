@@ -239,8 +239,9 @@ def _has(name: str) -> bool:
 
 def peer_copy_(dst: torch.Tensor, src: torch.Tensor) -> None:
     """dst (on its own GPU) pulls src's bytes over NVLink (K4a/K4b/K4c)."""
-    if not _has("pdb_peer_pull"):
-        dst.copy_(src, non_blocking=True)
+    nbytes = dst.numel() * dst.element_size()
+    if not _has("pdb_peer_pull") or nbytes % 16 or (dst.data_ptr() | src.data_ptr()) % 16:
+        dst.copy_(src, non_blocking=True)       # odd sizes (e.g. a handful of labels): plain copy engine
         return
     assert dst.is_contiguous() and src.is_contiguous() and dst.numel() * dst.element_size() == src.numel() * src.element_size()
     src_ev = torch.cuda.Event()

@@ -144,11 +144,10 @@ class DataParallel(nn.Module):
 
     # -- K4b: parameter + buffer broadcast --------------------------------------------------
     def _replicate(self, n: int) -> None:
-        src_p, src_f, src_i = self.arena.params, self.buffer_arena.floats, self.buffer_arena.ints
+        src_p, src_b = self.arena.params, self.buffer_arena.storage
         for a, b in zip(self._replica_arenas[1:n], self._replica_buffers[1:n]):
             _flat_copy(a.params, src_p)
-            _flat_copy(b.floats, src_f)
-            _flat_copy(b.ints, src_i)
+            _flat_copy(b.storage, src_b)          # fp32 statistics + int64 counters, one transfer
             a.grads.zero_()
             a.refresh_shadow()
 
