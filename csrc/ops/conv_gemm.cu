@@ -33,12 +33,32 @@ constexpr int kEpiThreads = 128;
 constexpr uint32_t A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KB
 constexpr uint32_t CHUNK_BYTES = 64 * 128;                  // 64 rows x 128 B = 8 KB (wgrad boxes)
 
+// Division by a runtime constant without the ~100-cycle integer divide: the TMA producer is ONE thread and
+// its address arithmetic sits on the critical path of every pipeline stage.  Valid for 0 <= n < 2^31.
+struct FastDiv {
+  uint32_t d, mul, shr;
+  __host__ void init(uint32_t div) {
+    d = div;
+    if (div <= 1) {
+      mul = 0, shr = 0;
+      return;
+    }
+    uint32_t l = 0;
+    while ((1u << l) < div) ++l;                 // ceil(log2(div))
+    const uint32_t p = 31 + l;
+    mul = (uint32_t)((((uint64_t)1 << p) + div - 1) / div);
+    shr = p - 32;
+  }
+  __device__ __forceinline__ uint32_t div(uint32_t n) const { return d <= 1 ? n : (__umulhi(n, mul) >> shr); }
+};
+
 struct FpropParams {
   int M, N;
   int num_m_blocks, num_n_blocks;
   int taps, cin_blocks, S;
   int P, Q, stride, pad;
   int a_im2col;
+  FastDiv div_pq, div_q;
   float* stats;        // [2N]: sum | sumsq, accumulated with atomics; may be null
   const float* bias;   // [N]; may be null
 };
@@ -119,26 +139,30 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int m_blk = tile % p.num_m_blocks, n_blk = tile / p.num_m_blocks;
         int base_w = 0, base_h = 0, n_img = 0;
         if (p.a_im2col) {
-          const int m0 = m_blk * BLOCK_M, pq = p.P * p.Q;
-          n_img = m0 / pq;
-          const int rem = m0 - n_img * pq;
-          const int pp = rem / p.Q, qq = rem - pp * p.Q;
+          const int m0 = m_blk * BLOCK_M;
+          n_img = (int)p.div_pq.div((uint32_t)m0);
+          const int rem = m0 - n_img * p.P * p.Q;
+          const int pp = (int)p.div_q.div((uint32_t)rem), qq = rem - pp * p.Q;
           base_w = qq * p.stride - p.pad;
           base_h = pp * p.stride - p.pad;
         }
+        // k-blocks in (tap, channel-block) order, walked with counters instead of div/mod
+        int r = 0, sx = 0, cb = 0;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(empty + stage, phase ^ 1);
           uint8_t* sA = smem + stage * L::STAGE_BYTES;
           uint8_t* sB = sA + A_STAGE_BYTES;
           mbar_arrive_expect_tx(full + stage, L::STAGE_BYTES);
           if (p.a_im2col) {
-            const int tap = kb / p.cin_blocks, cb = kb - tap * p.cin_blocks;
-            const int r = tap / p.S, s = tap - r * p.S;
-            tma_load_im2col_4d(sA, &tmA, full + stage, cb * BLOCK_K, base_w, base_h, n_img, (uint16_t)s, (uint16_t)r);
+            tma_load_im2col_4d(sA, &tmA, full + stage, cb * BLOCK_K, base_w, base_h, n_img, (uint16_t)sx, (uint16_t)r);
           } else {
             tma_load_2d(sA, &tmA, full + stage, kb * BLOCK_K, m_blk * BLOCK_M);
           }
           tma_load_2d(sB, &tmB, full + stage, kb * BLOCK_K, n_blk * BLOCK_N);
+          if (++cb == p.cin_blocks) {
+            cb = 0;
+            if (++sx == p.S) sx = 0, ++r;
+          }
           if (++stage == kStages) stage = 0, phase ^= 1;
         }
       }
@@ -287,6 +311,7 @@ struct WgradParams {
   int cin_blocks, S;        // 64-wide column chunk j -> tap = j / cin_blocks, c0 = (j % cin_blocks)*64
   int P, Q, stride, pad;
   int b_im2col;
+  FastDiv div_pq, div_q, div_cin;
   float* dw;
 };
 
@@ -349,6 +374,23 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
         const int m_blk = tile % p.num_m_blocks, n_blk = tile / p.num_m_blocks;
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.num_kb);
+        // the (tap, channel-block) of each 64-column chunk of this output tile is fixed for the whole item
+        int ch_c[BLOCK_N / 64], ch_s[BLOCK_N / 64], ch_r[BLOCK_N / 64];
+#pragma unroll
+        for (int j = 0; j < BLOCK_N / 64; ++j) {
+          const int chunk = n_blk * (BLOCK_N / 64) + j;            // global 64-column chunk index
+          if (p.b_im2col) {
+            const int tap = (int)p.div_cin.div((uint32_t)chunk);
+            const int cb = chunk - tap * p.cin_blocks;
+            const int r = tap / p.S;
+            // chunks past Ktot: channel coordinate past C -> zero fill (tap clamped to stay in range)
+            ch_c[j] = chunk * 64 < p.Ktot ? cb * 64 : (1 << 20);
+            ch_s[j] = tap - r * p.S;
+            ch_r[j] = min(r, 15);
+          } else {
+            ch_c[j] = chunk * 64, ch_s[j] = 0, ch_r[j] = 0;
+          }
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty + stage, phase ^ 1);
           uint8_t* sA = smem + stage * L::STAGE_BYTES;
@@ -358,28 +400,19 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
           // A: two boxes of [64 pixels][64 couts]; couts past Cout are zero-filled
           tma_load_2d(sA, &tmA, full + stage, m_blk * BLOCK_M, pix0);
           tma_load_2d(sA + CHUNK_BYTES, &tmA, full + stage, m_blk * BLOCK_M + 64, pix0);
-          int base_w = 0, base_h = 0, n_img = 0;
           if (p.b_im2col) {
-            const int pq = p.P * p.Q;
-            n_img = pix0 / pq;
-            const int rem = pix0 - n_img * pq;
-            const int pp = rem / p.Q, qq = rem - pp * p.Q;
-            base_w = qq * p.stride - p.pad;
-            base_h = pp * p.stride - p.pad;
-          }
+            const int n_img = (int)p.div_pq.div((uint32_t)pix0);
+            const int rem = pix0 - n_img * p.P * p.Q;
+            const int pp = (int)p.div_q.div((uint32_t)rem), qq = rem - pp * p.Q;
+            const int base_w = qq * p.stride - p.pad, base_h = pp * p.stride - p.pad;
 #pragma unroll
-          for (int j = 0; j < BLOCK_N / 64; ++j) {
-            const int chunk = n_blk * (BLOCK_N / 64) + j;          // global 64-column chunk index
-            if (p.b_im2col) {
-              int tap = chunk / p.cin_blocks;
-              const int cb = chunk - tap * p.cin_blocks;
-              const int r = tap / p.S, s = tap - r * p.S;
-              // chunks past Ktot: channel coordinate past C -> zero fill (tap clamped to stay in range)
-              tma_load_im2col_4d(sB + j * CHUNK_BYTES, &tmB, full + stage, chunk * 64 < p.Ktot ? cb * 64 : (1 << 20),
-                                 base_w, base_h, n_img, (uint16_t)s, (uint16_t)min(r, 15));
-            } else {
-              tma_load_2d(sB + j * CHUNK_BYTES, &tmB, full + stage, chunk * 64, pix0);
-            }
+            for (int j = 0; j < BLOCK_N / 64; ++j)
+              tma_load_im2col_4d(sB + j * CHUNK_BYTES, &tmB, full + stage, ch_c[j], base_w, base_h, n_img,
+                                 (uint16_t)ch_s[j], (uint16_t)ch_r[j]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BLOCK_N / 64; ++j)
+              tma_load_2d(sB + j * CHUNK_BYTES, &tmB, full + stage, ch_c[j], pix0);
           }
           if (++stage == kStages) stage = 0, phase ^= 1;
         }
@@ -593,6 +626,7 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
   p.taps = s->R * s->S, p.cin_blocks = (s->C + BLOCK_K - 1) / BLOCK_K, p.S = s->S;
   p.P = P, p.Q = Q, p.stride = s->stride, p.pad = s->pad;
   p.a_im2col = plain ? 0 : 1;
+  p.div_pq.init((uint32_t)(P * Q)), p.div_q.init((uint32_t)Q);
   p.stats = stats, p.bias = bias;
 
   CUtensorMap tmA, tmB, tmD;
@@ -654,6 +688,7 @@ extern "C" int pdb_conv_wgrad(const void* x, const void* dy, float* dw, int dtyp
   p.cin_blocks = (s->C + 63) / 64, p.S = s->S;
   p.P = P, p.Q = Q, p.stride = s->stride, p.pad = s->pad;
   p.b_im2col = plain ? 0 : 1;
+  p.div_pq.init((uint32_t)(P * Q)), p.div_q.init((uint32_t)Q), p.div_cin.init((uint32_t)p.cin_blocks);
   p.dw = dw;
 
   CUtensorMap tmA, tmB;
