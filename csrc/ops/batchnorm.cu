@@ -10,6 +10,7 @@
 //             branch gradient and the dgamma/dbeta accumulation.
 // Layout [rows, C] with C contiguous: a thread owns 8 consecutive channels (one 128-bit access).
 #include "common.cuh"
+#include "bn_fast.cuh"
 
 namespace pdb {
 
@@ -427,9 +428,26 @@ extern "C" int pdb_bn_apply(const void* x, const void* residual, void* y, int dt
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0 && count > 0, "pdb_bn_apply: bad shape rows=%lld C=%d",
                 (long long)rows, C);
   const int64_t nvec = rows * C / 8;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (bn_fast_ok(C)) {
+    const int fgrid = bn_fast_grid(nvec, kFastU);
+    const float inv_count = (float)(1.0 / count), unbias = (float)(count > 1.0 ? count / (count - 1.0) : 1.0);
+#define FAST(RES, RELU)                                                                                            \
+  bn_apply_fast_kernel<T, RES, RELU><<<fgrid, kFastThreads, 0, st>>>(                                              \
+      (const T*)x, (const T*)residual, (T*)y, nvec, C, sums, inv_count, unbias, gamma, beta, eps, momentum,        \
+      running_mean, running_var, num_batches_tracked, save_mean, save_rstd)
+    PDB_DISPATCH_16(dtype, T, {
+      if (residual && relu) FAST(true, true);
+      else if (residual) FAST(true, false);
+      else if (relu) FAST(false, true);
+      else FAST(false, false);
+    });
+#undef FAST
+    PDB_LAUNCH_CHECK();
+    return 0;
+  }
   const int grid = ew_grid(nvec);
   const size_t smem = 2 * (size_t)C * sizeof(float);
-  cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH(RES, RELU)                                                                                         \
   bn_apply_kernel<T, RES, RELU><<<grid, kThreads, smem, st>>>((const T*)x, (const T*)residual, (T*)y, nvec, C, sums, \
                                                               count, gamma, beta, eps, momentum, running_mean,    \
@@ -451,9 +469,24 @@ extern "C" int pdb_bn_apply_eval(const void* x, const void* residual, void* y, i
   PDB_CHECK_ARG(x && y && running_mean && running_var && gamma && beta, "pdb_bn_apply_eval: null pointer");
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_apply_eval: bad shape");
   const int64_t nvec = rows * C / 8;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (bn_fast_ok(C)) {
+    const int fgrid = bn_fast_grid(nvec, kFastU);
+#define FAST(RES, RELU)                                                                                     \
+  bn_apply_eval_fast_kernel<T, RES, RELU><<<fgrid, kFastThreads, 0, st>>>(                                  \
+      (const T*)x, (const T*)residual, (T*)y, nvec, C, running_mean, running_var, gamma, beta, eps)
+    PDB_DISPATCH_16(dtype, T, {
+      if (residual && relu) FAST(true, true);
+      else if (residual) FAST(true, false);
+      else if (relu) FAST(false, true);
+      else FAST(false, false);
+    });
+#undef FAST
+    PDB_LAUNCH_CHECK();
+    return 0;
+  }
   const int grid = ew_grid(nvec);
   const size_t smem = 2 * (size_t)C * sizeof(float);
-  cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH(RES, RELU)                                                                                    \
   bn_apply_eval_kernel<T, RES, RELU><<<grid, kThreads, smem, st>>>((const T*)x, (const T*)residual, (T*)y, nvec, C, \
                                                                    running_mean, running_var, gamma, beta, eps)
@@ -474,9 +507,26 @@ extern "C" int pdb_bn_bwd_apply(const void* dz, const void* z, const void* x, vo
   PDB_CHECK_ARG(dz && x && dx && mean && rstd && gamma && dsums, "pdb_bn_bwd_apply: null pointer");
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0 && count > 0, "pdb_bn_bwd_apply: bad shape");
   const int64_t nvec = rows * C / 8;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (bn_fast_ok(C)) {
+    const int fgrid = bn_fast_grid(nvec, kFastUBwd);
+    const float inv_count = (float)(1.0 / count);
+#define FAST(HZ, DR)                                                                                              \
+  bn_bwd_apply_fast_kernel<T, HZ, DR><<<fgrid, kFastThreads, 0, st>>>(                                            \
+      (const T*)dz, (const T*)z, (const T*)x, (T*)dx, (T*)dres, nvec, C, mean, rstd, gamma, dsums, inv_count,     \
+      dgamma, dbeta)
+    PDB_DISPATCH_16(dtype, T, {
+      if (z && dres) FAST(true, true);
+      else if (z) FAST(true, false);
+      else if (dres) FAST(false, true);
+      else FAST(false, false);
+    });
+#undef FAST
+    PDB_LAUNCH_CHECK();
+    return 0;
+  }
   const int grid = ew_grid(nvec);
   const size_t smem = 3 * (size_t)C * sizeof(float);
-  cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH(HZ, DR)                                                                                              \
   bn_bwd_apply_kernel<T, HZ, DR><<<grid, kThreads, smem, st>>>((const T*)dz, (const T*)z, (const T*)x, (T*)dx,     \
                                                                (T*)dres, nvec, C, mean, rstd, gamma, dsums, count, \

@@ -173,11 +173,21 @@ __global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restric
 template <typename T>
 __global__ void __launch_bounds__(256) add16_kernel(const T* __restrict__ a, const T* __restrict__ b,
                                                     T* __restrict__ o, int64_t nvec) {
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+  constexpr int U = 8;          // one tile per block (see bn_fast.cuh for the measurement behind this shape)
+  const int64_t base = (int64_t)blockIdx.x * (256 * U) + threadIdx.x;
+  uint4 va[U], vb[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int64_t i = base + (int64_t)u * 256;
+    if (i < nvec) va[u] = ldg128_stream(a + i * 8), vb[u] = ldg128_stream(b + i * 8);
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int64_t i = base + (int64_t)u * 256;
+    if (i >= nvec) continue;
     float fa[8], fb[8];
-    unpack8<T>(ldg128_stream(a + i * 8), fa);
-    unpack8<T>(ldg128_stream(b + i * 8), fb);
+    unpack8<T>(va[u], fa);
+    unpack8<T>(vb[u], fb);
 #pragma unroll
     for (int k = 0; k < 8; ++k) fa[k] += fb[k];
     stg128(o + i * 8, pack8<T>(fa));
@@ -289,7 +299,7 @@ extern "C" int pdb_stem_im2col(const float* x, void* col, int dtype, int N, int 
 
 extern "C" int pdb_add16(const void* a, const void* b, void* out, int dtype, int64_t n, void* stream) {
   PDB_CHECK_ARG(a && b && out && n > 0 && n % 8 == 0, "pdb_add16: bad arguments");
-  PDB_DISPATCH_16(dtype, T, (add16_kernel<T><<<ew_grid(n / 8), 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out, n / 8)));
+  PDB_DISPATCH_16(dtype, T, (add16_kernel<T><<<(int)((n / 8 + 2047) / 2048), 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out, n / 8)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
