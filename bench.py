@@ -32,7 +32,7 @@ ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
 # Derived from the reference's chart: train img/s per GPU.
-PUBLISHED_PER_GPU = {"ddp_amp": 693.3, "ddp": 669.0, "single": 717.0}
+PUBLISHED_PER_GPU = {"ddp_amp": 693.3, "ddp": 669.0, "single": 717.0, "dp": 162.7}
 
 
 # ------------------------------------------------------------------------------------ clocks
@@ -92,6 +92,10 @@ def dist_setup(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.mode == "dp":                      # single process drives every GPU (ref:resnet_dp.py)
+        torch.cuda.set_device(0)
+        args.gpus = min(args.gpus, torch.cuda.device_count())
+        return 1, 0, 0
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             raise SystemExit("--gpus N>1 must be launched with python -m torch.distributed.run --nproc-per-node N")
@@ -201,8 +205,12 @@ def run_ours(args):
         model.enable_native(batch_size=args.batch,
                             dtype=torch.bfloat16 if cfg.resolved_dtype() == "bf16" else torch.float16,
                             sync_bn=args.sync_bn)
+    ndp = args.gpus if args.mode == "dp" else 1
     if args.mode in ("ddp", "ddp_amp"):
         wrapped = DistributedDataParallel(model, device_ids=[local], backend=args.backend)
+    elif args.mode == "dp":
+        from pytorch_distributed_b200.parallel import DataParallel
+        wrapped = DataParallel(model, device_ids=list(range(ndp)), output_device=0)
     else:
         harness.ensure_arenas(model, device)
         wrapped = model
@@ -216,7 +224,7 @@ def run_ours(args):
     stock_autocast = not native
     wrapped.train()
 
-    x, y = synthetic_device_batch(args.batch, device, 1000 + rank)
+    x, y = synthetic_device_batch(args.batch * ndp, device, 1000 + rank)
 
     def step(_i):
         harness.train_step(wrapped, criterion, optimizer, x, y, cfg, device, scaler, stock_autocast)
@@ -231,7 +239,7 @@ def run_ours(args):
     launches = (ops.launch_count() - l0) if ops.available() else 0
 
     # ---- end to end through the public harness loop: pinned host batch -> H2D, loss -> D2H, each step
-    ring = PinnedRing(args.batch, args.warmup + args.steps, seed=rank)
+    ring = PinnedRing(args.batch * ndp, args.warmup + args.steps, seed=rank)
     losses = []
 
     class _E2E:
@@ -263,6 +271,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
     clocks = sampler.stop() if rank == 0 else {}
+    world = world * ndp                        # GPUs doing the work (DP mode: one process, ndp devices)
     e2e = {"value": round(args.batch * world * args.steps / (e2e_ms / 1e3), 2), "unit": "images/s",
            "ms_per_step": round(e2e_ms / args.steps, 3), "h2d_bytes_per_step": ring.bytes_per_step(),
            "d2h_bytes_per_step": 4, "api": "pytorch_distributed_b200.harness.train", "last_loss": losses[-1]}
@@ -277,7 +286,7 @@ def run_ours(args):
 # ------------------------------------------------------------------------------------ reference
 def run_reference(args):
     ref_dir = ROOT / "baseline" / "_ref"
-    script = {"ddp_amp": "resnet_ddp_apex", "ddp": "restnet_ddp", "single": "resnet_single_gpu"}[args.mode]
+    script = {"ddp_amp": "resnet_ddp_apex", "ddp": "restnet_ddp", "single": "resnet_single_gpu", "dp": "resnet_dp"}[args.mode]
     if not (ref_dir / f"{script}.py").exists():
         print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref missing: the reference has no "
                           "setup.py/pyproject (pip install fails); run python baseline/install_ref.py"}))
@@ -304,9 +313,12 @@ def run_reference(args):
 
     torch.manual_seed(rank)
     model = models.resnet50().cuda()
+    ndp = args.gpus if args.mode == "dp" else 1
     if args.mode in ("ddp", "ddp_amp"):
         kw = {} if args.mode == "ddp_amp" else {"device_ids": [local]}      # as in the two scripts
         model = torch.nn.parallel.DistributedDataParallel(model, **kw)
+    elif args.mode == "dp":
+        model = nn.DataParallel(model, device_ids=list(range(ndp)), output_device=0)     # ref:resnet_dp.py:82
     criterion = nn.CrossEntropyLoss()
     optimizer = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
     scheduler = StepLR(optimizer, step_size=30, gamma=0.1)
@@ -318,27 +330,30 @@ def run_reference(args):
             ref.train(loader, model, criterion, optimizer, scheduler, scaler, 0, local, 0, 0.0, save)
         elif args.mode == "ddp":
             ref.train(loader, model, criterion, optimizer, scheduler, 0, local, 0, 0.0, save)
+        elif args.mode == "dp":
+            ref.train(loader, model, criterion, optimizer, scheduler, 0, 0, 0.0, save)
         else:
             import contextlib
             import io
             with contextlib.redirect_stdout(io.StringIO()):          # its step ticker
                 ref.train(loader, model, criterion, optimizer, scheduler, 0, 0, 0.0, save)
 
-    x, y = synthetic_device_batch(args.batch, device, 1000 + rank)
+    x, y = synthetic_device_batch(args.batch * ndp, device, 1000 + rank)
     call_train([(x, y)] * args.warmup)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     ms = timed_region(lambda i: call_train([(x, y)]), args.steps, device)
-    ring = PinnedRing(args.batch, args.steps, seed=rank)
+    ring = PinnedRing(args.batch * ndp, args.steps, seed=rank)
     call_train(list(ring)[:2])
+    world = world * ndp
     e2e_ms = timed_region(lambda i: call_train([ring.items[i % len(ring.items)]]), args.steps, device)
     clocks = sampler.stop() if rank == 0 else {}
     e2e = {"value": round(args.batch * world * args.steps / (e2e_ms / 1e3), 2), "unit": "images/s",
            "ms_per_step": round(e2e_ms / args.steps, 3), "h2d_bytes_per_step": ring.bytes_per_step(),
            "d2h_bytes_per_step": 0, "api": f"baseline/_ref/{script}.py::train (unmodified)"}
     if rank == 0:
-        args.dtype = {"ddp_amp": "fp16-autocast", "ddp": "fp32(tf32 conv)", "single": "fp32(tf32 conv)"}[args.mode]
+        args.dtype = {"ddp_amp": "fp16-autocast", "ddp": "fp32(tf32 conv)", "single": "fp32(tf32 conv)", "dp": "fp32(tf32 conv)"}[args.mode]
         emit(args, world, ms, e2e, clocks, None,
              {"engine": "stock torch + cuDNN + NCCL", "cudnn_allow_tf32": torch.backends.cudnn.allow_tf32,
               "per_step_empty_cache": args.mode != "single"}, "reference")
@@ -353,7 +368,7 @@ def main():
     p.add_argument("--steps", type=int, default=20)
     p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--impl", choices=("ours", "reference"), default="ours")
-    p.add_argument("--mode", choices=("ddp_amp", "ddp", "single"), default="ddp_amp")
+    p.add_argument("--mode", choices=("ddp_amp", "ddp", "single", "dp"), default="ddp_amp")
     p.add_argument("--batch", type=int, default=400)
     p.add_argument("--dtype", choices=("bf16", "fp16", "fp32"), default="bf16")
     p.add_argument("--engine", choices=("auto", "native", "torch"), default="auto")
