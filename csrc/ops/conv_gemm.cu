@@ -571,11 +571,15 @@ static int set_smem(K kernel, uint32_t bytes) {
 template <int BLOCK_N, bool kBf16>
 static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const FpropParams& p,
                         cudaStream_t st) {
-  static bool configured = false;
+  // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute (the single-process
+  // DataParallel mode launches from one process on every GPU)
+  static bool configured[64] = {};
   auto kernel = conv_fprop_kernel<BLOCK_N, kBf16>;
-  if (!configured) {
+  int dev = 0;
+  PDB_CUDA(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
     if (int e = set_smem(kernel, FpropSmem<BLOCK_N>::TOTAL)) return e;
-    configured = true;
+    configured[dev & 63] = true;
   }
   const int tiles = p.num_m_blocks * p.num_n_blocks;
   const int grid = tiles < num_sms() ? tiles : num_sms();
@@ -586,11 +590,13 @@ static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtens
 
 template <int BLOCK_N, bool kBf16>
 static int launch_wgrad(const CUtensorMap& a, const CUtensorMap& b, const WgradParams& p, cudaStream_t st) {
-  static bool configured = false;
+  static bool configured[64] = {};
   auto kernel = conv_wgrad_kernel<BLOCK_N, kBf16>;
-  if (!configured) {
+  int dev = 0;
+  PDB_CUDA(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
     if (int e = set_smem(kernel, WgradSmem<BLOCK_N>::TOTAL)) return e;
-    configured = true;
+    configured[dev & 63] = true;
   }
   const int items = p.num_m_blocks * p.num_n_blocks * p.num_splits;
   const int grid = items < num_sms() ? items : num_sms();
