@@ -17,46 +17,9 @@
 // CAS at system scope (the protocol of torch's CUDASymmetricMemory sync_remote_blocks, re-implemented).
 // Every spin is bounded by the global timer and traps instead of hanging the box.
 #include "common.cuh"
+#include "comm/peer_sync.cuh"
 
 namespace pdb {
-
-constexpr int kMaxWorld = 16;
-constexpr int kCommThreads = 512;
-constexpr unsigned long long kSpinTimeoutNs = 20ull * 1000 * 1000 * 1000;     // 20 s
-
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
-
-__device__ __forceinline__ uint32_t cas_release_sys(uint32_t* addr, uint32_t cmp, uint32_t val) {
-  uint32_t old;
-  asm volatile("atom.global.release.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
-  return old;
-}
-__device__ __forceinline__ uint32_t cas_acquire_sys(uint32_t* addr, uint32_t cmp, uint32_t val) {
-  uint32_t old;
-  asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(addr), "r"(cmp), "r"(val) : "memory");
-  return old;
-}
-
-// Block-level barrier across ranks: block b of every rank meets block b of every other rank.
-// Slot layout in each rank's pad: pad[b * world + src_rank].
-__device__ __forceinline__ void cross_rank_barrier(uint32_t* const* pads, int rank, int world) {
-  __syncthreads();
-  if (threadIdx.x < world && (int)threadIdx.x != rank) {
-    const int peer = threadIdx.x;
-    uint32_t* remote = pads[peer] + blockIdx.x * world + rank;        // my flag in the peer's pad
-    uint32_t* local = pads[rank] + blockIdx.x * world + peer;         // the peer's flag in my pad
-    const unsigned long long t0 = globaltimer_ns();
-    while (cas_release_sys(remote, 0u, 1u) != 0u)
-      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
-    while (cas_acquire_sys(local, 1u, 0u) != 1u)
-      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
-  }
-  __syncthreads();
-}
 
 struct PeerPtrs {
   float* buf[kMaxWorld];
@@ -162,6 +125,99 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_kernel(PeerPtrs pp, fl
   }
   __threadfence_system();
   cross_rank_barrier(pp.pad, rank, world);            // all shards have landed everywhere
+}
+
+// ---- 16-bit wire variant (fp16_compress / bf16_compress hooks, default_comm_hooks.hpp:9-34) -------------------
+// Gradients stay fp32 in the arena; only what crosses NVLink is 16-bit:
+//   pack own range -> S (x 1/world, like the hook's div)  | barrier |  rank r: sum shard r of every S in fp32,
+//   x 1/loss_scale, non-finite check, store 16-bit into every R  | barrier |  unpack R -> fp32 gradients.
+// S and R are the two halves of a symmetric staging buffer (elements of W, `half_elems` each).
+struct PeerPtrs16 {
+  void* stage[kMaxWorld];
+};
+
+template <typename W>
+__global__ void __launch_bounds__(kCommThreads) allreduce_wire16_kernel(PeerPtrs pp, PeerPtrs16 st, int rank, int world,
+                                                                        int64_t start, int64_t n, int64_t half_elems,
+                                                                        float pre_scale,
+                                                                        const float* __restrict__ inv_scale) {
+  const int64_t n8 = n / 8;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  float* grads = pp.buf[rank] + start;
+  W* S_own = static_cast<W*>(st.stage[rank]);
+  W* R_own = S_own + half_elems;
+  for (int64_t i = tid; i < n8; i += nth) {            // phase 1: pack (local)
+    const float4 a = reinterpret_cast<const float4*>(grads)[2 * i], b = reinterpret_cast<const float4*>(grads)[2 * i + 1];
+    float f[8] = {a.x * pre_scale, a.y * pre_scale, a.z * pre_scale, a.w * pre_scale,
+                  b.x * pre_scale, b.y * pre_scale, b.z * pre_scale, b.w * pre_scale};
+    reinterpret_cast<uint4*>(S_own)[i] = pack8<W>(f);
+  }
+  __threadfence_system();
+  cross_rank_barrier(pp.pad, rank, world);
+  const float s = inv_scale ? *inv_scale : 1.0f;
+  const int64_t per = (n8 + world - 1) / world;
+  const int64_t lo = min(per * rank, n8), hi = min(lo + per, n8);
+  bool bad = false;
+  constexpr int kUnroll = 4;
+  const int64_t tile = (int64_t)blockDim.x * kUnroll;
+  for (int64_t base = lo + (int64_t)blockIdx.x * tile; base < hi; base += (int64_t)gridDim.x * tile) {
+    float acc[kUnroll][8];
+    bool live[kUnroll];
+    int64_t idx[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      idx[u] = base + (int64_t)u * blockDim.x + threadIdx.x;
+      live[u] = idx[u] < hi;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[u][k] = 0.f;
+    }
+#pragma unroll 1
+    for (int kk = 0; kk < world; ++kk) {
+      const int p = rank + kk < world ? rank + kk : rank + kk - world;
+      const uint4* src = static_cast<const uint4*>(st.stage[p]);
+      uint4 v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u)
+        if (live[u])
+          asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + idx[u]));
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        if (!live[u]) continue;
+        float f[8];
+        unpack8<W>(v[u], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[u][k] += f[k];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      if (!live[u]) continue;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        acc[u][k] *= s;
+        bad |= !isfinite(acc[u][k]);
+      }
+      const uint4 w = pack8<W>(acc[u]);
+#pragma unroll 1
+      for (int kk = 0; kk < world; ++kk) {
+        const int p = rank + kk < world ? rank + kk : rank + kk - world;
+        uint4* dst = reinterpret_cast<uint4*>(static_cast<W*>(st.stage[p]) + half_elems) + idx[u];
+        asm volatile("st.global.cg.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(w.x), "r"(w.y), "r"(w.z), "r"(w.w) : "memory");
+      }
+    }
+  }
+  if (pp.flag[0] != nullptr && __syncthreads_or(bad) && threadIdx.x < world)
+    *reinterpret_cast<volatile float*>(pp.flag[threadIdx.x]) = 1.0f;
+  __threadfence_system();
+  cross_rank_barrier(pp.pad, rank, world);
+  for (int64_t i = tid; i < n8; i += nth) {            // phase 3: unpack (local; R was written by the shard owners)
+    uint4 v;
+    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(reinterpret_cast<const uint4*>(R_own) + i));
+    float f[8];
+    unpack8<W>(v, f);
+    reinterpret_cast<float4*>(grads)[2 * i] = make_float4(f[0], f[1], f[2], f[3]);
+    reinterpret_cast<float4*>(grads)[2 * i + 1] = make_float4(f[4], f[5], f[6], f[7]);
+  }
 }
 
 // Broadcast of [start, start+n) from `root` to every rank: non-root ranks pull over NVLink.
@@ -284,6 +340,27 @@ extern "C" int pdb_allreduce_inplace(void* const* bufs, void* const* pads, void*
     allreduce_kernel<true><<<blocks, kCommThreads, 0, st>>>(pp, static_cast<float*>(multicast), rank, world, start, n, scale, inv_scale);
   else
     allreduce_kernel<false><<<blocks, kCommThreads, 0, st>>>(pp, nullptr, rank, world, start, n, scale, inv_scale);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_allreduce_inplace_wire16(void* const* bufs, void* const* pads, void* const* flags, void* const* staging,
+                                            int64_t staging_half_elems, int wire_dtype, int rank, int world,
+                                            int64_t start, int64_t n, float pre_scale, const float* inv_scale,
+                                            int blocks, void* stream) {
+  PDB_CHECK_ARG(bufs && pads && staging && n >= 0 && start >= 0, "pdb_allreduce_inplace_wire16: bad arguments");
+  PDB_CHECK_ARG(n % 8 == 0 && start % 4 == 0, "pdb_allreduce_inplace_wire16: n must be a multiple of 8, start of 4");
+  PDB_CHECK_ARG(n <= staging_half_elems, "pdb_allreduce_inplace_wire16: range (%lld) exceeds the staging half (%lld)",
+                (long long)n, (long long)staging_half_elems);
+  PDB_CHECK_ARG(rank >= 0 && rank < world && blocks >= 1 && blocks <= 64, "pdb_allreduce_inplace_wire16: bad rank/blocks");
+  if (n == 0) return 0;
+  PeerPtrs pp;
+  if (int e = fill_peers(&pp, bufs, pads, flags, world)) return e;
+  PeerPtrs16 st16;
+  for (int i = 0; i < kMaxWorld; ++i) st16.stage[i] = i < world ? staging[i] : nullptr;
+  cudaStream_t st = (cudaStream_t)stream;
+  PDB_DISPATCH_16(wire_dtype, W, (allreduce_wire16_kernel<W><<<blocks, kCommThreads, 0, st>>>(
+                                     pp, st16, rank, world, start, n, staging_half_elems, pre_scale, inv_scale)));
   PDB_LAUNCH_CHECK();
   return 0;
 }

@@ -11,6 +11,7 @@
 // Layout [rows, C] with C contiguous: a thread owns 8 consecutive channels (one 128-bit access).
 #include "common.cuh"
 #include "bn_fast.cuh"
+#include "comm/peer_sync.cuh"
 
 namespace pdb {
 
@@ -145,6 +146,85 @@ __global__ void __launch_bounds__(kThreads) bn_stats_kernel(const T* __restrict_
       sums[c] = acc;
     }
     if (threadIdx.x == 0) scratch->ticket = 0;     // ready for the next launch on this scratch
+  }
+}
+
+// K6: SyncBatchNorm statistics with the cross-GPU reduction INSIDE the statistics kernel.  The delegate runs
+// batch_norm_stats -> all_gather (NCCL) -> batch_norm_gather_stats_with_counts, three launches and a library
+// collective per BN layer and direction (torch:nn/modules/_functions.py:7-124).  Here the block that folds
+// the per-block partials also pushes the [2C] sums into slot `rank` of every peer's symmetric staging
+// buffer (P2P stores over NVLink), meets the peers on the signal pad, and adds up the `world` slots — the
+// kernel returns global sums, no collective call.
+struct SyncPeers {
+  float* staging[kMaxWorld];      // float[world][slot_stride] per rank
+  uint32_t* pad[kMaxWorld];
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) bn_stats_sync_kernel(const T* __restrict__ x, int64_t rows, int C, int cx,
+                                                                 int ry, float* __restrict__ sums,
+                                                                 StatsScratch* __restrict__ scratch, SyncPeers sp,
+                                                                 int rank, int world, int slot_stride) {
+  extern __shared__ float smem[];
+  __shared__ bool is_last;
+  const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
+  float* partial = reinterpret_cast<float*>(scratch + 1) + (size_t)blockIdx.x * 2 * C;
+  const int ncg = C / 8;
+  for (int cg = tx; cg < ncg; cg += cx) {
+    float s0[8] = {0}, s1[8] = {0};
+    if (ty < ry) reduce_rows<T, 0, false>(x, nullptr, nullptr, rows, C, cg, cx, ry, ty, nullptr, nullptr, s0, s1);
+    block_fold(s0, s1, tx, ty, cx, ry, smem);
+    if (ty == 0) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        partial[cg * 8 + k] = s0[k];
+        partial[C + cg * 8 + k] = s1[k];
+      }
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(&scratch->ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  const float* all = reinterpret_cast<const float*>(scratch + 1);
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
+    float acc = 0.f;
+    for (unsigned b = 0; b < gridDim.x; ++b) acc += __ldcg(all + (size_t)b * 2 * C + c);
+    for (int p = 0; p < world; ++p) sp.staging[p][(int64_t)rank * slot_stride + c] = acc;      // push to every rank
+  }
+  if (threadIdx.x == 0) scratch->ticket = 0;
+  __threadfence_system();
+  // one block per rank takes part: it uses signal-pad row 0 of the (dedicated) staging allocation
+  __syncthreads();
+  if (threadIdx.x < world && (int)threadIdx.x != rank) {
+    const int peer = threadIdx.x;
+    uint32_t* remote = sp.pad[peer] + rank;
+    uint32_t* local = sp.pad[rank] + peer;
+    const unsigned long long t0 = globaltimer_ns();
+    while (cas_release_sys(remote, 0u, 1u) != 0u)
+      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
+    while (cas_acquire_sys(local, 1u, 0u) != 1u)
+      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
+    float acc = 0.f;
+    for (int p = 0; p < world; ++p) acc += __ldcg(sp.staging[rank] + (int64_t)p * slot_stride + c);
+    sums[c] = acc;
+  }
+  // second meeting: nobody may overwrite a slot (next layer) before every rank has read it
+  __syncthreads();
+  if (threadIdx.x < world && (int)threadIdx.x != rank) {
+    const int peer = threadIdx.x;
+    uint32_t* remote = sp.pad[peer] + rank;
+    uint32_t* local = sp.pad[rank] + peer;
+    const unsigned long long t0 = globaltimer_ns();
+    while (cas_release_sys(remote, 0u, 1u) != 0u)
+      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
+    while (cas_acquire_sys(local, 1u, 0u) != 1u)
+      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
   }
 }
 
@@ -394,6 +474,30 @@ extern "C" int pdb_bn_stats(const void* x, int dtype, int64_t rows, int C, float
   const size_t smem = (size_t)kThreads * 16 * sizeof(float);
   PDB_DISPATCH_16(dtype, T, (bn_stats_kernel<T><<<grid, kThreads, smem, (cudaStream_t)stream>>>(
                                 (const T*)x, rows, C, cx, ry, sums, (StatsScratch*)scratch)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_bn_stats_sync(const void* x, int dtype, int64_t rows, int C, float* sums, void* scratch,
+                                 size_t scratch_bytes, void* const* staging, void* const* pads, int rank, int world,
+                                 int slot_stride, void* stream) {
+  PDB_CHECK_ARG(x && sums && scratch && staging && pads, "pdb_bn_stats_sync: null pointer");
+  PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_stats_sync: bad shape rows=%lld C=%d", (long long)rows, C);
+  PDB_CHECK_ARG(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "pdb_bn_stats_sync: bad rank/world");
+  PDB_CHECK_ARG(2 * C <= slot_stride, "pdb_bn_stats_sync: 2C=%d exceeds the staging slot (%d floats)", 2 * C, slot_stride);
+  int cx, ry;
+  reduce_geometry(C, &cx, &ry);
+  const int grid = reduce_grid(rows, ry);
+  const size_t need = sizeof(StatsScratch) + (size_t)grid * 2 * C * sizeof(float);
+  PDB_CHECK_ARG(scratch_bytes >= need && ((uintptr_t)scratch) % 256 == 0, "pdb_bn_stats_sync: scratch too small or misaligned");
+  SyncPeers sp;
+  for (int i = 0; i < kMaxWorld; ++i) {
+    sp.staging[i] = i < world ? static_cast<float*>(staging[i]) : nullptr;
+    sp.pad[i] = i < world ? static_cast<uint32_t*>(pads[i]) : nullptr;
+  }
+  const size_t smem = (size_t)kThreads * 16 * sizeof(float);
+  PDB_DISPATCH_16(dtype, T, (bn_stats_sync_kernel<T><<<grid, kThreads, smem, (cudaStream_t)stream>>>(
+                                (const T*)x, rows, C, cx, ry, sums, (StatsScratch*)scratch, sp, rank, world, slot_stride)));
   PDB_LAUNCH_CHECK();
   return 0;
 }

@@ -71,6 +71,14 @@ size_t pdb_bn_stats_scratch_bytes(int C);
 int pdb_bn_stats(const void* x, int dtype, int64_t rows, int C, float* sums, void* scratch,
                  size_t scratch_bytes, void* stream);
 
+/* K6 — SyncBatchNorm statistics (torch:nn/modules/_functions.py:7-124): pdb_bn_stats with the cross-GPU
+ * reduction inside the kernel.  The block that folds the partials pushes the [2C] sums into slot `rank` of
+ * every peer's symmetric staging buffer (float[world][slot_stride], P2P stores), meets the peers on the
+ * staging allocation's signal pad and adds the `world` slots: `sums` comes back global.  One rank per GPU. */
+int pdb_bn_stats_sync(const void* x, int dtype, int64_t rows, int C, float* sums, void* scratch,
+                      size_t scratch_bytes, void* const* staging, void* const* pads, int rank, int world,
+                      int slot_stride, void* stream);
+
 /* Same result as pdb_bn_stats for callers that cannot obtain device memory for the scratch buffer
  * (hosts whose GPU memory is fully committed to their own pools, code in the middle of a step where
  * cudaMalloc/cudaFree would synchronise the device, embedders that may not call the CUDA allocator).
@@ -184,6 +192,15 @@ int pdb_comm_max_blocks(int world, size_t signal_pad_bytes);
 int pdb_allreduce_inplace(void* const* bufs, void* const* pads, void* const* flags, void* multicast, int rank,
                           int world, int64_t start, int64_t n, float scale, const float* inv_scale, int blocks,
                           void* stream);
+/* K1 with a 16-bit wire format (the fp16_compress / bf16_compress comm hooks, torch:distributed/
+ * algorithms/ddp_comm_hooks/default_hooks.py:57-134): gradients stay fp32 in the arena, each rank packs
+ * its range (x pre_scale = 1/world) into the first half of a symmetric 16-bit staging buffer, shard owners
+ * sum the peers' packed data in fp32, apply *inv_scale and the non-finite check, store the 16-bit result
+ * into the second half of every rank's staging buffer, and every rank unpacks it back to fp32.
+ * staging[r] holds 2 * staging_half_elems 16-bit elements. */
+int pdb_allreduce_inplace_wire16(void* const* bufs, void* const* pads, void* const* flags, void* const* staging,
+                                 int64_t staging_half_elems, int wire_dtype, int rank, int world, int64_t start,
+                                 int64_t n, float pre_scale, const float* inv_scale, int blocks, void* stream);
 /* K2/K3 (DDP _sync_module_states / per-iteration buffer broadcast): every rank != root pulls
  * [start, start+n) from root's buffer. */
 int pdb_broadcast_inplace(void* const* bufs, void* const* pads, int rank, int world, int root, int64_t start,

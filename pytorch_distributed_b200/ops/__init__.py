@@ -8,3 +8,4 @@ from __future__ import annotations
 
 from ._lib import available, launch_count, lib, require  # noqa: F401
 from .elementwise import *  # noqa: F401,F403
+from . import elementwise  # noqa: E402,F401

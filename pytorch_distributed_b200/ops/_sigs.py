@@ -51,6 +51,8 @@ def declare(L):
 
 OPTIONAL = {
     "pdb_allreduce_inplace": [P, P, P, P, c_int, c_int, c_int64, c_int64, c_float, P, c_int, P],
+    "pdb_allreduce_inplace_wire16": [P, P, P, P, c_int64, c_int, c_int, c_int, c_int64, c_int64, c_float, P, c_int, P],
+    "pdb_bn_stats_sync": [P, c_int, c_int64, c_int, P, P, c_size_t, P, P, c_int, c_int, c_int, P],
     "pdb_broadcast_inplace": [P, P, c_int, c_int, c_int, c_int64, c_int64, c_int, P],
     "pdb_small_allreduce": [P, P, c_int, c_int, P, c_int, c_int, P],
     "pdb_peer_pull": [P, P, c_int64, P],

@@ -67,6 +67,7 @@ class NativeComm:
         self._staging_ptrs = (ctypes.c_void_p * self.world)(*[p + 64 * 4 for p in fl])
         self.use_multicast = os.environ.get("PDB200_NVLS", "1") != "0"
         self.blocks = int(os.environ.get("PDB200_COMM_BLOCKS", "32"))
+        self._wire: Dict[torch.dtype, tuple] = {}       # wire dtype -> (mapped staging, half_elems)
         self._events: List[torch.cuda.Event] = []
         self._pass_started = False
         self._found_inf: Optional[torch.Tensor] = None
@@ -88,6 +89,19 @@ class NativeComm:
                                "the model's arenas (ParamArena allocates symmetric memory when it is initialised)")
         self._map(arena.grads)
         self._map(arena.params)
+
+    def _wire_staging(self, dtype: torch.dtype, n: int):
+        """Symmetric 16-bit staging (send half | receive half) for the compressed-wire all-reduce; sized once
+        for the largest bucket.  Collective (rendezvous): every rank reaches it for the same bucket."""
+        import torch.distributed._symmetric_memory as symm_mem
+        cur = self._wire.get(dtype)
+        if cur is None or cur[1] < n:
+            half = (max(n, 8 << 20) + 63) // 64 * 64
+            t = symm_mem.empty(2 * half, dtype=dtype, device=self.device)
+            m = _Mapped(t, self.group)
+            cur = (m, half)
+            self._wire[dtype] = cur
+        return cur
 
     def _blocks(self, m: _Mapped, n: int) -> int:
         cap = require().pdb_comm_max_blocks(self.world, m.pad_bytes)
@@ -131,6 +145,18 @@ class NativeComm:
                 self.flag.zero_()
             self._found_inf = found_inf
             n = end - start
+            if wire_dtype in (torch.float16, torch.bfloat16) and n % 8 == 0:
+                wm, half = self._wire_staging(wire_dtype, n)
+                check(require().pdb_allreduce_inplace_wire16(
+                    m.bufs, m.pads, self._flag_ptrs if found_inf is not None else None, wm.bufs, half,
+                    0 if wire_dtype == torch.bfloat16 else 1, self.rank, self.world, start, n,
+                    (1.0 / self.world) if average else 1.0, ptr(inv_scale), self._blocks(m, n),
+                    ctypes.c_void_p(self.stream.cuda_stream)), "pdb_allreduce_inplace_wire16")
+                count_launch()
+                done = torch.cuda.Event()
+                done.record(self.stream)
+                self._events.append(done)
+                return
             check(require().pdb_allreduce_inplace(
                 m.bufs, m.pads, self._flag_ptrs if found_inf is not None else None,
                 ctypes.c_void_p(m.multicast if self.use_multicast else 0), self.rank, self.world, start, n,
@@ -162,4 +188,15 @@ class NativeComm:
         check(require().pdb_small_allreduce(self._staging_ptrs, self._aux.pads, self.rank, self.world, ptr(data), n,
                                             self.slot, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)),
               "pdb_small_allreduce")
+        count_launch()
+
+    def bn_stats_sync(self, x2d: torch.Tensor, sums: torch.Tensor) -> None:
+        """Per-channel sum / sum-of-squares of x2d[rows, C] over ALL ranks, exchanged inside the statistics
+        kernel (K6)."""
+        rows, C = x2d.shape
+        scratch = ops.elementwise.bn_stats_scratch(C, x2d.device)
+        check(require().pdb_bn_stats_sync(ptr(x2d), ops.dtype_tag(x2d.dtype), rows, C, ptr(sums), ptr(scratch),
+                                          scratch.numel(), self._staging_ptrs, self._aux.pads, self.rank, self.world,
+                                          self.slot, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)),
+              "pdb_bn_stats_sync")
         count_launch()

@@ -53,6 +53,26 @@ def comm_worker(rank, world, port, out_dir):
         torch.cuda.synchronize()
         res[f"found_inf_injected_mc{int(use_mc)}"] = float(found)
     res["multicast_available"] = bool(comm._map(buf).multicast)
+    # 16-bit wire (bf16_compress / fp16_compress semantics)
+    for wd, tag in ((torch.bfloat16, "bf16"), (torch.float16, "fp16")):
+        buf.copy_(torch.randn(n_total, device=dev, generator=g))
+        ref = buf.clone()
+        dist.all_reduce(ref)
+        ref.mul_(1.0 / world)
+        n = BUCKET_ELEMS[0]
+        comm.allreduce_range(buf, 0, n, average=True, wire_dtype=wd)
+        comm.wait_all()
+        torch.cuda.synchronize()
+        res[f"wire_{tag}_err"] = float((buf[:n] - ref[:n]).abs().max() / ref[:n].abs().max())
+    # K6: statistics kernel with the cross-GPU reduction inside
+    xs = (torch.randn(3000, 256, device=dev, generator=g) + rank).to(torch.bfloat16)
+    sums = torch.empty(512, device=dev)
+    comm.bn_stats_sync(xs, sums)
+    comm.bn_stats_sync(xs, sums)                 # twice: slots and tickets are reusable
+    want = torch.cat([xs.float().sum(0), (xs.float() ** 2).sum(0)])
+    dist.all_reduce(want)
+    torch.cuda.synchronize()
+    res["bn_stats_sync_err"] = float((sums - want).abs().max() / want.abs().max())
     # broadcast
     buf.fill_(float(rank + 1))
     comm.broadcast_(buf, 0)
