@@ -142,24 +142,34 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_wire16_kernel(PeerPtrs
                                                                         float pre_scale,
                                                                         const float* __restrict__ inv_scale) {
   const int64_t n8 = n / 8;
-  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
   float* grads = pp.buf[rank] + start;
   W* S_own = static_cast<W*>(st.stage[rank]);
   W* R_own = S_own + half_elems;
-  for (int64_t i = tid; i < n8; i += nth) {            // phase 1: pack (local)
-    const float4 a = reinterpret_cast<const float4*>(grads)[2 * i], b = reinterpret_cast<const float4*>(grads)[2 * i + 1];
-    float f[8] = {a.x * pre_scale, a.y * pre_scale, a.z * pre_scale, a.w * pre_scale,
-                  b.x * pre_scale, b.y * pre_scale, b.z * pre_scale, b.w * pre_scale};
-    reinterpret_cast<uint4*>(S_own)[i] = pack8<W>(f);
+  constexpr int kUnroll = 4;
+  const int64_t tile = (int64_t)blockDim.x * kUnroll;
+  const int64_t per = (n8 + world - 1) / world;
+  // The cross-rank barrier pairs block b of this rank with block b of every peer — nothing orders block b
+  // against the OTHER blocks of a peer.  So block b packs (phase 1) and unpacks (phase 3) exactly the vectors
+  // that block b of the shard owner reads / writes in phase 2: the same index walk, repeated for every shard.
+  for (int q = 0; q < world; ++q) {                    // phase 1: pack (local)
+    const int64_t qlo = min(per * q, n8), qhi = min(qlo + per, n8);
+    for (int64_t base = qlo + (int64_t)blockIdx.x * tile; base < qhi; base += (int64_t)gridDim.x * tile) {
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+        if (i >= qhi) continue;
+        const float4 a = reinterpret_cast<const float4*>(grads)[2 * i], b = reinterpret_cast<const float4*>(grads)[2 * i + 1];
+        float f[8] = {a.x * pre_scale, a.y * pre_scale, a.z * pre_scale, a.w * pre_scale,
+                      b.x * pre_scale, b.y * pre_scale, b.z * pre_scale, b.w * pre_scale};
+        reinterpret_cast<uint4*>(S_own)[i] = pack8<W>(f);
+      }
+    }
   }
   __threadfence_system();
   cross_rank_barrier(pp.pad, rank, world);
   const float s = inv_scale ? *inv_scale : 1.0f;
-  const int64_t per = (n8 + world - 1) / world;
   const int64_t lo = min(per * rank, n8), hi = min(lo + per, n8);
   bool bad = false;
-  constexpr int kUnroll = 4;
-  const int64_t tile = (int64_t)blockDim.x * kUnroll;
   for (int64_t base = lo + (int64_t)blockIdx.x * tile; base < hi; base += (int64_t)gridDim.x * tile) {
     float acc[kUnroll][8];
     bool live[kUnroll];
@@ -210,13 +220,21 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_wire16_kernel(PeerPtrs
     *reinterpret_cast<volatile float*>(pp.flag[threadIdx.x]) = 1.0f;
   __threadfence_system();
   cross_rank_barrier(pp.pad, rank, world);
-  for (int64_t i = tid; i < n8; i += nth) {            // phase 3: unpack (local; R was written by the shard owners)
-    uint4 v;
-    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(reinterpret_cast<const uint4*>(R_own) + i));
-    float f[8];
-    unpack8<W>(v, f);
-    reinterpret_cast<float4*>(grads)[2 * i] = make_float4(f[0], f[1], f[2], f[3]);
-    reinterpret_cast<float4*>(grads)[2 * i + 1] = make_float4(f[4], f[5], f[6], f[7]);
+  for (int q = 0; q < world; ++q) {                    // phase 3: unpack (local; shard q was written by rank q's block b)
+    const int64_t qlo = min(per * q, n8), qhi = min(qlo + per, n8);
+    for (int64_t base = qlo + (int64_t)blockIdx.x * tile; base < qhi; base += (int64_t)gridDim.x * tile) {
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+        if (i >= qhi) continue;
+        uint4 v;
+        asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(reinterpret_cast<const uint4*>(R_own) + i));
+        float f[8];
+        unpack8<W>(v, f);
+        reinterpret_cast<float4*>(grads)[2 * i] = make_float4(f[0], f[1], f[2], f[3]);
+        reinterpret_cast<float4*>(grads)[2 * i + 1] = make_float4(f[4], f[5], f[6], f[7]);
+      }
+    }
   }
 }
 
