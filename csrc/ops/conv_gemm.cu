@@ -28,8 +28,9 @@ using namespace tc05;
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;                 // 64 x 16-bit = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kNumThreads = 192;            // 6 warps: producer, mma, 4 x epilogue
-constexpr int kEpiThreads = 128;
+constexpr int kNumThreads = 320;            // 10 warps: producer, mma, 8 x epilogue
+constexpr int kEpiThreads = 256;            // two warps per TMEM lane quarter, splitting the columns:
+                                            // with K <= 512 the epilogue, not the MMA, sets the tile rate
 constexpr uint32_t A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KB
 constexpr uint32_t CHUNK_BYTES = 64 * 128;                  // 64 rows x 128 B = 8 KB (wgrad boxes)
 
@@ -117,7 +118,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull + i, 1);
-      mbar_init(tempty + i, 4);          // one arrive per epilogue warp
+      mbar_init(tempty + i, kEpiThreads / 32);   // one arrive per epilogue warp
     }
     fence_barrier_init();
   }
@@ -199,11 +200,14 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   } else {
     // ================================ epilogue ====================================
     const int quarter = warp & 3;                     // TMEM lanes [32*quarter, +32) are visible to this warp
+    const int half = (warp - 2) >> 2;                 // the two warps of a quarter take alternate 32-column groups
     const int row = quarter * 32 + lane;              // row of the 128-row tile owned by this thread
-    const int tid_e = threadIdx.x - 64;               // 0..127
+    const int tid_e = threadIdx.x - 64;               // 0..255
     const bool leader = tid_e == 0;
     constexpr int PAIRS = BLOCK_N / 2;                // column pairs for the statistics pass
-    constexpr int G = kEpiThreads / PAIRS;            // row groups (1, 2, 4)
+    constexpr int G = kEpiThreads / PAIRS;            // row groups (2, 4, 8)
+    constexpr int GPW = BLOCK_N / 64;                 // 32-column groups per warp (1, 2, 4)
+    constexpr int BATCH = GPW < 2 ? GPW : 2;          // groups loaded from TMEM before one wait
     const int pair = tid_e % PAIRS, rg = tid_e / PAIRS;
     float st_sum[2] = {0.f, 0.f}, st_sq[2] = {0.f, 0.f};
     int st_nblk = -1;
@@ -227,34 +231,34 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       if (leader) tma_store_wait_read0();
       named_bar_sync(1, kEpiThreads);
 #pragma unroll
-      for (int j = 0; j < BLOCK_N / 64; ++j) {
-        uint32_t v0[32], v1[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BLOCK_N + j * 64;
-        tmem_ld_32x32(taddr, v0);
-        tmem_ld_32x32(taddr + 32, v1);
-        tmem_ld_wait();
-        if (p.bias) {
+      for (int b0 = 0; b0 < GPW; b0 += BATCH) {
+        uint32_t v[BATCH][32];
 #pragma unroll
-          for (int c = 0; c < 32; ++c) {
-            const int n = n0 + j * 64 + c;
-            v0[c] = __float_as_uint(__uint_as_float(v0[c]) + (n < p.N ? __ldg(p.bias + n) : 0.f));
-            v1[c] = __float_as_uint(__uint_as_float(v1[c]) + (n + 32 < p.N ? __ldg(p.bias + n + 32) : 0.f));
-          }
+        for (int b = 0; b < BATCH; ++b) {
+          const int g = half + 2 * (b0 + b);          // 32-column group of the tile
+          tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BLOCK_N + g * 32, v[b]);
         }
-        uint8_t* dst = out_stage + j * 16384 + row * 128;
+        tmem_ld_wait();
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {           // 16-byte chunks 0..3 come from v0, 4..7 from v1
-          uint4 w0, w1;
-          w0.x = pack2<kBf16>(__uint_as_float(v0[8 * c + 0]), __uint_as_float(v0[8 * c + 1]));
-          w0.y = pack2<kBf16>(__uint_as_float(v0[8 * c + 2]), __uint_as_float(v0[8 * c + 3]));
-          w0.z = pack2<kBf16>(__uint_as_float(v0[8 * c + 4]), __uint_as_float(v0[8 * c + 5]));
-          w0.w = pack2<kBf16>(__uint_as_float(v0[8 * c + 6]), __uint_as_float(v0[8 * c + 7]));
-          w1.x = pack2<kBf16>(__uint_as_float(v1[8 * c + 0]), __uint_as_float(v1[8 * c + 1]));
-          w1.y = pack2<kBf16>(__uint_as_float(v1[8 * c + 2]), __uint_as_float(v1[8 * c + 3]));
-          w1.z = pack2<kBf16>(__uint_as_float(v1[8 * c + 4]), __uint_as_float(v1[8 * c + 5]));
-          w1.w = pack2<kBf16>(__uint_as_float(v1[8 * c + 6]), __uint_as_float(v1[8 * c + 7]));
-          *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = w0;
-          *reinterpret_cast<uint4*>(dst + (((c + 4) ^ (row & 7)) << 4)) = w1;
+        for (int b = 0; b < BATCH; ++b) {
+          const int g = half + 2 * (b0 + b);
+          if (p.bias) {
+#pragma unroll
+            for (int c = 0; c < 32; ++c) {
+              const int n = n0 + g * 32 + c;
+              v[b][c] = __float_as_uint(__uint_as_float(v[b][c]) + (n < p.N ? __ldg(p.bias + n) : 0.f));
+            }
+          }
+          uint8_t* dst = out_stage + (g >> 1) * 16384 + row * 128;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {               // four 16-byte chunks of this group's half row
+            uint4 w;
+            w.x = pack2<kBf16>(__uint_as_float(v[b][8 * c + 0]), __uint_as_float(v[b][8 * c + 1]));
+            w.y = pack2<kBf16>(__uint_as_float(v[b][8 * c + 2]), __uint_as_float(v[b][8 * c + 3]));
+            w.z = pack2<kBf16>(__uint_as_float(v[b][8 * c + 4]), __uint_as_float(v[b][8 * c + 5]));
+            w.w = pack2<kBf16>(__uint_as_float(v[b][8 * c + 6]), __uint_as_float(v[b][8 * c + 7]));
+            *reinterpret_cast<uint4*>(dst + ((((g & 1) * 4 + c) ^ (row & 7)) << 4)) = w;
+          }
         }
       }
       // accumulator fully read: hand the TMEM stage back to the MMA warp
@@ -352,7 +356,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull + i, 1);
-      mbar_init(tempty + i, 4);
+      mbar_init(tempty + i, kEpiThreads / 32);
     }
     fence_barrier_init();
   }
@@ -454,6 +458,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
     }
   } else {
     const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;                 // two warps per lane quarter, alternate 32-column groups
     const int row = quarter * 32 + lane;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -467,7 +472,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
       fence_after_thread_sync();
       const int cout = m_blk * BLOCK_M + row;
 #pragma unroll
-      for (int j = 0; j < BLOCK_N / 32; ++j) {
+      for (int j = half; j < BLOCK_N / 32; j += 2) {
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BLOCK_N + j * 32, v);
         tmem_ld_wait();
