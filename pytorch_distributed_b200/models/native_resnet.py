@@ -89,15 +89,36 @@ class _NativeStep(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, anchor, engine):
-        logits, saved = engine._forward_train(x)
-        ctx.engine, ctx.saved = engine, saved
+        logits, plan = engine._forward_train(x)
+        ctx.engine, ctx.plan = engine, plan
         return logits
 
     @staticmethod
     def backward(ctx, dlogits):
-        ctx.engine._backward(ctx.saved, dlogits)
-        ctx.saved = None
+        ctx.engine._backward(ctx.plan, dlogits)
+        ctx.plan = None
         return None, None, None
+
+
+class _StepPlan:
+    """Everything that is fixed for one input shape: the buffers of the step (allocated once, in a fixed
+    order, then handed out again in the same order every step) and, once warm, the CUDA graphs of the forward
+    pass and of each backward segment.  A training step then costs ~20 graph launches instead of ~350 kernel
+    launches, which is what lets ONE Python process drive eight replicas in the DataParallel mode."""
+
+    def __init__(self):
+        self.bufs: List[torch.Tensor] = []
+        self.cursor = 0
+        self.steps = 0
+        self.fwd_end = 0
+        self.logits = None
+        self.saved = None
+        self.x_static = None
+        self.dlogits = None
+        self.fwd_graph = None
+        self.bwd_graphs = None          # [(graph, ready parameter indices)]
+        self.backward_ran = False
+        self.graphs_failed = False
 
 
 class NativeResNetEngine:
@@ -118,6 +139,13 @@ class NativeResNetEngine:
         self.pindex: Dict[str, int] = {e.name: i for i, e in enumerate(self.arena.entries)}
         self._stat_floats = 0
         self.ddp = None
+        import os
+        self.graphs = os.environ.get("PDB200_GRAPHS", "1") != "0" and not sync_bn
+        self.graph_warmup = 2                     # eager steps per shape before capture
+        self._plans: Dict[tuple, _StepPlan] = {}
+        self._plan: Optional[_StepPlan] = None
+        self._ready_log: Optional[List[int]] = None
+        self._cap_stream = None
 
         self.stem_conv = self._conv("conv1", model.conv1)
         self.stem_bn = self._bn("bn1", model.bn1)
@@ -169,13 +197,52 @@ class NativeResNetEngine:
         self.ddp = ddp
 
     def _ready(self, *indices: int) -> None:
-        if self.ddp is not None:
+        if self._ready_log is not None:           # capturing: remember, tell DDP when the segment is replayed
+            self._ready_log.extend(indices)
+        elif self.ddp is not None:
             for i in indices:
                 self.ddp.mark_param_ready(i)
 
     # -- helpers -------------------------------------------------------------------------------------
-    def _new(self, *shape) -> torch.Tensor:
-        return torch.empty(shape, dtype=self.dtype, device=self.device)
+    def _new(self, *shape, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+        """Step buffers come from the current plan: allocated on the first step of a shape, re-used (same
+        order, same addresses) afterwards — no allocator traffic in the step and capturable in a CUDA graph."""
+        dtype = dtype or self.dtype
+        p = self._plan
+        if p is None:
+            return torch.empty(shape, dtype=dtype, device=self.device)
+        if p.cursor < len(p.bufs):
+            t = p.bufs[p.cursor]
+            if tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+                raise RuntimeError("native engine: the step's buffer sequence changed between steps "
+                                   f"(slot {p.cursor}: {tuple(t.shape)} vs {tuple(shape)})")
+        else:
+            t = torch.empty(shape, dtype=dtype, device=self.device)
+            p.bufs.append(t)
+        p.cursor += 1
+        return t
+
+    def _capture(self, fn):
+        """Captures fn's launches into a CUDA graph; the returned graph remembers how many of our kernels it
+        holds so that replays keep the library's launch counter honest."""
+        from ..ops import _lib
+        n0 = _lib.launch_count()
+        g = torch.cuda.CUDAGraph()
+        if self._cap_stream is None:
+            self._cap_stream = torch.cuda.Stream(self.device)
+        cur = torch.cuda.current_stream(self.device)
+        self._cap_stream.wait_stream(cur)
+        with torch.cuda.graph(g, stream=self._cap_stream, capture_error_mode="thread_local"):
+            fn()
+        cur.wait_stream(self._cap_stream)
+        g.pdb200_kernels = _lib.launch_count() - n0
+        return g
+
+    @staticmethod
+    def _replay(g) -> None:
+        from ..ops import _lib
+        g.replay()
+        _lib.count_launch(getattr(g, "pdb200_kernels", 0))
 
     def _refresh_weights(self, need_dgrad: bool) -> None:
         """16-bit operand copies derived from the weight shadow: padded stem rows and, for training,
@@ -239,7 +306,7 @@ class NativeResNetEngine:
                               bn.beta, bn.eps, True)
         Hp, Wp = (P + 2 - 3) // 2 + 1, (Q + 2 - 3) // 2 + 1
         pooled = self._new(N, Hp, Wp, cv.K)
-        argmax = torch.empty(N, Hp, Wp, cv.K, dtype=torch.uint8, device=self.device)
+        argmax = self._new(N, Hp, Wp, cv.K, dtype=torch.uint8)
         ops.maxpool_fwd(z, pooled, argmax)
         return col, y, z, argmax, pooled
 
@@ -262,7 +329,7 @@ class NativeResNetEngine:
                        block_n=128)
         return pooled, logits
 
-    def _forward_train(self, x: torch.Tensor):
+    def _forward_impl(self, x: torch.Tensor):
         self.stats.zero_()
         self._refresh_weights(need_dgrad=True)
         stem = self._stem(x, True)
@@ -272,6 +339,44 @@ class NativeResNetEngine:
             saved_blocks.append(sv)
         pooled, logits = self._head(cur)
         return logits, (stem, saved_blocks, pooled, tuple(cur.shape))
+
+    def _forward_train(self, x: torch.Tensor):
+        x = x.contiguous()
+        if x.dtype != torch.float32:
+            x = x.float()
+        key = (tuple(x.shape), "train")
+        plan = self._plans.get(key)
+        if plan is None:
+            plan = self._plans[key] = _StepPlan()
+        self._plan = plan
+        plan.cursor = 0
+        plan.steps += 1
+        try:
+            if plan.fwd_graph is None and self.graphs and not plan.graphs_failed and plan.backward_ran \
+                    and plan.steps > self.graph_warmup:
+                try:
+                    plan.x_static = x.clone()
+
+                    def fwd():
+                        plan.cursor = 0
+                        plan.logits, plan.saved = self._forward_impl(plan.x_static)
+                        plan.fwd_end = plan.cursor
+                    plan.fwd_graph = self._capture(fwd)
+                except Exception as e:            # capture is an optimisation: fall back to eager launches
+                    import warnings
+                    warnings.warn(f"pdb200: CUDA-graph capture of the forward pass failed, staying eager: {e}")
+                    plan.fwd_graph, plan.graphs_failed = None, True
+            if plan.fwd_graph is not None:
+                plan.x_static.copy_(x, non_blocking=True)
+                self._replay(plan.fwd_graph)
+                plan.cursor = plan.fwd_end
+            else:
+                plan.logits, plan.saved = self._forward_impl(x)
+                plan.fwd_end = plan.cursor
+        finally:
+            self._plan = None
+        # autograd needs a tensor of its own per step (the static logits buffer is overwritten by the next one)
+        return plan.logits.clone(), plan
 
     @torch.no_grad()
     def forward_eval(self, x: torch.Tensor, train_stats: bool = False) -> torch.Tensor:
@@ -296,8 +401,8 @@ class NativeResNetEngine:
         v = lambda t: None if t is None else t.view(rows, bn.C)    # noqa: E731
         ops.bn_bwd_reduce(v(dz), v(z), v(y), bn.mean, bn.rstd, ds)
         world = self._sync_stats(ds)
-        dy = torch.empty_like(y)
-        dres = torch.empty_like(y) if want_dres else None
+        dy = self._new(*y.shape)
+        dres = self._new(*y.shape) if want_dres else None
         ops.bn_bwd_apply(v(dz), v(z), v(y), v(dy), v(dres), bn.mean, bn.rstd, bn.gamma, ds, rows * world, bn.dgamma,
                          bn.dbeta)
         return dy, dres
@@ -336,7 +441,7 @@ class NativeResNetEngine:
         self._ready(*b.bn1.pindex)
         dxa = self._conv_bwd(b.conv1, x, dy1)
         self._ready(b.conv1.pindex)
-        dx = torch.empty_like(dxa)
+        dx = self._new(*dxa.shape)
         if b.convd is None:
             ops.add16(dxa, dres, dx)
         else:
@@ -350,26 +455,32 @@ class NativeResNetEngine:
                 ops.add16(dxa, dxd, dx)
         return dx
 
-    def _backward(self, saved, dlogits: torch.Tensor) -> None:
-        stem, saved_blocks, pooled, feat_shape = saved
-        dlogits = dlogits.contiguous()
-        if dlogits.dtype != self.dtype:
-            dlogits = dlogits.to(self.dtype)
+    # The backward pass as a list of segments (head, one per bottleneck in reverse, stem).  Each segment is a
+    # CUDA graph once warm; DDP is told about a segment's parameters right after the segment has been enqueued,
+    # so bucket all-reduces still overlap with the remaining segments.
+    def _seg_head(self, plan: _StepPlan, st: dict) -> None:
+        _, _, pooled, feat_shape = plan.saved
+        dl = plan.dlogits
+        N = dl.shape[0]
         self.dstats.zero_()
-        N = dlogits.shape[0]
-        # fc: wgrad, bias grad, dgrad
-        ops.conv_wgrad(pooled, dlogits, self.fc_dw, ConvShape(N, 1, 1, self.fc_C, self.fc_K, 1, 1, 1, 0))
-        ops.colsum16(dlogits, self.fc_db)
+        ops.conv_wgrad(pooled, dl, self.fc_dw, ConvShape(N, 1, 1, self.fc_C, self.fc_K, 1, 1, 1, 0))
+        ops.colsum16(dl, self.fc_db)
         self._ready(*self.fc_pindex[::-1])
         dpooled = self._new(N, self.fc_C)
-        ops.conv_fprop(dlogits, self.fc_wt16, dpooled, ConvShape(N, 1, 1, self.fc_K, self.fc_C, 1, 1, 1, 0))
+        ops.conv_fprop(dl, self.fc_wt16, dpooled, ConvShape(N, 1, 1, self.fc_K, self.fc_C, 1, 1, 1, 0))
         d = self._new(*feat_shape)
         ops.avgpool_bwd(dpooled, d)
-        for b, sv in zip(reversed(self.blocks), reversed(saved_blocks)):
-            d = self._block_bwd(b, sv, d)
-        col, y0, z0, argmax, _ = stem
-        dz0 = torch.empty_like(z0)
-        ops.maxpool_bwd(d, argmax, dz0)
+        st["d"] = d
+
+    def _seg_block(self, i: int):
+        def run(plan: _StepPlan, st: dict) -> None:
+            st["d"] = self._block_bwd(self.blocks[i], plan.saved[1][i], st["d"])
+        return run
+
+    def _seg_stem(self, plan: _StepPlan, st: dict) -> None:
+        col, y0, z0, argmax, _ = plan.saved[0]
+        dz0 = self._new(*z0.shape)
+        ops.maxpool_bwd(st["d"], argmax, dz0)
         dy0, _ = self._bn_bwd(self.stem_bn, dz0, z0, y0, want_dres=False)
         self._ready(*self.stem_bn.pindex)
         cv = self.stem_conv
@@ -377,3 +488,39 @@ class NativeResNetEngine:
         ops.conv_wgrad(col, dy0.view(rows, cv.K), cv.dw, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0),
                        ldw=cv.R * cv.S * cv.C, kvalid=cv.R * cv.S * cv.C)
         self._ready(cv.pindex)
+
+    def _segments(self):
+        return [self._seg_head] + [self._seg_block(i) for i in reversed(range(len(self.blocks)))] + [self._seg_stem]
+
+    def _backward(self, plan: _StepPlan, dlogits: torch.Tensor) -> None:
+        self._plan = plan
+        try:
+            plan.cursor = plan.fwd_end
+            plan.dlogits = self._new(*dlogits.shape)
+            plan.dlogits.copy_(dlogits)                   # also converts an fp32 incoming gradient
+            if plan.bwd_graphs is None and plan.fwd_graph is not None and not plan.graphs_failed:
+                try:
+                    graphs, st = [], {}
+                    for seg in self._segments():
+                        self._ready_log = []
+                        g = self._capture(lambda seg=seg: seg(plan, st))
+                        graphs.append((g, tuple(self._ready_log)))
+                    plan.bwd_graphs = graphs
+                except Exception as e:
+                    import warnings
+                    warnings.warn(f"pdb200: CUDA-graph capture of the backward pass failed, staying eager: {e}")
+                    plan.bwd_graphs, plan.graphs_failed = None, True
+                finally:
+                    self._ready_log = None
+                    plan.cursor = plan.fwd_end + 1
+            if plan.bwd_graphs is not None:
+                for g, ready in plan.bwd_graphs:
+                    self._replay(g)
+                    self._ready(*ready)
+            else:
+                st: dict = {}
+                for seg in self._segments():
+                    seg(plan, st)
+            plan.backward_ran = True
+        finally:
+            self._plan = None
