@@ -22,9 +22,10 @@ constexpr int kMaxC = 4096;
 // Channel reductions.  Block = cx channel-groups (8 ch each) x ry rows.
 // MODE 0: (sum x, sum x^2)           — forward statistics
 // MODE 1: (sum g, sum g*xhat), g = dz * (z>0)   — backward reductions
-template <typename T, int MODE, bool kHasZ>
+template <typename T, int MODE, int kMask /* 0 none, 1 z > 0, 2 bit mask */>
 __device__ __forceinline__ void reduce_rows(const T* __restrict__ a, const T* __restrict__ z,
-                                            const T* __restrict__ x, int64_t rows, int C, int cg, int cx, int ry,
+                                            const uint8_t* __restrict__ bits, const T* __restrict__ x, int64_t rows,
+                                            int C, int cg, int cx, int ry,
                                             int ty, const float* __restrict__ mean, const float* __restrict__ rstd,
                                             float (&s0)[8], float (&s1)[8]) {
   float mu[8], rs[8];
@@ -39,6 +40,7 @@ __device__ __forceinline__ void reduce_rows(const T* __restrict__ a, const T* __
   const int64_t rstride = (int64_t)gridDim.x * ry;
   for (int64_t r0 = (int64_t)blockIdx.x * ry + ty; r0 < rows; r0 += rstride * U) {
     uint4 va[U], vx[U], vz[U];
+    uint32_t vb[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t r = r0 + u * rstride;
@@ -47,7 +49,8 @@ __device__ __forceinline__ void reduce_rows(const T* __restrict__ a, const T* __
         va[u] = ldg128_stream(a + off);
         if (MODE == 1) {
           vx[u] = ldg128_stream(x + off);
-          if (kHasZ) vz[u] = ldg128_stream(z + off);
+          if (kMask == 1) vz[u] = ldg128_stream(z + off);
+          if (kMask == 2) vb[u] = __ldg(bits + (off >> 3));
         }
       }
     }
@@ -66,11 +69,15 @@ __device__ __forceinline__ void reduce_rows(const T* __restrict__ a, const T* __
       } else {
         float fx[8];
         unpack8<T>(vx[u], fx);
-        if (kHasZ) {
+        if (kMask == 1) {
           float fz[8];
           unpack8<T>(vz[u], fz);
 #pragma unroll
           for (int k = 0; k < 8; ++k) fa[k] = fz[k] > 0.f ? fa[k] : 0.f;
+        }
+        if (kMask == 2) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) fa[k] = (vb[u] >> k) & 1u ? fa[k] : 0.f;
         }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -122,7 +129,7 @@ __global__ void __launch_bounds__(kThreads) bn_stats_kernel(const T* __restrict_
   const int ncg = C / 8;
   for (int cg = tx; cg < ncg; cg += cx) {
     float s0[8] = {0}, s1[8] = {0};
-    if (ty < ry) reduce_rows<T, 0, false>(x, nullptr, nullptr, rows, C, cg, cx, ry, ty, nullptr, nullptr, s0, s1);
+    if (ty < ry) reduce_rows<T, 0, 0>(x, nullptr, nullptr, nullptr, rows, C, cg, cx, ry, ty, nullptr, nullptr, s0, s1);
     block_fold(s0, s1, tx, ty, cx, ry, smem);
     if (ty == 0) {
 #pragma unroll
@@ -172,7 +179,7 @@ __global__ void __launch_bounds__(kThreads) bn_stats_sync_kernel(const T* __rest
   const int ncg = C / 8;
   for (int cg = tx; cg < ncg; cg += cx) {
     float s0[8] = {0}, s1[8] = {0};
-    if (ty < ry) reduce_rows<T, 0, false>(x, nullptr, nullptr, rows, C, cg, cx, ry, ty, nullptr, nullptr, s0, s1);
+    if (ty < ry) reduce_rows<T, 0, 0>(x, nullptr, nullptr, nullptr, rows, C, cg, cx, ry, ty, nullptr, nullptr, s0, s1);
     block_fold(s0, s1, tx, ty, cx, ry, smem);
     if (ty == 0) {
 #pragma unroll
@@ -228,8 +235,9 @@ __global__ void __launch_bounds__(kThreads) bn_stats_sync_kernel(const T* __rest
   }
 }
 
-template <typename T, bool kHasZ>
+template <typename T, int kMask>
 __global__ void __launch_bounds__(kThreads) bn_bwd_reduce_kernel(const T* __restrict__ dz, const T* __restrict__ z,
+                                                                 const uint8_t* __restrict__ bits,
                                                                  const T* __restrict__ x, int64_t rows, int C, int cx,
                                                                  int ry, const float* __restrict__ mean,
                                                                  const float* __restrict__ rstd,
@@ -239,7 +247,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_reduce_kernel(const T* __rest
   const int ncg = C / 8;
   for (int cg = tx; cg < ncg; cg += cx) {
     float s0[8] = {0}, s1[8] = {0};
-    if (ty < ry) reduce_rows<T, 1, kHasZ>(dz, z, x, rows, C, cg, cx, ry, ty, mean, rstd, s0, s1);
+    if (ty < ry) reduce_rows<T, 1, kMask>(dz, z, bits, x, rows, C, cg, cx, ry, ty, mean, rstd, s0, s1);
     block_fold(s0, s1, tx, ty, cx, ry, smem);
     if (ty == 0) {
 #pragma unroll
@@ -502,8 +510,9 @@ extern "C" int pdb_bn_stats_sync(const void* x, int dtype, int64_t rows, int C, 
   return 0;
 }
 
-extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const void* x, int dtype, int64_t rows, int C,
-                                 const float* mean, const float* rstd, float* dsums, void* stream) {
+extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, int dtype,
+                                 int64_t rows, int C, const float* mean, const float* rstd, float* dsums,
+                                 void* stream) {
   PDB_CHECK_ARG(dz && x && mean && rstd && dsums, "pdb_bn_bwd_reduce: null pointer");
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_bwd_reduce: bad shape rows=%lld C=%d",
                 (long long)rows, C);
@@ -513,12 +522,15 @@ extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const void* x, i
   const size_t smem = (size_t)kThreads * 16 * sizeof(float);
   cudaStream_t st = (cudaStream_t)stream;
   PDB_DISPATCH_16(dtype, T, {
-    if (z)
-      bn_bwd_reduce_kernel<T, true><<<grid, kThreads, smem, st>>>((const T*)dz, (const T*)z, (const T*)x, rows, C, cx,
-                                                                  ry, mean, rstd, dsums);
+    if (relu_mask)
+      bn_bwd_reduce_kernel<T, 2><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, relu_mask, (const T*)x, rows, C,
+                                                               cx, ry, mean, rstd, dsums);
+    else if (z)
+      bn_bwd_reduce_kernel<T, 1><<<grid, kThreads, smem, st>>>((const T*)dz, (const T*)z, nullptr, (const T*)x, rows, C,
+                                                               cx, ry, mean, rstd, dsums);
     else
-      bn_bwd_reduce_kernel<T, false><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, (const T*)x, rows, C, cx, ry,
-                                                                   mean, rstd, dsums);
+      bn_bwd_reduce_kernel<T, 0><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, nullptr, (const T*)x, rows, C, cx,
+                                                               ry, mean, rstd, dsums);
   });
   PDB_LAUNCH_CHECK();
   return 0;
@@ -527,8 +539,10 @@ extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const void* x, i
 extern "C" int pdb_bn_apply(const void* x, const void* residual, void* y, int dtype, int64_t rows, int C,
                             const float* sums, double count, const float* gamma, const float* beta, float eps,
                             float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
-                            float* save_mean, float* save_rstd, int relu, void* stream) {
+                            float* save_mean, float* save_rstd, int relu, uint8_t* relu_mask, void* stream) {
   PDB_CHECK_ARG(x && y && sums && gamma && beta, "pdb_bn_apply: null pointer");
+  PDB_CHECK_ARG(!relu_mask || (relu && bn_fast_ok(C)),
+                "pdb_bn_apply: relu_mask needs relu and a channel count whose 8-channel groups divide 256 (C=%d)", C);
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0 && count > 0, "pdb_bn_apply: bad shape rows=%lld C=%d",
                 (long long)rows, C);
   const int64_t nvec = rows * C / 8;
@@ -539,7 +553,7 @@ extern "C" int pdb_bn_apply(const void* x, const void* residual, void* y, int dt
 #define FAST(RES, RELU)                                                                                            \
   bn_apply_fast_kernel<T, RES, RELU><<<fgrid, kFastThreads, 0, st>>>(                                              \
       (const T*)x, (const T*)residual, (T*)y, nvec, C, sums, inv_count, unbias, gamma, beta, eps, momentum,        \
-      running_mean, running_var, num_batches_tracked, save_mean, save_rstd)
+      running_mean, running_var, num_batches_tracked, save_mean, save_rstd, relu_mask)
     PDB_DISPATCH_16(dtype, T, {
       if (residual && relu) FAST(true, true);
       else if (residual) FAST(true, false);
@@ -605,25 +619,29 @@ extern "C" int pdb_bn_apply_eval(const void* x, const void* residual, void* y, i
   return 0;
 }
 
-extern "C" int pdb_bn_bwd_apply(const void* dz, const void* z, const void* x, void* dx, void* dres, int dtype,
-                                int64_t rows, int C, const float* mean, const float* rstd, const float* gamma,
-                                const float* dsums, double count, float* dgamma, float* dbeta, void* stream) {
+extern "C" int pdb_bn_bwd_apply(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, void* dx,
+                                void* dres, int dtype, int64_t rows, int C, const float* mean, const float* rstd,
+                                const float* gamma, const float* dsums, double count, float* dgamma, float* dbeta,
+                                void* stream) {
   PDB_CHECK_ARG(dz && x && dx && mean && rstd && gamma && dsums, "pdb_bn_bwd_apply: null pointer");
+  PDB_CHECK_ARG(!relu_mask || bn_fast_ok(C), "pdb_bn_bwd_apply: relu_mask needs a power-of-two channel count (C=%d)", C);
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0 && count > 0, "pdb_bn_bwd_apply: bad shape");
   const int64_t nvec = rows * C / 8;
   cudaStream_t st = (cudaStream_t)stream;
   if (bn_fast_ok(C)) {
     const int fgrid = bn_fast_grid(nvec, kFastUBwd);
     const float inv_count = (float)(1.0 / count);
-#define FAST(HZ, DR)                                                                                              \
-  bn_bwd_apply_fast_kernel<T, HZ, DR><<<fgrid, kFastThreads, 0, st>>>(                                            \
-      (const T*)dz, (const T*)z, (const T*)x, (T*)dx, (T*)dres, nvec, C, mean, rstd, gamma, dsums, inv_count,     \
-      dgamma, dbeta)
+#define FAST(MK, DR)                                                                                              \
+  bn_bwd_apply_fast_kernel<T, MK, DR><<<fgrid, kFastThreads, 0, st>>>(                                            \
+      (const T*)dz, (const T*)z, relu_mask, (const T*)x, (T*)dx, (T*)dres, nvec, C, mean, rstd, gamma, dsums,     \
+      inv_count, dgamma, dbeta)
     PDB_DISPATCH_16(dtype, T, {
-      if (z && dres) FAST(true, true);
-      else if (z) FAST(true, false);
-      else if (dres) FAST(false, true);
-      else FAST(false, false);
+      if (relu_mask && dres) FAST(2, true);
+      else if (relu_mask) FAST(2, false);
+      else if (z && dres) FAST(1, true);
+      else if (z) FAST(1, false);
+      else if (dres) FAST(0, true);
+      else FAST(0, false);
     });
 #undef FAST
     PDB_LAUNCH_CHECK();

@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(kFastThreads) bn_apply_fast_kernel(
     const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, int64_t nvec, int C,
     const float* __restrict__ sums, float inv_count, float unbias, const float* __restrict__ gamma,
     const float* __restrict__ beta, float eps, float momentum, float* running_mean, float* running_var,
-    int64_t* num_batches_tracked, float* save_mean, float* save_rstd) {
+    int64_t* num_batches_tracked, float* save_mean, float* save_rstd, uint8_t* __restrict__ relu_mask) {
   const int cvec = C >> 3;
   const int c0 = (int)(threadIdx.x % cvec) << 3;
   float sc[8], sh[8];
@@ -84,6 +84,12 @@ __global__ void __launch_bounds__(kFastThreads) bn_apply_fast_kernel(
       for (int k = 0; k < 8; ++k) f[k] += r[k];
     }
     if (kRelu) {
+      if (relu_mask) {       // one bit per element: the backward pass reads this instead of the 16x larger z
+        uint32_t m = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) m |= (f[k] > 0.f ? 1u : 0u) << k;
+        relu_mask[i] = (uint8_t)m;
+      }
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
     }
@@ -142,9 +148,10 @@ __global__ void __launch_bounds__(kFastThreads) bn_apply_eval_fast_kernel(
 
 // dx = A*g + B*x + Cc,  A = gamma*rstd, B = -A*k2*rstd, Cc = -B*mean - A*k1, k1 = dsums[c]/count, k2 = dsums[C+c]/count
 constexpr int kFastUBwd = 4;      // three input streams: fewer vectors per thread keep the registers in check
-template <typename T, bool kHasZ, bool kDres>
+template <typename T, int kMask /* 0 none, 1 z > 0, 2 bit mask */, bool kDres>
 __global__ void __launch_bounds__(kFastThreads) bn_bwd_apply_fast_kernel(
-    const T* __restrict__ dz, const T* __restrict__ z, const T* __restrict__ x, T* __restrict__ dx, T* __restrict__ dres,
+    const T* __restrict__ dz, const T* __restrict__ z, const uint8_t* __restrict__ bits, const T* __restrict__ x,
+    T* __restrict__ dx, T* __restrict__ dres,
     int64_t nvec, int C, const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
     const float* __restrict__ dsums, float inv_count, float* dgamma, float* dbeta) {
   const int cvec = C >> 3;
@@ -169,13 +176,15 @@ __global__ void __launch_bounds__(kFastThreads) bn_bwd_apply_fast_kernel(
   }
   const int64_t base = (int64_t)blockIdx.x * (kFastThreads * kFastUBwd) + threadIdx.x;
   uint4 vg[kFastUBwd], vx[kFastUBwd], vz[kFastUBwd];
+  uint32_t vb[kFastUBwd];
 #pragma unroll
   for (int u = 0; u < kFastUBwd; ++u) {
     const int64_t i = base + (int64_t)u * kFastThreads;
     if (i < nvec) {
       vg[u] = ldg128_stream(dz + i * 8);
       vx[u] = ldg128_stream(x + i * 8);
-      if (kHasZ) vz[u] = ldg128_stream(z + i * 8);
+      if (kMask == 1) vz[u] = ldg128_stream(z + i * 8);
+      if (kMask == 2) vb[u] = __ldg(bits + i);
     }
   }
 #pragma unroll
@@ -185,11 +194,15 @@ __global__ void __launch_bounds__(kFastThreads) bn_bwd_apply_fast_kernel(
     float g[8], fx[8];
     unpack8<T>(vg[u], g);
     unpack8<T>(vx[u], fx);
-    if (kHasZ) {
+    if (kMask == 1) {
       float fz[8];
       unpack8<T>(vz[u], fz);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] = fz[k] > 0.f ? g[k] : 0.f;
+    }
+    if (kMask == 2) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = (vb[u] >> k) & 1u ? g[k] : 0.f;
     }
     if (kDres) stg128(dres + i * 8, pack8<T>(g));
     float o[8];

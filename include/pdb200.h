@@ -92,27 +92,29 @@ int pdb_bn_stats_noalloc(const void* x, int dtype, int64_t rows, int C, float* s
 /* y = [relu]( (x - mean) * rstd * gamma + beta [+ residual] ).  mean/rstd are derived from
  * sums[2*C] over `count` elements per channel (count may exceed rows under SyncBN) inside the
  * kernel; block 0 stores save_mean/save_rstd and updates running_mean/var/num_batches_tracked when
- * given.  x and y may alias. */
+ * given.  relu_mask (nullable, rows*C/8 bytes): bit k of byte i says whether element 8*i+k passed the
+ * ReLU — the backward kernels read it instead of the 16x larger activation. */
 int pdb_bn_apply(const void* x, const void* residual, void* y, int dtype, int64_t rows, int C,
                  const float* sums, double count, const float* gamma, const float* beta, float eps,
                  float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
-                 float* save_mean, float* save_rstd, int relu, void* stream);
+                 float* save_mean, float* save_rstd, int relu, uint8_t* relu_mask, void* stream);
 
 /* Inference-mode BN: uses running statistics. */
 int pdb_bn_apply_eval(const void* x, const void* residual, void* y, int dtype, int64_t rows, int C,
                       const float* running_mean, const float* running_var, const float* gamma,
                       const float* beta, float eps, int relu, void* stream);
 
-/* Backward reductions: with g = dz * (z > 0 if z given), dsums[0:C] += sum g,
- * dsums[C:2C] += sum g * (x - mean) * rstd.  dsums must be zeroed by the caller. */
-int pdb_bn_bwd_reduce(const void* dz, const void* z, const void* x, int dtype, int64_t rows, int C,
-                      const float* mean, const float* rstd, float* dsums, void* stream);
+/* Backward reductions: with g = dz masked by the ReLU (relu_mask bits if given, else z > 0 if z is
+ * given, else unmasked), dsums[0:C] += sum g, dsums[C:2C] += sum g * (x - mean) * rstd.  dsums must be
+ * zeroed by the caller. */
+int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, int dtype,
+                      int64_t rows, int C, const float* mean, const float* rstd, float* dsums, void* stream);
 
 /* dx = gamma*rstd * (g - dsums[c]/count - xhat * dsums[C+c]/count);  optionally also writes
  * dres = g (gradient of the residual branch).  Block 0 accumulates dgamma += dsums[C:], dbeta +=
  * dsums[:C] (fp32 gradient arena views; may be null). */
-int pdb_bn_bwd_apply(const void* dz, const void* z, const void* x, void* dx, void* dres, int dtype,
-                     int64_t rows, int C, const float* mean, const float* rstd, const float* gamma,
+int pdb_bn_bwd_apply(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, void* dx, void* dres,
+                     int dtype, int64_t rows, int C, const float* mean, const float* rstd, const float* gamma,
                      const float* dsums, double count, float* dgamma, float* dbeta, void* stream);
 
 /* ---------------------------------------------------------------------------------------------

@@ -226,7 +226,7 @@ class NativeResNetEngine:
         """Captures fn's launches into a CUDA graph; the returned graph remembers how many of our kernels it
         holds so that replays keep the library's launch counter honest."""
         from ..ops import _lib
-        n0 = _lib.launch_count()
+        n0 = _lib.thread_launch_count()
         g = torch.cuda.CUDAGraph()
         if self._cap_stream is None:
             self._cap_stream = torch.cuda.Stream(self.device)
@@ -235,7 +235,7 @@ class NativeResNetEngine:
         with torch.cuda.graph(g, stream=self._cap_stream, capture_error_mode="thread_local"):
             fn()
         cur.wait_stream(self._cap_stream)
-        g.pdb200_kernels = _lib.launch_count() - n0
+        g.pdb200_kernels = _lib.thread_launch_count() - n0
         return g
 
     @staticmethod
@@ -277,13 +277,16 @@ class NativeResNetEngine:
         rows = N * P * Q
         if train:
             world = self._sync_stats(sums)
+            # one bit per element records the ReLU decision; BN backward reads it instead of z (1/16 the bytes)
+            mask = self._new(rows * cv.K // 8, dtype=torch.uint8) if relu else None
             ops.bn_apply(y.view(rows, cv.K), None if residual is None else residual.view(rows, cv.K),
                          z.view(rows, cv.K), sums, rows * world, bn.gamma, bn.beta, bn.eps, bn.momentum,
-                         bn.running_mean, bn.running_var, bn.nbt, bn.mean, bn.rstd, relu)
+                         bn.running_mean, bn.running_var, bn.nbt, bn.mean, bn.rstd, relu, mask)
+            return y, z, mask
         else:
             ops.bn_apply_eval(y.view(rows, cv.K), None if residual is None else residual.view(rows, cv.K),
                               z.view(rows, cv.K), bn.running_mean, bn.running_var, bn.gamma, bn.beta, bn.eps, relu)
-        return y, z
+        return y, z, None
 
     # -- forward -----------------------------------------------------------------------------------------
     def _stem(self, x: torch.Tensor, train: bool):
@@ -297,10 +300,12 @@ class NativeResNetEngine:
         sums = self.stats[bn.slot: bn.slot + 2 * bn.C] if train else None
         ops.conv_fprop(col, self.stem_w16, y, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0), stats=sums)
         z = self._new(N, P, Q, cv.K)
+        mask = None
         if train:
             world = self._sync_stats(sums)
+            mask = self._new(rows * cv.K // 8, dtype=torch.uint8)
             ops.bn_apply(y.view(rows, cv.K), None, z.view(rows, cv.K), sums, rows * world, bn.gamma, bn.beta, bn.eps,
-                         bn.momentum, bn.running_mean, bn.running_var, bn.nbt, bn.mean, bn.rstd, True)
+                         bn.momentum, bn.running_mean, bn.running_var, bn.nbt, bn.mean, bn.rstd, True, mask)
         else:
             ops.bn_apply_eval(y.view(rows, cv.K), None, z.view(rows, cv.K), bn.running_mean, bn.running_var, bn.gamma,
                               bn.beta, bn.eps, True)
@@ -308,17 +313,17 @@ class NativeResNetEngine:
         pooled = self._new(N, Hp, Wp, cv.K)
         argmax = self._new(N, Hp, Wp, cv.K, dtype=torch.uint8)
         ops.maxpool_fwd(z, pooled, argmax)
-        return col, y, z, argmax, pooled
+        return col, y, z, argmax, mask, pooled
 
     def _block_fwd(self, b: _BlockPlan, x: torch.Tensor, train: bool):
-        y1, z1 = self._conv_bn(b.conv1, b.bn1, x, train=train)
-        y2, z2 = self._conv_bn(b.conv2, b.bn2, z1, train=train)
+        y1, z1, m1 = self._conv_bn(b.conv1, b.bn1, x, train=train)
+        y2, z2, m2 = self._conv_bn(b.conv2, b.bn2, z1, train=train)
         if b.convd is not None:
-            yd, sc = self._conv_bn(b.convd, b.bnd, x, relu=False, train=train)
+            yd, sc, _ = self._conv_bn(b.convd, b.bnd, x, relu=False, train=train)
         else:
             yd, sc = None, x
-        y3, out = self._conv_bn(b.conv3, b.bn3, z2, residual=sc, relu=True, train=train)
-        return (x, y1, z1, y2, z2, y3, yd, out), out
+        y3, out, m3 = self._conv_bn(b.conv3, b.bn3, z2, residual=sc, relu=True, train=train)
+        return (x, y1, z1, m1, y2, z2, m2, y3, yd, m3), out
 
     def _head(self, feat: torch.Tensor):
         N, H, W, C = feat.shape
@@ -394,17 +399,18 @@ class NativeResNetEngine:
         return self.forward_eval(x, train_stats=self.model.training)
 
     # -- backward ----------------------------------------------------------------------------------------
-    def _bn_bwd(self, bn: _BNPlan, dz, z, y, *, want_dres: bool):
-        """Returns (dy, dres).  dres = dz * relu_mask (gradient of the residual branch)."""
+    def _bn_bwd(self, bn: _BNPlan, dz, mask, y, *, want_dres: bool):
+        """Returns (dy, dres).  dres = dz * relu_mask (gradient of the residual branch); `mask` is the bit mask
+        written by the forward pass (None for a BN that is not followed by a ReLU)."""
         rows = y.numel() // bn.C
         ds = self.dstats[bn.slot: bn.slot + 2 * bn.C]
         v = lambda t: None if t is None else t.view(rows, bn.C)    # noqa: E731
-        ops.bn_bwd_reduce(v(dz), v(z), v(y), bn.mean, bn.rstd, ds)
+        ops.bn_bwd_reduce(v(dz), None, v(y), bn.mean, bn.rstd, ds, relu_mask=mask)
         world = self._sync_stats(ds)
         dy = self._new(*y.shape)
         dres = self._new(*y.shape) if want_dres else None
-        ops.bn_bwd_apply(v(dz), v(z), v(y), v(dy), v(dres), bn.mean, bn.rstd, bn.gamma, ds, rows * world, bn.dgamma,
-                         bn.dbeta)
+        ops.bn_bwd_apply(v(dz), None, v(y), v(dy), v(dres), bn.mean, bn.rstd, bn.gamma, ds, rows * world, bn.dgamma,
+                         bn.dbeta, relu_mask=mask)
         return dy, dres
 
     def _conv_bwd(self, cv: _ConvPlan, x: torch.Tensor, dy: torch.Tensor, need_dx: bool = True):
@@ -428,16 +434,16 @@ class NativeResNetEngine:
         return dx
 
     def _block_bwd(self, b: _BlockPlan, sv, dout: torch.Tensor) -> torch.Tensor:
-        x, y1, z1, y2, z2, y3, yd, out = sv
-        dy3, dres = self._bn_bwd(b.bn3, dout, out, y3, want_dres=True)
+        x, y1, z1, m1, y2, z2, m2, y3, yd, m3 = sv
+        dy3, dres = self._bn_bwd(b.bn3, dout, m3, y3, want_dres=True)
         self._ready(*b.bn3.pindex)
         dz2 = self._conv_bwd(b.conv3, z2, dy3)
         self._ready(b.conv3.pindex)
-        dy2, _ = self._bn_bwd(b.bn2, dz2, z2, y2, want_dres=False)
+        dy2, _ = self._bn_bwd(b.bn2, dz2, m2, y2, want_dres=False)
         self._ready(*b.bn2.pindex)
         dz1 = self._conv_bwd(b.conv2, z1, dy2)
         self._ready(b.conv2.pindex)
-        dy1, _ = self._bn_bwd(b.bn1, dz1, z1, y1, want_dres=False)
+        dy1, _ = self._bn_bwd(b.bn1, dz1, m1, y1, want_dres=False)
         self._ready(*b.bn1.pindex)
         dxa = self._conv_bwd(b.conv1, x, dy1)
         self._ready(b.conv1.pindex)
@@ -478,10 +484,10 @@ class NativeResNetEngine:
         return run
 
     def _seg_stem(self, plan: _StepPlan, st: dict) -> None:
-        col, y0, z0, argmax, _ = plan.saved[0]
+        col, y0, z0, argmax, m0, _ = plan.saved[0]
         dz0 = self._new(*z0.shape)
         ops.maxpool_bwd(st["d"], argmax, dz0)
-        dy0, _ = self._bn_bwd(self.stem_bn, dz0, z0, y0, want_dres=False)
+        dy0, _ = self._bn_bwd(self.stem_bn, dz0, m0, y0, want_dres=False)
         self._ready(*self.stem_bn.pindex)
         cv = self.stem_conv
         rows = col.shape[0]

@@ -3,6 +3,7 @@ from __future__ import annotations
 
 import ctypes
 import os
+import threading
 from typing import Optional
 
 import torch
@@ -68,11 +69,18 @@ def check(code: int, what: str) -> None:
 
 
 _launches = 0
+_tls = threading.local()
 
 
 def count_launch(n: int = 1) -> None:
     global _launches
     _launches += n
+    _tls.n = getattr(_tls, "n", 0) + n
+
+
+def thread_launch_count() -> int:
+    """Launches issued by the calling thread (CUDA-graph capture runs per thread in the DataParallel mode)."""
+    return getattr(_tls, "n", 0)
 
 
 def launch_count() -> int:

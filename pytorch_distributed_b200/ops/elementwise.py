@@ -103,11 +103,11 @@ def bn_stats(x2d: torch.Tensor, sums: torch.Tensor, scratch: Optional[torch.Tens
 
 
 def bn_apply(x, residual, y, sums, count, gamma, beta, eps, momentum, running_mean, running_var, nbt, save_mean,
-             save_rstd, relu: bool) -> None:
+             save_rstd, relu: bool, relu_mask=None) -> None:
     rows, C = x.shape
     check(require().pdb_bn_apply(ptr(x), ptr(residual), ptr(y), dtype_tag(x.dtype), rows, C, ptr(sums), float(count),
                                  ptr(gamma), ptr(beta), eps, momentum, ptr(running_mean), ptr(running_var), ptr(nbt),
-                                 ptr(save_mean), ptr(save_rstd), int(relu), _st(x)), "pdb_bn_apply")
+                                 ptr(save_mean), ptr(save_rstd), int(relu), ptr(relu_mask), _st(x)), "pdb_bn_apply")
     count_launch()
 
 
@@ -119,16 +119,16 @@ def bn_apply_eval(x, residual, y, running_mean, running_var, gamma, beta, eps, r
     count_launch()
 
 
-def bn_bwd_reduce(dz, z, x, mean, rstd, dsums) -> None:
+def bn_bwd_reduce(dz, z, x, mean, rstd, dsums, relu_mask=None) -> None:
     rows, C = x.shape
-    check(require().pdb_bn_bwd_reduce(ptr(dz), ptr(z), ptr(x), dtype_tag(x.dtype), rows, C, ptr(mean), ptr(rstd),
-                                      ptr(dsums), _st(x)), "pdb_bn_bwd_reduce")
+    check(require().pdb_bn_bwd_reduce(ptr(dz), ptr(z), ptr(relu_mask), ptr(x), dtype_tag(x.dtype), rows, C, ptr(mean),
+                                      ptr(rstd), ptr(dsums), _st(x)), "pdb_bn_bwd_reduce")
     count_launch()
 
 
-def bn_bwd_apply(dz, z, x, dx, dres, mean, rstd, gamma, dsums, count, dgamma, dbeta) -> None:
+def bn_bwd_apply(dz, z, x, dx, dres, mean, rstd, gamma, dsums, count, dgamma, dbeta, relu_mask=None) -> None:
     rows, C = x.shape
-    check(require().pdb_bn_bwd_apply(ptr(dz), ptr(z), ptr(x), ptr(dx), ptr(dres), dtype_tag(x.dtype), rows, C,
+    check(require().pdb_bn_bwd_apply(ptr(dz), ptr(z), ptr(relu_mask), ptr(x), ptr(dx), ptr(dres), dtype_tag(x.dtype), rows, C,
                                      ptr(mean), ptr(rstd), ptr(gamma), ptr(dsums), float(count), ptr(dgamma),
                                      ptr(dbeta), _st(x)), "pdb_bn_bwd_apply")
     count_launch()

@@ -91,7 +91,12 @@ def test_bn_forward(dt, rows, C):
     nbt = torch.zeros((), dtype=torch.int64, device="cuda")
     mean, rstd = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
     y = torch.empty_like(x)
-    ops.bn_apply(x, res, y, sums, rows, gamma, beta, 1e-5, 0.1, rm, rv, nbt, mean, rstd, True)
+    pow2 = (C & (C - 1)) == 0
+    bits = torch.zeros(rows * C // 8, dtype=torch.uint8, device="cuda") if pow2 else None
+    ops.bn_apply(x, res, y, sums, rows, gamma, beta, 1e-5, 0.1, rm, rv, nbt, mean, rstd, True, relu_mask=bits)
+    if pow2:       # bit k of byte i <-> element 8*i + k passed the ReLU
+        want = ((y.reshape(-1, 8) > 0).to(torch.int32) << torch.arange(8, device="cuda", dtype=torch.int32)).sum(1)
+        assert torch.equal(bits.to(torch.int32), want)
     rrm, rrv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
     ref = F.batch_norm(xf, rrm, rrv, gamma, beta, True, 0.1, 1e-5)
     ref = F.relu(ref + res.float())
@@ -126,6 +131,14 @@ def test_bn_backward(dt, rows, C, with_z):
     dx, dres = torch.empty_like(x), torch.empty_like(x)
     dgamma, dbeta = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
     ops.bn_bwd_apply(dz, zt, x, dx, dres, mean, rstd, gamma, dsums, rows, dgamma, dbeta)
+    if with_z:     # the bit-mask variant must agree with the z-based one
+        bits = ((zt.reshape(-1, 8) > 0).to(torch.int32) << torch.arange(8, device="cuda", dtype=torch.int32)).sum(1).to(torch.uint8)
+        ds2 = torch.zeros(2 * C, device="cuda")
+        ops.bn_bwd_reduce(dz, None, x, mean, rstd, ds2, relu_mask=bits)
+        assert rel_err(ds2, dsums) < 1e-4
+        dx2, dres2 = torch.empty_like(x), torch.empty_like(x)
+        ops.bn_bwd_apply(dz, None, x, dx2, dres2, mean, rstd, gamma, dsums, rows, None, None, relu_mask=bits)
+        assert torch.equal(dx2, dx) and torch.equal(dres2, dres)
     tol = 2e-2 if dt == torch.bfloat16 else 4e-3
     assert rel_err(dgamma, gr.grad) < tol and rel_err(dbeta, br.grad) < tol
     assert rel_err(dx, xr.grad) < tol
