@@ -37,8 +37,10 @@ __device__ __forceinline__ void reduce_rows(const T* __restrict__ a, const T* __
     }
   }
   constexpr int U = 4;                     // rows in flight per thread
-  const int64_t rstride = (int64_t)gridDim.x * ry;
-  for (int64_t r0 = (int64_t)blockIdx.x * ry + ty; r0 < rows; r0 += rstride * U) {
+  // a block walks slabs of U*ry ADJACENT rows (U*ry*C*2 bytes contiguous per stream, >= 16 KB): DRAM likes
+  // long contiguous bursts far better than U scattered 4 KB pieces
+  const int64_t rstride = ry;
+  for (int64_t r0 = (int64_t)blockIdx.x * ry * U + ty; r0 < rows; r0 += (int64_t)gridDim.x * ry * U) {
     uint4 va[U], vx[U], vz[U];
     uint32_t vb[U];
 #pragma unroll
@@ -449,7 +451,7 @@ static void reduce_geometry(int C, int* cx, int* ry) {
 }
 
 static int reduce_grid(int64_t rows, int ry) {
-  int64_t want = (rows + ry - 1) / ry;
+  int64_t want = (rows + (int64_t)ry * 4 - 1) / ((int64_t)ry * 4);      // a block walks slabs of 4*ry rows
   int64_t cap = (int64_t)num_sms() * 4;
   return (int)(want < cap ? (want > 0 ? want : 1) : cap);
 }

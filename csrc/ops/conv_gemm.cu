@@ -59,6 +59,7 @@ struct FpropParams {
   int taps, cin_blocks, S;
   int P, Q, stride, pad;
   int a_im2col;
+  int accumulate;      // epilogue adds the tile into y (TMA reduction store) instead of overwriting it
   FastDiv div_pq, div_q;
   float* stats;        // [2N]: sum | sumsq, accumulated with atomics; may be null
   const float* bias;   // [N]; may be null
@@ -270,7 +271,12 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       if (leader) {
 #pragma unroll
         for (int j = 0; j < BLOCK_N / 64; ++j)
-          if (n0 + j * 64 < p.N) tma_store_2d(&tmD, out_stage + j * 16384, n0 + j * 64, m_blk * BLOCK_M);
+          if (n0 + j * 64 < p.N) {
+            if (p.accumulate)
+              tma_reduce_add_2d(&tmD, out_stage + j * 16384, n0 + j * 64, m_blk * BLOCK_M);
+            else
+              tma_store_2d(&tmD, out_stage + j * 16384, n0 + j * 64, m_blk * BLOCK_M);
+          }
         tma_store_commit();
       }
       if (p.stats) {
@@ -614,7 +620,8 @@ static int launch_wgrad(const CUtensorMap& a, const CUtensorMap& b, const WgradP
 using namespace pdb;
 
 extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, const pdb_conv_shape* s, int64_t lda,
-                              int64_t ldd, float* stats, const float* bias, int block_n, void* stream) {
+                              int64_t ldd, float* stats, const float* bias, int block_n, int accumulate,
+                              void* stream) {
   PDB_CHECK_ARG(x && w && y && s, "pdb_conv_fprop: null pointer");
   PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16, "pdb_conv_fprop: dtype must be PDB_BF16 or PDB_FP16");
   if (int e = load_driver_fns()) return e;
@@ -637,6 +644,7 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
   p.taps = s->R * s->S, p.cin_blocks = (s->C + BLOCK_K - 1) / BLOCK_K, p.S = s->S;
   p.P = P, p.Q = Q, p.stride = s->stride, p.pad = s->pad;
   p.a_im2col = plain ? 0 : 1;
+  p.accumulate = accumulate ? 1 : 0;
   p.div_pq.init((uint32_t)(P * Q)), p.div_q.init((uint32_t)Q);
   p.stats = stats, p.bias = bias;
 

@@ -155,10 +155,12 @@ typedef struct {
  * row pitch in elements of x (plain 1x1 path only) and y; <= 0 means dense.  stats (nullable):
  * fp32 [2K], per-channel sum | sum of squares of the rounded outputs are ADDED to it (zero it
  * first) — the BatchNorm statistics pass fused into the epilogue.  bias (nullable): fp32 [K].
- * block_n: 64 / 128 / 256, or 0 for the default heuristic.  dgrad is the same call on dY with the
+ * block_n: 64 / 128 / 256, or 0 for the default heuristic.  accumulate != 0: y += conv(x, w) through a TMA
+ * reduction store (the residual-branch gradient is summed in the dgrad epilogue instead of by a separate
+ * elementwise kernel).  dgrad is the same call on dY with the
  * weights rearranged by pdb_weight_dgrad_layout. */
 int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, const pdb_conv_shape* s, int64_t lda,
-                   int64_t ldd, float* stats, const float* bias, int block_n, void* stream);
+                   int64_t ldd, float* stats, const float* bias, int block_n, int accumulate, void* stream);
 
 /* dw[K, R*S*C] (fp32, row pitch ldw) += dy[N*P*Q, K]^T * im2col(x).  The pixel range is split over
  * CTAs (`splits`, 0 = heuristic) and partial tiles are added with fp32 vector reductions, so dw

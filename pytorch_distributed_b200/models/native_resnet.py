@@ -413,8 +413,10 @@ class NativeResNetEngine:
                          bn.dbeta, relu_mask=mask)
         return dy, dres
 
-    def _conv_bwd(self, cv: _ConvPlan, x: torch.Tensor, dy: torch.Tensor, need_dx: bool = True):
-        """wgrad into the arena; returns dx (same spatial size as x) when requested."""
+    def _conv_bwd(self, cv: _ConvPlan, x: torch.Tensor, dy: torch.Tensor, need_dx: bool = True, into=None):
+        """wgrad into the arena; returns dx (same spatial size as x) when requested.  `into`: an existing
+        gradient buffer of dx's shape that the dgrad result is ADDED to in the GEMM epilogue (TMA reduction
+        store) — how the two branches of a residual block are summed without a separate elementwise pass."""
         N, H, W, _ = x.shape
         ops.conv_wgrad(x, dy, cv.dw, cv.shape(N, H, W))
         if not need_dx:
@@ -422,8 +424,8 @@ class NativeResNetEngine:
         _, P, Q, _ = dy.shape
         if cv.R == 1:
             # 1x1: plain GEMM on the (possibly strided-compact) pixel set
-            dx = self._new(N, P, Q, cv.C)
-            ops.conv_fprop(dy, cv.wt16, dx, ConvShape(N, P, Q, cv.K, cv.C, 1, 1, 1, 0))
+            dx = into if into is not None else self._new(N, P, Q, cv.C)
+            ops.conv_fprop(dy, cv.wt16, dx, ConvShape(N, P, Q, cv.K, cv.C, 1, 1, 1, 0), accumulate=into is not None)
             return dx            # compact [N, P, Q, C]; the caller scatters it if stride == 2
         if cv.stride == 2:
             up = self._new(N, H, W, cv.K)
@@ -445,20 +447,23 @@ class NativeResNetEngine:
         self._ready(b.conv2.pindex)
         dy1, _ = self._bn_bwd(b.bn1, dz1, m1, y1, want_dres=False)
         self._ready(*b.bn1.pindex)
+        if b.convd is None:
+            # identity shortcut: dx = dgrad(conv1) + dres, summed in the GEMM epilogue on top of dres
+            dx = self._conv_bwd(b.conv1, x, dy1, into=dres)
+            self._ready(b.conv1.pindex)
+            return dx
         dxa = self._conv_bwd(b.conv1, x, dy1)
         self._ready(b.conv1.pindex)
-        dx = self._new(*dxa.shape)
-        if b.convd is None:
-            ops.add16(dxa, dres, dx)
-        else:
-            dyd, _ = self._bn_bwd(b.bnd, dres, None, yd, want_dres=False)
-            self._ready(*b.bnd.pindex)
+        dyd, _ = self._bn_bwd(b.bnd, dres, None, yd, want_dres=False)
+        self._ready(*b.bnd.pindex)
+        if b.convd.stride == 2:
             dxd = self._conv_bwd(b.convd, x, dyd)
             self._ready(b.convd.pindex)
-            if b.convd.stride == 2:
-                ops.add_strided2(dxa, dxd, dx)
-            else:
-                ops.add16(dxa, dxd, dx)
+            dx = self._new(*dxa.shape)
+            ops.add_strided2(dxa, dxd, dx)
+            return dx
+        dx = self._conv_bwd(b.convd, x, dyd, into=dxa)       # stride-1 projection (layer1.0): same trick
+        self._ready(b.convd.pindex)
         return dx
 
     # The backward pass as a list of segments (head, one per bottleneck in reverse, stem).  Each segment is a

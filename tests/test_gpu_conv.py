@@ -40,3 +40,21 @@ def test_dgrad(case):
 def test_wgrad(case):
     N, H, W, C, K, R, S, stride, pad, bn = case
     assert wgrad_case(N, H, W, C, K, R, S, stride, pad, block_n=bn) < 5e-3
+
+
+def test_fprop_accumulate_epilogue():
+    """y += conv(x, w) through the TMA reduction store (how residual gradients are summed)."""
+    import torch.nn.functional as F
+    from pytorch_distributed_b200 import ops
+    from pytorch_distributed_b200.ops import ConvShape
+    from ._gpu_helpers import rel_err
+    g = torch.Generator(device="cuda").manual_seed(7)
+    N, H, C, K = 3, 14, 256, 1024
+    x = torch.randn(N, H, H, C, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(K, 1, 1, C, device="cuda", generator=g) / C ** 0.5).bfloat16()
+    y0 = torch.randn(N, H, H, K, device="cuda", generator=g).bfloat16()
+    y = y0.clone()
+    ops.conv_fprop(x, w, y, ConvShape(N, H, H, C, K, 1, 1, 1, 0), accumulate=True)
+    torch.cuda.synchronize()
+    ref = y0.float() + (x.float().reshape(-1, C) @ w.float().reshape(K, C).t()).reshape(N, H, H, K)
+    assert rel_err(y, ref) < TOL
