@@ -139,34 +139,45 @@ __global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const float* __restri
 }
 
 // ---- stem im2col: [N,3,H,W] fp32 -> [N*Ho*Wo, Kpad] 16-bit, column = (kh*7 + kw)*3 + c -----------
-// A block handles a run of output pixels of one output row; the needed input rows are read through
-// L1/L2 (each input element is reused by up to 16 patches).  One thread writes 8 columns (128 bit).
+// One block per output row (n, ho): the 7 input rows x 3 channels it needs are staged in shared memory with
+// coalesced loads (zero halo included), then every thread assembles 128-bit output vectors from smem through a
+// per-column offset table — no per-element div/mod, no scattered global loads, fully coalesced 34 KB of writes
+// per block.  (The first version did the gather straight from global memory: 1.76 ms; this one is bandwidth
+// bound on the 1.5 GB it writes.)
+constexpr int kStemTaps = 7, kStemK = 147, kStemHalo = 3;
 template <typename T>
 __global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restrict__ x, T* __restrict__ col, int N,
                                                           int H, int W, int Ho, int Wo, int Kpad) {
-  const int kvec = Kpad / 8;
-  const int64_t total = (int64_t)N * Ho * Wo * kvec, stride = (int64_t)gridDim.x * blockDim.x;
+  extern __shared__ float srows[];                 // [7*3][pitch] input rows with a zero halo of 3 on both sides
+  __shared__ short off_tab[160];                   // column kk -> (kh*3 + c)*pitch + kw
+  const int pitch = W + 2 * kStemHalo + 2;
+  const int n = blockIdx.x / Ho, ho = blockIdx.x - n * Ho;
+  for (int kk = threadIdx.x; kk < 160; kk += blockDim.x) {
+    const int c = kk % 3, tap = kk / 3, kw = tap % kStemTaps, kh = tap / kStemTaps;
+    off_tab[kk] = kk < kStemK ? (short)((kh * 3 + c) * pitch + kw) : (short)-1;
+  }
   const int64_t HW = (int64_t)H * W;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int kv = (int)(i % kvec);
-    int64_t t = i / kvec;
-    const int wo = (int)(t % Wo);
-    t /= Wo;
-    const int ho = (int)(t % Ho);
-    const int n = (int)(t / Ho);
+  for (int i = threadIdx.x; i < kStemTaps * 3 * pitch; i += blockDim.x) {
+    const int rc = i / pitch, wp = i - rc * pitch;           // rc = kh*3 + c
+    const int kh = rc / 3, c = rc - kh * 3;
+    const int h = 2 * ho - kStemHalo + kh, w = wp - kStemHalo;
+    float v = 0.f;
+    if (h >= 0 && h < H && w >= 0 && w < W) v = __ldg(x + ((int64_t)n * 3 + c) * HW + (int64_t)h * W + w);
+    srows[i] = v;
+  }
+  __syncthreads();
+  const int kvec = Kpad / 8;
+  T* out = col + ((int64_t)n * Ho + ho) * Wo * Kpad;
+  for (int i = threadIdx.x; i < Wo * kvec; i += blockDim.x) {
+    const int wo = i / kvec, kv = i - wo * kvec;
+    const float* base = srows + 2 * wo;                      // window of pixel wo starts at smem column 2*wo
     float f[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const int kk = kv * 8 + k;
-      float v = 0.f;
-      if (kk < 147) {
-        const int c = kk % 3, tap = kk / 3, kw = tap % 7, kh = tap / 7;
-        const int h = 2 * ho - 3 + kh, w = 2 * wo - 3 + kw;
-        if (h >= 0 && h < H && w >= 0 && w < W) v = __ldg(x + ((int64_t)n * 3 + c) * HW + (int64_t)h * W + w);
-      }
-      f[k] = v;
+      const int o = off_tab[kv * 8 + k];
+      f[k] = o >= 0 ? base[o] : 0.f;
     }
-    stg128(col + i * 8, pack8<T>(f));
+    stg128(out + (int64_t)i * 8, pack8<T>(f));
   }
 }
 
@@ -290,9 +301,11 @@ extern "C" int pdb_nchw_f32_to_nhwc16(const float* x, void* y, int dtype, int N,
 
 extern "C" int pdb_stem_im2col(const float* x, void* col, int dtype, int N, int H, int W, int Kpad, void* stream) {
   PDB_CHECK_ARG(x && col && N > 0 && H > 0 && W > 0 && Kpad >= 147 && Kpad % 8 == 0, "pdb_stem_im2col: bad arguments");
+  PDB_CHECK_ARG(Kpad <= 160, "pdb_stem_im2col: Kpad must be <= 160");
   const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
-  const int64_t total = (int64_t)N * Ho * Wo * (Kpad / 8);
-  PDB_DISPATCH_16(dtype, T, (stem_im2col_kernel<T><<<ew_grid(total), 256, 0, ST>>>(x, (T*)col, N, H, W, Ho, Wo, Kpad)));
+  const size_t smem = (size_t)7 * 3 * (W + 8) * sizeof(float);
+  PDB_CHECK_ARG(smem <= 48 * 1024, "pdb_stem_im2col: image width %d too large for the row staging buffer", W);
+  PDB_DISPATCH_16(dtype, T, (stem_im2col_kernel<T><<<N * Ho, 256, smem, ST>>>(x, (T*)col, N, H, W, Ho, Wo, Kpad)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
