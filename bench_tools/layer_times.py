@@ -57,6 +57,15 @@ def main():
                 flops = 2.0 * s.N * ((s.H + 2 * s.pad - s.R) // s.stride + 1) * ((s.W + 2 * s.pad - s.S) // s.stride + 1) * s.K * s.C * s.R * s.S
             else:
                 flops = 0.0
+                if name.startswith("bn_") or name in ("maxpool_fwd", "maxpool_bwd", "add_strided2", "avgpool_bwd"):
+                    t = a[2] if name in ("bn_bwd_reduce", "bn_bwd_apply") else a[0]
+                    tag = f"{name} {tuple(t.shape)}" + (" +res" if name == "bn_apply" and a[1] is not None else "") \
+                        + (" +dres" if name == "bn_bwd_apply" and a[4] is not None else "")
+                    # bytes moved (16-bit streams): for a GB/s column
+                    n = t.numel()
+                    streams = {"bn_apply": 2 + (a[1] is not None), "bn_bwd_reduce": 2.06,
+                               "bn_bwd_apply": 3.06 + (a[4] is not None if name == "bn_bwd_apply" else 0)}.get(name, 0)
+                    flops = -2.0 * n * streams          # negative => bytes, reported as GB/s
             records.append((name, tag, e0, e1, flops))
             return r
         return inner
@@ -83,10 +92,12 @@ def main():
         t[0] += 1; t[1] += ms; t[2] += flops
     total = a0.elapsed_time(a1)
     out = {"batch": args.batch, "step_ms_serialised": total, "launches": len(records),
-           "by_class": {k: {"n": v[0], "ms": round(v[1], 3), "tflops": round(v[2] / v[1] / 1e9, 1) if v[1] > 0 and v[2] else None}
+           "by_class": {k: {"n": v[0], "ms": round(v[1], 3), "tflops": round(v[2] / v[1] / 1e9, 1) if v[1] > 0 and v[2] > 0 else None}
                         for k, v in sorted(by_class.items(), key=lambda kv: -kv[1][1])},
-           "by_shape": {k: {"n": v[0], "ms": round(v[1], 3), "tflops": round(v[2] / v[1] / 1e9, 1) if v[1] > 0 and v[2] else None}
-                        for k, v in sorted(by_tag.items(), key=lambda kv: -kv[1][1])[:60]}}
+           "by_shape": {k: {"n": v[0], "ms": round(v[1], 3),
+                            "tflops": round(v[2] / v[1] / 1e9, 1) if v[1] > 0 and v[2] > 0 else None,
+                            "GBps": round(-v[2] / v[1] / 1e6, 0) if v[1] > 0 and v[2] < 0 else None}
+                        for k, v in sorted(by_tag.items(), key=lambda kv: -kv[1][1])[:90]}}
     os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
     with open(args.out, "w") as f:
         json.dump(out, f, indent=1)

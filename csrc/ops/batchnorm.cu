@@ -448,9 +448,18 @@ static void reduce_geometry(int C, int* cx, int* ry) {
   *ry = kThreads / x;
 }
 
-static int reduce_grid(int64_t rows, int ry) {
+// Persistent grid-stride kernels must be launched as exactly ONE wave: with more blocks than can be resident the
+// leftover blocks run alone on a mostly idle GPU (3 blocks/SM resident and a grid of 4/SM = 1.33 waves cost 4 %).
+template <typename K>
+static int resident_blocks(K kernel, size_t smem) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, smem) != cudaSuccess || per_sm < 1) per_sm = 2;
+  return per_sm * num_sms();
+}
+
+static int reduce_grid(int64_t rows, int ry, int cap = 0) {
   int64_t want = (rows + (int64_t)ry * 4 - 1) / ((int64_t)ry * 4);      // a block walks slabs of 4*ry rows
-  int64_t cap = (int64_t)num_sms() * 4;
+  if (cap <= 0) cap = num_sms() * 4;
   return (int)(want < cap ? (want > 0 ? want : 1) : cap);
 }
 
@@ -518,8 +527,10 @@ extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* r
                 (long long)rows, C);
   int cx, ry;
   reduce_geometry(C, &cx, &ry);
-  const int grid = reduce_grid(rows, ry);
   const size_t smem = (size_t)kThreads * 16 * sizeof(float);
+  static int cap = 0;
+  if (cap == 0) cap = resident_blocks(bn_bwd_reduce_kernel<__nv_bfloat16, 2>, smem);
+  const int grid = reduce_grid(rows, ry, cap);
   cudaStream_t st = (cudaStream_t)stream;
   PDB_DISPATCH_16(dtype, T, {
     if (relu_mask)
