@@ -234,16 +234,25 @@ __global__ void __launch_bounds__(kThreads) bn_stats_sync_kernel(const T* __rest
   }
 }
 
+// Every block ends by adding its per-channel partials to global memory.  Hundreds of blocks hitting the same 2C
+// addresses serialise in the L2 atomic units (~100 ns per atomic per address: 45 us per launch with 444 blocks,
+// more than the data movement of the small layers).  With `rep` the adds are spread over kReduceReplicas copies
+// (block b -> copy b % R), and the last block to finish (ticket) folds the copies into dsums.
+constexpr int kReduceReplicas = 16;
+
 template <typename T, int kMask>
 __global__ void __launch_bounds__(kThreads, 3) bn_bwd_reduce_kernel(const T* __restrict__ dz, const T* __restrict__ z,
-                                                                 const uint8_t* __restrict__ bits,
-                                                                 const T* __restrict__ x, int64_t rows, int C, int cx,
-                                                                 int ry, const float* __restrict__ mean,
-                                                                 const float* __restrict__ rstd,
-                                                                 float* __restrict__ dsums) {
+                                                                    const uint8_t* __restrict__ bits,
+                                                                    const T* __restrict__ x, int64_t rows, int C, int cx,
+                                                                    int ry, const float* __restrict__ mean,
+                                                                    const float* __restrict__ rstd,
+                                                                    float* __restrict__ dsums, float* __restrict__ rep,
+                                                                    unsigned int* __restrict__ ticket) {
   extern __shared__ float smem[];
+  __shared__ bool is_last;
   const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
   const int ncg = C / 8;
+  float* target = rep ? rep + (size_t)(blockIdx.x % kReduceReplicas) * 2 * C : dsums;
   for (int cg = tx; cg < ncg; cg += cx) {
     float s0[8] = {0}, s1[8] = {0};
     if (ty < ry) reduce_rows<T, 1, kMask>(dz, z, bits, x, rows, C, cg, cx, ry, ty, mean, rstd, s0, s1);
@@ -252,10 +261,23 @@ __global__ void __launch_bounds__(kThreads, 3) bn_bwd_reduce_kernel(const T* __r
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const int c = cg * 8 + k;
-        atomicAdd(dsums + c, s0[k]);
-        atomicAdd(dsums + C + c, rstd[c] * (s1[k] - mean[c] * s0[k]));     // block-local sum(g * xhat)
+        atomicAdd(target + c, s0[k]);
+        atomicAdd(target + C + c, rstd[c] * (s1[k] - mean[c] * s0[k]));     // block-local sum(g * xhat)
       }
     }
+  }
+  if (rep == nullptr) return;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
+    float acc = 0.f;
+#pragma unroll
+    for (int r = 0; r < kReduceReplicas; ++r) acc += __ldcg(rep + (size_t)r * 2 * C + c);
+    dsums[c] = acc;
   }
 }
 
@@ -519,10 +541,14 @@ extern "C" int pdb_bn_stats_sync(const void* x, int dtype, int64_t rows, int C, 
   return 0;
 }
 
+extern "C" size_t pdb_bn_bwd_reduce_scratch_floats(int C) { return (size_t)kReduceReplicas * 2 * C + 32; }
+
 extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, int dtype,
                                  int64_t rows, int C, const float* mean, const float* rstd, float* dsums,
-                                 void* stream) {
+                                 float* scratch, void* stream) {
   PDB_CHECK_ARG(dz && x && mean && rstd && dsums, "pdb_bn_bwd_reduce: null pointer");
+  float* rep = scratch;
+  unsigned int* ticket = scratch ? reinterpret_cast<unsigned int*>(scratch + (size_t)kReduceReplicas * 2 * C) : nullptr;
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_bwd_reduce: bad shape rows=%lld C=%d",
                 (long long)rows, C);
   int cx, ry;
@@ -535,13 +561,13 @@ extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* r
   PDB_DISPATCH_16(dtype, T, {
     if (relu_mask)
       bn_bwd_reduce_kernel<T, 2><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, relu_mask, (const T*)x, rows, C,
-                                                               cx, ry, mean, rstd, dsums);
+                                                               cx, ry, mean, rstd, dsums, rep, ticket);
     else if (z)
       bn_bwd_reduce_kernel<T, 1><<<grid, kThreads, smem, st>>>((const T*)dz, (const T*)z, nullptr, (const T*)x, rows, C,
-                                                               cx, ry, mean, rstd, dsums);
+                                                               cx, ry, mean, rstd, dsums, rep, ticket);
     else
       bn_bwd_reduce_kernel<T, 0><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, nullptr, (const T*)x, rows, C, cx,
-                                                               ry, mean, rstd, dsums);
+                                                               ry, mean, rstd, dsums, rep, ticket);
   });
   PDB_LAUNCH_CHECK();
   return 0;

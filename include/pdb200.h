@@ -106,9 +106,14 @@ int pdb_bn_apply_eval(const void* x, const void* residual, void* y, int dtype, i
 
 /* Backward reductions: with g = dz masked by the ReLU (relu_mask bits if given, else z > 0 if z is
  * given, else unmasked), dsums[0:C] += sum g, dsums[C:2C] += sum g * (x - mean) * rstd.  dsums must be
- * zeroed by the caller. */
+ * zeroed by the caller.
+ * scratch (nullable): pdb_bn_bwd_reduce_scratch_floats(C) ZEROED floats; when given, the per-block partials are
+ * spread over 16 replicas and folded by the last block (dsums is then overwritten, not accumulated) — this
+ * removes the atomic contention that otherwise costs ~45 us per launch. */
+size_t pdb_bn_bwd_reduce_scratch_floats(int C);
 int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, int dtype,
-                      int64_t rows, int C, const float* mean, const float* rstd, float* dsums, void* stream);
+                      int64_t rows, int C, const float* mean, const float* rstd, float* dsums, float* scratch,
+                      void* stream);
 
 /* dx = gamma*rstd * (g - dsums[c]/count - xhat * dsums[C+c]/count);  optionally also writes
  * dres = g (gradient of the residual branch).  Block 0 accumulates dgamma += dsums[C:], dbeta +=

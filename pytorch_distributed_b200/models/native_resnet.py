@@ -68,6 +68,9 @@ class _BNPlan:
         self.running_mean, self.running_var = bn.running_mean, bn.running_var
         self.nbt = bn.num_batches_tracked
         self.slot = slot                 # offset (floats) of this layer's [2C] block in the stats buffers
+        self.rslot = eng._scratch_floats  # offset of this layer's replica scratch for the backward reduction
+        self.rsize = ops.bn_bwd_reduce_scratch_floats(self.C)
+        eng._scratch_floats += self.rsize
         self.mean = torch.empty(self.C, dtype=torch.float32, device=eng.device)
         self.rstd = torch.empty(self.C, dtype=torch.float32, device=eng.device)
 
@@ -138,6 +141,7 @@ class NativeResNetEngine:
         self.arena.ensure_shadow(dtype)
         self.pindex: Dict[str, int] = {e.name: i for i, e in enumerate(self.arena.entries)}
         self._stat_floats = 0
+        self._scratch_floats = 0
         self.ddp = None
         import os
         self.graphs = os.environ.get("PDB200_GRAPHS", "1") != "0" and not sync_bn
@@ -164,7 +168,8 @@ class NativeResNetEngine:
         self.fc_db = self.arena.grad_view("fc.bias")
         self.fc_pindex = (self.pindex["fc.weight"], self.pindex["fc.bias"])
         self.stats = torch.zeros(self._stat_floats, dtype=torch.float32, device=self.device)
-        self.dstats = torch.zeros(self._stat_floats, dtype=torch.float32, device=self.device)
+        # backward: [dsums of every BN | replica scratch + tickets of every BN], zeroed once per backward pass
+        self.dstats = torch.zeros(self._stat_floats + self._scratch_floats, dtype=torch.float32, device=self.device)
         self._anchor = model.fc.bias
         self._convs: List[_ConvPlan] = [self.stem_conv] + [c for b in self.blocks for c in
                                                            (b.conv1, b.conv2, b.conv3, b.convd) if c is not None]
@@ -405,7 +410,9 @@ class NativeResNetEngine:
         rows = y.numel() // bn.C
         ds = self.dstats[bn.slot: bn.slot + 2 * bn.C]
         v = lambda t: None if t is None else t.view(rows, bn.C)    # noqa: E731
-        ops.bn_bwd_reduce(v(dz), None, v(y), bn.mean, bn.rstd, ds, relu_mask=mask)
+        r0 = self._stat_floats + bn.rslot
+        scratch = self.dstats[r0: r0 + bn.rsize]
+        ops.bn_bwd_reduce(v(dz), None, v(y), bn.mean, bn.rstd, ds, relu_mask=mask, scratch=scratch)
         world = self._sync_stats(ds)
         dy = self._new(*y.shape)
         dres = self._new(*y.shape) if want_dres else None

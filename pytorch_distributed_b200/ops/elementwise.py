@@ -11,7 +11,7 @@ from ._lib import check, count_launch, ptr, require, stream_ptr
 from ._sigs import ConvShape
 
 __all__ = ["dtype_tag", "sgd_step", "check_finite", "cast_to_16", "xent_fwd_bwd", "topk_correct", "bn_stats",
-           "bn_apply", "bn_apply_eval", "bn_bwd_reduce", "bn_bwd_apply", "maxpool_fwd", "maxpool_bwd",
+           "bn_apply", "bn_apply_eval", "bn_bwd_reduce", "bn_bwd_reduce_scratch_floats", "bn_bwd_apply", "maxpool_fwd", "maxpool_bwd",
            "avgpool_fwd", "avgpool_bwd", "nchw_to_nhwc16", "stem_im2col", "add16", "upsample2_zero",
            "add_strided2", "conv_fprop", "conv_wgrad", "weight_dgrad_layout", "weight_dgrad_layout_batched", "pad_rows16", "colsum16",
            "peer_copy", "peer_copy_", "reduce_to_root", "ConvShape"]
@@ -119,10 +119,14 @@ def bn_apply_eval(x, residual, y, running_mean, running_var, gamma, beta, eps, r
     count_launch()
 
 
-def bn_bwd_reduce(dz, z, x, mean, rstd, dsums, relu_mask=None) -> None:
+def bn_bwd_reduce_scratch_floats(C: int) -> int:
+    return int(require().pdb_bn_bwd_reduce_scratch_floats(C))
+
+
+def bn_bwd_reduce(dz, z, x, mean, rstd, dsums, relu_mask=None, scratch=None) -> None:
     rows, C = x.shape
     check(require().pdb_bn_bwd_reduce(ptr(dz), ptr(z), ptr(relu_mask), ptr(x), dtype_tag(x.dtype), rows, C, ptr(mean),
-                                      ptr(rstd), ptr(dsums), _st(x)), "pdb_bn_bwd_reduce")
+                                      ptr(rstd), ptr(dsums), ptr(scratch), _st(x)), "pdb_bn_bwd_reduce")
     count_launch()
 
 

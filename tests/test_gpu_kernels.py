@@ -136,6 +136,11 @@ def test_bn_backward(dt, rows, C, with_z):
         ds2 = torch.zeros(2 * C, device="cuda")
         ops.bn_bwd_reduce(dz, None, x, mean, rstd, ds2, relu_mask=bits)
         assert rel_err(ds2, dsums) < 1e-4
+        # replicated accumulators + last-block fold (the contention-free path the engine uses)
+        ds3 = torch.full((2 * C,), float("nan"), device="cuda")
+        scratch = torch.zeros(ops.bn_bwd_reduce_scratch_floats(C), device="cuda")
+        ops.bn_bwd_reduce(dz, None, x, mean, rstd, ds3, relu_mask=bits, scratch=scratch)
+        assert rel_err(ds3, dsums) < 1e-4
         dx2, dres2 = torch.empty_like(x), torch.empty_like(x)
         ops.bn_bwd_apply(dz, None, x, dx2, dres2, mean, rstd, gamma, dsums, rows, None, None, relu_mask=bits)
         assert torch.equal(dx2, dx) and torch.equal(dres2, dres)
