@@ -15,7 +15,15 @@ from pytorch_distributed_b200.ops import ConvShape  # noqa: E402
 def main():
     what = sys.argv[1] if len(sys.argv) > 1 else "fprop"
     N, dt = 400, torch.bfloat16
-    if what in ("fprop", "wgrad"):
+    if what == "fprop1x1":
+        H, C, K = 14, 256, 1024
+        x = torch.randn(N, H, H, C, device="cuda", dtype=dt)
+        w = torch.randn(K, 1, 1, C, device="cuda", dtype=dt) * 0.05
+        y = torch.empty(N, H, H, K, device="cuda", dtype=dt)
+        st = torch.zeros(2 * K, device="cuda")
+        for _ in range(6):
+            ops.conv_fprop(x, w, y, ConvShape(N, H, H, C, K, 1, 1, 1, 0), stats=st)
+    elif what in ("fprop", "wgrad"):
         H, C, K, R = 14, 256, 256, 3
         x = torch.randn(N, H, H, C, device="cuda", dtype=dt)
         sh = ConvShape(N, H, H, C, K, R, R, 1, 1)
