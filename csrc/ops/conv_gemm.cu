@@ -210,6 +210,19 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     constexpr int GPW = BLOCK_N / 64;                 // 32-column groups per warp (1, 2, 4)
     constexpr int BATCH = GPW < 2 ? GPW : 2;          // groups loaded from TMEM before one wait
     const int pair = tid_e % PAIRS, rg = tid_e / PAIRS;
+    const uint32_t out_stage_s = smem_u32(out_stage);
+    // statistics pass: this thread owns column pair `pair` and rows rg, rg+G, ...; G divides 8, so the swizzle
+    // term (row & 7) repeats every 8/G rows: its 8/G byte offsets are computed once, outside the row loop
+    constexpr int SWZ = 8 / G;
+    uint32_t st_off[SWZ];
+    {
+      const int col = pair * 2, chunk = (col & 63) >> 3;
+#pragma unroll
+      for (int i = 0; i < SWZ; ++i) {
+        const int r = rg + i * G;
+        st_off[i] = out_stage_s + (col >> 6) * 16384 + ((col & 7) << 1) + r * 128 + ((chunk ^ (r & 7)) << 4);
+      }
+    }
     float st_sum[2] = {0.f, 0.f}, st_sq[2] = {0.f, 0.f};
     int st_nblk = -1;
     int acc = 0;
@@ -250,7 +263,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               v[b][c] = __float_as_uint(__uint_as_float(v[b][c]) + (n < p.N ? __ldg(p.bias + n) : 0.f));
             }
           }
-          uint8_t* dst = out_stage + (g >> 1) * 16384 + row * 128;
+          const uint32_t dst = out_stage_s + (g >> 1) * 16384 + row * 128;
 #pragma unroll
           for (int c = 0; c < 4; ++c) {               // four 16-byte chunks of this group's half row
             uint4 w;
@@ -258,7 +271,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             w.y = pack2<kBf16>(__uint_as_float(v[b][8 * c + 2]), __uint_as_float(v[b][8 * c + 3]));
             w.z = pack2<kBf16>(__uint_as_float(v[b][8 * c + 4]), __uint_as_float(v[b][8 * c + 5]));
             w.w = pack2<kBf16>(__uint_as_float(v[b][8 * c + 6]), __uint_as_float(v[b][8 * c + 7]));
-            *reinterpret_cast<uint4*>(dst + ((((g & 1) * 4 + c) ^ (row & 7)) << 4)) = w;
+            sts128(dst + ((((g & 1) * 4 + c) ^ (row & 7)) << 4), w);
           }
         }
       }
@@ -282,15 +295,14 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       if (p.stats) {
         // per-channel sum / sum of squares of the ROUNDED outputs, read back from the staged tile
         // (rows past M are exact zeros: their A rows were zero-filled by TMA)
-        const int col = pair * 2;
-        const uint8_t* src = out_stage + (col >> 6) * 16384 + ((col & 7) << 1);
-        const int chunk = (col & 63) >> 3;
-#pragma unroll 8
-        for (int r = rg; r < BLOCK_M; r += G) {
-          const uint32_t w = *reinterpret_cast<const uint32_t*>(src + r * 128 + ((chunk ^ (r & 7)) << 4));
-          const float2 f = unpack2<kBf16>(w);
-          st_sum[0] += f.x, st_sum[1] += f.y;
-          st_sq[0] = fmaf(f.x, f.x, st_sq[0]), st_sq[1] = fmaf(f.y, f.y, st_sq[1]);
+#pragma unroll 4
+        for (int rb = 0; rb < BLOCK_M / 8; ++rb) {       // 8 rows per step: rows rg + 8*rb + i*G
+#pragma unroll
+          for (int i = 0; i < SWZ; ++i) {
+            const float2 f = unpack2<kBf16>(lds32(st_off[i] + rb * (8 * 128)));
+            st_sum[0] += f.x, st_sum[1] += f.y;
+            st_sq[0] = fmaf(f.x, f.x, st_sq[0]), st_sq[1] = fmaf(f.y, f.y, st_sq[1]);
+          }
         }
       }
       if ((acc ^= 1) == 0) acc_phase ^= 1;
