@@ -53,6 +53,8 @@ struct FastDiv {
   __device__ __forceinline__ uint32_t div(uint32_t n) const { return d <= 1 ? n : (__umulhi(n, mul) >> shr); }
 };
 
+constexpr int kStatReplicas = 16;
+
 struct FpropParams {
   int M, N;
   int num_m_blocks, num_n_blocks;
@@ -62,6 +64,9 @@ struct FpropParams {
   int accumulate;      // epilogue adds the tile into y (TMA reduction store) instead of overwriting it
   FastDiv div_pq, div_q;
   float* stats;        // [2N]: sum | sumsq, accumulated with atomics; may be null
+  float* stats_rep;    // optional kStatReplicas x [2N] spread accumulators (+ ticket word after them): CTA b adds
+                       // to copy b % R and the last CTA folds the copies into `stats` — hundreds of CTAs adding to
+                       // the same 2N addresses serialise in L2 (~100 ns each, 20-30 us per launch otherwise)
   const float* bias;   // [N]; may be null
 };
 
@@ -69,8 +74,9 @@ template <int BLOCK_N>
 struct FpropSmem {
   static constexpr uint32_t B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
   static constexpr uint32_t STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int kStages = BLOCK_N == 256 ? 3 : (BLOCK_N == 128 ? 5 : 6);
-  static constexpr uint32_t OUT_BYTES = (BLOCK_N / 64) * 16384;       // 128 rows x 128 B per 64-col chunk
+  static constexpr int PASS_N = BLOCK_N < 128 ? BLOCK_N : 128;        // columns staged per epilogue pass
+  static constexpr int kStages = BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8);
+  static constexpr uint32_t OUT_BYTES = (PASS_N / 64) * 16384;        // 128 rows x 128 B per 64-col chunk
   static constexpr uint32_t BAR_OFFSET = kStages * STAGE_BYTES + OUT_BYTES;
   static constexpr uint32_t TOTAL = BAR_OFFSET + 256 + 1024;           // barriers + alignment slack
 };
@@ -205,14 +211,18 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     const int row = quarter * 32 + lane;              // row of the 128-row tile owned by this thread
     const int tid_e = threadIdx.x - 64;               // 0..255
     const bool leader = tid_e == 0;
-    constexpr int PAIRS = BLOCK_N / 2;                // column pairs for the statistics pass
-    constexpr int G = kEpiThreads / PAIRS;            // row groups (2, 4, 8)
-    constexpr int GPW = BLOCK_N / 64;                 // 32-column groups per warp (1, 2, 4)
-    constexpr int BATCH = GPW < 2 ? GPW : 2;          // groups loaded from TMEM before one wait
+    // The tile leaves in passes of at most 128 columns: a 256-wide tile re-uses a 32 KB staging buffer twice
+    // instead of owning 64 KB, and the 32 KB saved buy one more pipeline stage — these kernels are bound by
+    // TMA latency x bytes in flight (ncu: tensor pipe 30 % active, L2 and DRAM far from their limits).
+    constexpr int PASS_N = L::PASS_N;
+    constexpr int PASSES = BLOCK_N / PASS_N;          // 1, 1, 2
+    constexpr int PAIRS = PASS_N / 2;                 // column pairs per pass for the statistics
+    constexpr int G = kEpiThreads / PAIRS;            // row groups (8 or 4)
+    constexpr int GPP = PASS_N / 64;                  // 32-column groups per warp and pass (1 or 2)
     const int pair = tid_e % PAIRS, rg = tid_e / PAIRS;
     const uint32_t out_stage_s = smem_u32(out_stage);
-    // statistics pass: this thread owns column pair `pair` and rows rg, rg+G, ...; G divides 8, so the swizzle
-    // term (row & 7) repeats every 8/G rows: its 8/G byte offsets are computed once, outside the row loop
+    // statistics: this thread owns column pair `pair` of every pass and rows rg, rg+G, ...; G divides 8, so the
+    // swizzle term (row & 7) repeats every 8/G rows: its byte offsets are computed once, outside the row loop
     constexpr int SWZ = 8 / G;
     uint32_t st_off[SWZ];
     {
@@ -223,47 +233,60 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         st_off[i] = out_stage_s + (col >> 6) * 16384 + ((col & 7) << 1) + r * 128 + ((chunk ^ (r & 7)) << 4);
       }
     }
-    float st_sum[2] = {0.f, 0.f}, st_sq[2] = {0.f, 0.f};
+    float st_sum[PASSES][2], st_sq[PASSES][2];
+#pragma unroll
+    for (int ps = 0; ps < PASSES; ++ps) st_sum[ps][0] = st_sum[ps][1] = st_sq[ps][0] = st_sq[ps][1] = 0.f;
     int st_nblk = -1;
+    float* const st_tgt = p.stats_rep ? p.stats_rep + (size_t)(blockIdx.x % kStatReplicas) * 2 * p.N : p.stats;
+    auto flush_stats = [&]() {
+#pragma unroll
+      for (int ps = 0; ps < PASSES; ++ps) {
+        const int c = st_nblk * BLOCK_N + ps * PASS_N + pair * 2;
+        if (c < p.N) atomicAdd(st_tgt + c, st_sum[ps][0]), atomicAdd(st_tgt + p.N + c, st_sq[ps][0]);
+        if (c + 1 < p.N) atomicAdd(st_tgt + c + 1, st_sum[ps][1]), atomicAdd(st_tgt + p.N + c + 1, st_sq[ps][1]);
+        st_sum[ps][0] = st_sum[ps][1] = st_sq[ps][0] = st_sq[ps][1] = 0.f;
+      }
+    };
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_blk = tile % p.num_m_blocks, n_blk = tile / p.num_m_blocks;
       const int n0 = n_blk * BLOCK_N;
       if (p.stats && st_nblk != n_blk) {
-        if (st_nblk >= 0) {
-          const int c = st_nblk * BLOCK_N + pair * 2;
-          if (c < p.N) atomicAdd(p.stats + c, st_sum[0]), atomicAdd(p.stats + p.N + c, st_sq[0]);
-          if (c + 1 < p.N) atomicAdd(p.stats + c + 1, st_sum[1]), atomicAdd(p.stats + p.N + c + 1, st_sq[1]);
-        }
-        st_sum[0] = st_sum[1] = st_sq[0] = st_sq[1] = 0.f;
+        if (st_nblk >= 0) flush_stats();
         st_nblk = n_blk;
       }
       mbar_wait(tfull + acc, acc_phase);
       fence_after_thread_sync();
-      // the previous tile's TMA store must have finished reading the staging buffer
-      if (leader) tma_store_wait_read0();
-      named_bar_sync(1, kEpiThreads);
 #pragma unroll
-      for (int b0 = 0; b0 < GPW; b0 += BATCH) {
-        uint32_t v[BATCH][32];
+      for (int ps = 0; ps < PASSES; ++ps) {
+        // the previous TMA store must have finished reading the staging buffer
+        if (leader) tma_store_wait_read0();
+        named_bar_sync(1, kEpiThreads);
+        uint32_t v[GPP][32];
 #pragma unroll
-        for (int b = 0; b < BATCH; ++b) {
-          const int g = half + 2 * (b0 + b);          // 32-column group of the tile
+        for (int b = 0; b < GPP; ++b) {
+          const int g = ps * (PASS_N / 32) + half + 2 * b;          // 32-column group of the tile
           tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BLOCK_N + g * 32, v[b]);
         }
         tmem_ld_wait();
+        if (ps == PASSES - 1) {
+          // accumulator fully read: hand the TMEM stage back to the MMA warp
+          fence_before_thread_sync();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty + acc);
+        }
 #pragma unroll
-        for (int b = 0; b < BATCH; ++b) {
-          const int g = half + 2 * (b0 + b);
+        for (int b = 0; b < GPP; ++b) {
+          const int lg = half + 2 * b;                               // group within the pass
           if (p.bias) {
 #pragma unroll
             for (int c = 0; c < 32; ++c) {
-              const int n = n0 + g * 32 + c;
+              const int n = n0 + ps * PASS_N + lg * 32 + c;
               v[b][c] = __float_as_uint(__uint_as_float(v[b][c]) + (n < p.N ? __ldg(p.bias + n) : 0.f));
             }
           }
-          const uint32_t dst = out_stage_s + (g >> 1) * 16384 + row * 128;
+          const uint32_t dst = out_stage_s + (lg >> 1) * 16384 + row * 128;
 #pragma unroll
           for (int c = 0; c < 4; ++c) {               // four 16-byte chunks of this group's half row
             uint4 w;
@@ -271,46 +294,60 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             w.y = pack2<kBf16>(__uint_as_float(v[b][8 * c + 2]), __uint_as_float(v[b][8 * c + 3]));
             w.z = pack2<kBf16>(__uint_as_float(v[b][8 * c + 4]), __uint_as_float(v[b][8 * c + 5]));
             w.w = pack2<kBf16>(__uint_as_float(v[b][8 * c + 6]), __uint_as_float(v[b][8 * c + 7]));
-            sts128(dst + ((((g & 1) * 4 + c) ^ (row & 7)) << 4), w);
+            sts128(dst + ((((lg & 1) * 4 + c) ^ (row & 7)) << 4), w);
           }
         }
-      }
-      // accumulator fully read: hand the TMEM stage back to the MMA warp
-      fence_before_thread_sync();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty + acc);
-      fence_proxy_async();                       // generic-proxy smem writes -> visible to the TMA engine
-      named_bar_sync(1, kEpiThreads);
-      if (leader) {
+        fence_proxy_async();                     // generic-proxy smem writes -> visible to the TMA engine
+        named_bar_sync(1, kEpiThreads);
+        if (leader) {
 #pragma unroll
-        for (int j = 0; j < BLOCK_N / 64; ++j)
-          if (n0 + j * 64 < p.N) {
-            if (p.accumulate)
-              tma_reduce_add_2d(&tmD, out_stage + j * 16384, n0 + j * 64, m_blk * BLOCK_M);
-            else
-              tma_store_2d(&tmD, out_stage + j * 16384, n0 + j * 64, m_blk * BLOCK_M);
+          for (int j = 0; j < PASS_N / 64; ++j) {
+            const int nc = n0 + ps * PASS_N + j * 64;
+            if (nc < p.N) {
+              if (p.accumulate)
+                tma_reduce_add_2d(&tmD, out_stage + j * 16384, nc, m_blk * BLOCK_M);
+              else
+                tma_store_2d(&tmD, out_stage + j * 16384, nc, m_blk * BLOCK_M);
+            }
           }
-        tma_store_commit();
-      }
-      if (p.stats) {
-        // per-channel sum / sum of squares of the ROUNDED outputs, read back from the staged tile
-        // (rows past M are exact zeros: their A rows were zero-filled by TMA)
+          tma_store_commit();
+        }
+        if (p.stats) {
+          // per-channel sum / sum of squares of the ROUNDED outputs, read back from the staged columns
+          // (rows past M are exact zeros: their A rows were zero-filled by TMA)
 #pragma unroll 4
-        for (int rb = 0; rb < BLOCK_M / 8; ++rb) {       // 8 rows per step: rows rg + 8*rb + i*G
+          for (int rb = 0; rb < BLOCK_M / 8; ++rb) {     // 8 rows per step: rows rg + 8*rb + i*G
 #pragma unroll
-          for (int i = 0; i < SWZ; ++i) {
-            const float2 f = unpack2<kBf16>(lds32(st_off[i] + rb * (8 * 128)));
-            st_sum[0] += f.x, st_sum[1] += f.y;
-            st_sq[0] = fmaf(f.x, f.x, st_sq[0]), st_sq[1] = fmaf(f.y, f.y, st_sq[1]);
+            for (int i = 0; i < SWZ; ++i) {
+              const float2 f = unpack2<kBf16>(lds32(st_off[i] + rb * (8 * 128)));
+              st_sum[ps][0] += f.x, st_sum[ps][1] += f.y;
+              st_sq[ps][0] = fmaf(f.x, f.x, st_sq[ps][0]), st_sq[ps][1] = fmaf(f.y, f.y, st_sq[ps][1]);
+            }
           }
         }
       }
       if ((acc ^= 1) == 0) acc_phase ^= 1;
     }
-    if (p.stats && st_nblk >= 0) {
-      const int c = st_nblk * BLOCK_N + pair * 2;
-      if (c < p.N) atomicAdd(p.stats + c, st_sum[0]), atomicAdd(p.stats + p.N + c, st_sq[0]);
-      if (c + 1 < p.N) atomicAdd(p.stats + c + 1, st_sum[1]), atomicAdd(p.stats + p.N + c + 1, st_sq[1]);
+    if (p.stats && st_nblk >= 0) flush_stats();
+    if (p.stats && p.stats_rep) {
+      // last CTA to get here folds the replicas (ticket lives right after them)
+      __threadfence();
+      named_bar_sync(1, kEpiThreads);
+      volatile uint32_t* last_flag = tmem_slot + 1;
+      if (leader) {
+        unsigned int* ticket = reinterpret_cast<unsigned int*>(p.stats_rep + (size_t)kStatReplicas * 2 * p.N);
+        *last_flag = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+      }
+      named_bar_sync(1, kEpiThreads);
+      if (*last_flag) {
+        __threadfence();
+        for (int c = tid_e; c < 2 * p.N; c += kEpiThreads) {
+          float a = 0.f;
+#pragma unroll
+          for (int r = 0; r < kStatReplicas; ++r) a += __ldcg(p.stats_rep + (size_t)r * 2 * p.N + c);
+          p.stats[c] = a;
+        }
+      }
     }
     if (leader) tma_store_wait0();
   }
@@ -631,9 +668,11 @@ static int launch_wgrad(const CUtensorMap& a, const CUtensorMap& b, const WgradP
 }  // namespace pdb
 using namespace pdb;
 
+extern "C" size_t pdb_conv_stats_scratch_floats(int K) { return (size_t)kStatReplicas * 2 * K + 32; }
+
 extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, const pdb_conv_shape* s, int64_t lda,
-                              int64_t ldd, float* stats, const float* bias, int block_n, int accumulate,
-                              void* stream) {
+                              int64_t ldd, float* stats, float* stats_scratch, const float* bias, int block_n,
+                              int accumulate, void* stream) {
   PDB_CHECK_ARG(x && w && y && s, "pdb_conv_fprop: null pointer");
   PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16, "pdb_conv_fprop: dtype must be PDB_BF16 or PDB_FP16");
   if (int e = load_driver_fns()) return e;
@@ -658,7 +697,7 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
   p.a_im2col = plain ? 0 : 1;
   p.accumulate = accumulate ? 1 : 0;
   p.div_pq.init((uint32_t)(P * Q)), p.div_q.init((uint32_t)Q);
-  p.stats = stats, p.bias = bias;
+  p.stats = stats, p.stats_rep = stats ? stats_scratch : nullptr, p.bias = bias;
 
   CUtensorMap tmA, tmB, tmD;
   if (plain) {

@@ -164,8 +164,13 @@ typedef struct {
  * reduction store (the residual-branch gradient is summed in the dgrad epilogue instead of by a separate
  * elementwise kernel).  dgrad is the same call on dY with the
  * weights rearranged by pdb_weight_dgrad_layout. */
+/* stats_scratch (nullable): pdb_conv_stats_scratch_floats(K) ZEROED floats.  When given, the CTAs spread their
+ * per-channel partial sums over 16 replicas and the last CTA folds them (stats is then overwritten): without it
+ * every CTA adds to the same 2K addresses and the L2 atomic units serialise (20-30 us on wide layers). */
+size_t pdb_conv_stats_scratch_floats(int K);
 int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, const pdb_conv_shape* s, int64_t lda,
-                   int64_t ldd, float* stats, const float* bias, int block_n, int accumulate, void* stream);
+                   int64_t ldd, float* stats, float* stats_scratch, const float* bias, int block_n, int accumulate,
+                   void* stream);
 
 /* dw[K, R*S*C] (fp32, row pitch ldw) += dy[N*P*Q, K]^T * im2col(x).  The pixel range is split over
  * CTAs (`splits`, 0 = heuristic) and partial tiles are added with fp32 vector reductions, so dw

@@ -167,7 +167,8 @@ class NativeResNetEngine:
         self.fc_dw = self.arena.grads[e.offset: e.offset + e.numel]
         self.fc_db = self.arena.grad_view("fc.bias")
         self.fc_pindex = (self.pindex["fc.weight"], self.pindex["fc.bias"])
-        self.stats = torch.zeros(self._stat_floats, dtype=torch.float32, device=self.device)
+        # forward: [sums of every BN | replica scratch + tickets for the conv epilogues], zeroed once per forward
+        self.stats = torch.zeros(self._stat_floats + self._scratch_floats, dtype=torch.float32, device=self.device)
         # backward: [dsums of every BN | replica scratch + tickets of every BN], zeroed once per backward pass
         self.dstats = torch.zeros(self._stat_floats + self._scratch_floats, dtype=torch.float32, device=self.device)
         self._anchor = model.fc.bias
@@ -257,6 +258,10 @@ class NativeResNetEngine:
         if need_dgrad:
             ops.weight_dgrad_layout_batched(self.arena.shadow, self.wt_all, self._wt_table, self._wt_table.shape[0])
 
+    def _fwd_scratch(self, bn: _BNPlan) -> torch.Tensor:
+        r0 = self._stat_floats + bn.rslot
+        return self.stats[r0: r0 + bn.rsize]
+
     def _sync_stats(self, buf: torch.Tensor) -> float:
         """SyncBatchNorm: sums are additive, so one all-reduce of [2C] per layer and direction."""
         if not self.sync_bn:
@@ -277,7 +282,7 @@ class NativeResNetEngine:
         P, Q = cv.out_hw(H, W)
         y = self._new(N, P, Q, cv.K)
         sums = self.stats[bn.slot: bn.slot + 2 * bn.C] if train else None
-        ops.conv_fprop(x, cv.w16, y, cv.shape(N, H, W), stats=sums)
+        ops.conv_fprop(x, cv.w16, y, cv.shape(N, H, W), stats=sums, stats_scratch=self._fwd_scratch(bn) if train else None)
         z = self._new(N, P, Q, cv.K)
         rows = N * P * Q
         if train:
@@ -303,7 +308,8 @@ class NativeResNetEngine:
         ops.stem_im2col(x.contiguous().float(), col)
         y = self._new(N, P, Q, cv.K)
         sums = self.stats[bn.slot: bn.slot + 2 * bn.C] if train else None
-        ops.conv_fprop(col, self.stem_w16, y, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0), stats=sums)
+        ops.conv_fprop(col, self.stem_w16, y, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0), stats=sums,
+                       stats_scratch=self._fwd_scratch(bn) if train else None)
         z = self._new(N, P, Q, cv.K)
         mask = None
         if train:

@@ -39,7 +39,8 @@ def declare(L):
     sig("pdb_add16", [P, P, P, c_int, c_int64, P])
     sig("pdb_upsample2_zero", [P, P, c_int, c_int, c_int, c_int, c_int, P])
     sig("pdb_add_strided2", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])
-    sig("pdb_conv_fprop", [P, P, P, c_int, POINTER(ConvShape), c_int64, c_int64, P, P, c_int, c_int, P])
+    sig("pdb_conv_fprop", [P, P, P, c_int, POINTER(ConvShape), c_int64, c_int64, P, P, P, c_int, c_int, P])
+    sig("pdb_conv_stats_scratch_floats", [c_int], c_size_t)
     sig("pdb_conv_wgrad", [P, P, P, c_int, POINTER(ConvShape), c_int64, c_int64, c_int64, c_int64, c_int, c_int, P])
     sig("pdb_weight_dgrad_layout", [P, P, c_int, c_int, c_int, c_int, c_int, P])
     sig("pdb_weight_dgrad_layout_batched", [P, P, P, c_int, c_int, P])

@@ -198,10 +198,11 @@ def add_strided2(a, b, out) -> None:
     count_launch()
 
 
-def conv_fprop(x, w, y, shape: ConvShape, *, lda: int = 0, ldd: int = 0, stats=None, bias=None, block_n: int = 0,
-               accumulate: bool = False) -> None:
+def conv_fprop(x, w, y, shape: ConvShape, *, lda: int = 0, ldd: int = 0, stats=None, stats_scratch=None, bias=None,
+               block_n: int = 0, accumulate: bool = False) -> None:
     check(require().pdb_conv_fprop(ptr(x), ptr(w), ptr(y), dtype_tag(x.dtype), ctypes.byref(shape), lda, ldd,
-                                   ptr(stats), ptr(bias), block_n, int(accumulate), _st(x)), "pdb_conv_fprop")
+                                   ptr(stats), ptr(stats_scratch), ptr(bias), block_n, int(accumulate), _st(x)),
+          "pdb_conv_fprop")
     count_launch()
 
 
