@@ -54,6 +54,7 @@ class TrainConfig:
     device: str = "auto"           # auto -> cuda if available else cpu
     seed: int = 0
     log_jsonl: Optional[str] = None
+    profile: bool = False          # NVTX ranges per phase + per-step device timing in the JSONL log
     arch: str = "resnet50"
     width: int = 64                # tests shrink the net; 64 == torchvision resnet50
     layers: Sequence[int] = (3, 4, 6, 3)
@@ -99,6 +100,7 @@ def add_arguments(p: argparse.ArgumentParser, mode: str) -> argparse.ArgumentPar
     p.add_argument("--device", choices=("auto", "cuda", "cpu"), default="auto")
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--log-jsonl", type=str, default=None)
+    p.add_argument("--profile", action="store_true", help="NVTX ranges per phase, per-step device time in --log-jsonl")
     p.add_argument("--width", type=int, default=64)
     return p
 

@@ -86,24 +86,48 @@ class DevicePrefetcher:
             yield cur
 
 
+class _Range:
+    """NVTX range when profiling on CUDA (``--profile``), otherwise free."""
+
+    def __init__(self, name: str, on: bool):
+        self.name, self.on = name, on
+
+    def __enter__(self):
+        if self.on:
+            torch.cuda.nvtx.range_push(self.name)
+        return self
+
+    def __exit__(self, *a):
+        if self.on:
+            torch.cuda.nvtx.range_pop()
+        return False
+
+
 def train_step(model, criterion, optimizer, samples, labels, cfg: TrainConfig, device: torch.device,
                loss_scaler: Optional[amp.GradScaler] = None, stock_autocast: bool = True):
     """One optimisation step in the reference's order (ref:restnet_ddp.py:26-30; amp variant
     ref:resnet_ddp_apex.py:27-34)."""
+    prof = bool(getattr(cfg, "profile", False)) and device.type == "cuda"
     if cfg.mode == "ddp_amp":
         with amp.autocast(cfg.resolved_dtype(), stock=stock_autocast, device_type=device.type):
-            outputs = model(samples)
-            loss = criterion(outputs, labels)
-        loss_scaler.scale(loss).backward()
-        loss_scaler.step(optimizer)
-        loss_scaler.update()
-        optimizer.zero_grad()
+            with _Range("pdb200.forward", prof):
+                outputs = model(samples)
+                loss = criterion(outputs, labels)
+        with _Range("pdb200.backward", prof):
+            loss_scaler.scale(loss).backward()
+        with _Range("pdb200.optimizer", prof):
+            loss_scaler.step(optimizer)
+            loss_scaler.update()
+            optimizer.zero_grad()
     else:
-        outputs = model(samples)
-        optimizer.zero_grad()
-        loss = criterion(outputs, labels)
-        loss.backward()
-        optimizer.step()
+        with _Range("pdb200.forward", prof):
+            outputs = model(samples)
+            optimizer.zero_grad()
+            loss = criterion(outputs, labels)
+        with _Range("pdb200.backward", prof):
+            loss.backward()
+        with _Range("pdb200.optimizer", prof):
+            optimizer.step()
     return loss
 
 
@@ -124,8 +148,16 @@ def train(dataloader, model, criterion, optimizer, scheduler, epoch: int, start_
             metrics.print_step(epoch, step)
 
         samples, labels = to_device(batch, device)
+        timer = None
+        if getattr(cfg, "profile", False) and logger is not None and logger.enabled:
+            timer = metrics.DeviceTimer(device)
+            timer.start()
         loss = train_step(model, criterion, optimizer, samples, labels, cfg, device, loss_scaler, stock_autocast)
         last_loss = loss
+        if timer is not None:
+            ms = metrics.max_over_ranks(timer.stop(), device)       # device-timed, max over ranks
+            logger.log(event="step_time", epoch=epoch, step=step, ms=ms,
+                       images_per_s=samples.size(0) * max(1, comm.get_world_size() if cfg.mode in ("ddp", "ddp_amp") else 1) / (ms / 1e3))
 
         if cfg.empty_cache and device.type == "cuda" and cfg.mode != "single":
             torch.cuda.synchronize()
