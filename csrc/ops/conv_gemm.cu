@@ -10,13 +10,14 @@
 //       the reduction runs over pixels, so both operands are MN-major in shared memory; the pixel range
 //       is split over CTAs and partial tiles are added to the fp32 gradient with vector reductions.
 //
-// Structure (both kernels): persistent CTAs, one per SM; warp 0 = TMA producer, warp 1 = MMA issuer
-// (one elected thread issues tcgen05.mma), warps 2-5 = epilogue.  kStages-deep smem ring guarded by
-// full/empty mbarriers; the fp32 accumulator lives in TMEM and is double-buffered so the epilogue of
-// tile i overlaps the main loop of tile i+1.  The fprop epilogue converts to 16-bit, stages the tile
-// in 128B-swizzled smem, writes it with TMA, and (optionally) accumulates the per-channel sum and
-// sum-of-squares that the following BatchNorm needs — the statistics pass of the delegate's BN kernel
-// (torch:nn/modules/batchnorm.py:144-210 over cuDNN) disappears.
+// Structure (both kernels): persistent CTAs, one per SM; warp 0 = TMA producer (one elected thread; its address
+// arithmetic is division-free), warp 1 = MMA issuer (one elected thread issues tcgen05.mma), warps 2-9 =
+// epilogue (two warps per TMEM lane quarter).  kStages-deep smem ring guarded by full/empty mbarriers; the fp32
+// accumulator lives in TMEM and is double-buffered so the epilogue of tile i overlaps the main loop of tile
+// i+1.  The fprop epilogue converts to 16-bit, stages at most 128 columns at a time in 128B-swizzled smem,
+// writes them with TMA (plain store, or reduction store when the tile is added to an existing gradient), and
+// (optionally) accumulates the per-channel sum and sum-of-squares that the following BatchNorm needs — the
+// statistics pass of the delegate's BN kernel (torch:nn/modules/batchnorm.py:144-210 over cuDNN) disappears.
 //
 // Delegates being replaced: cuDNN 9.22 convolutions and cuBLAS(Lt) linear.
 #include "common.cuh"

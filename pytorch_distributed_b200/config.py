@@ -70,9 +70,24 @@ class TrainConfig:
         return Path(self.save_path)
 
     def resolved_dtype(self) -> str:
+        """`auto`: the amp mode computes in 16 bit like the reference's autocast script.  The three fp32 scripts
+        of the reference run cuDNN convolutions in TF32 (10-bit mantissa, torch's default); on a CUDA device
+        with the sm_100a library their `auto` here is bf16 activations + fp32 master weights, gradients,
+        statistics and loss on the native step graph — pass ``--dtype fp32`` for the stock TF32 cuDNN path."""
         if self.dtype != "auto":
             return self.dtype
-        return "bf16" if self.mode == "ddp_amp" else "fp32"
+        if self.mode == "ddp_amp":
+            return "bf16"
+        if self.engine != "torch" and self.device != "cpu" and self.width % 64 == 0:
+            try:
+                import torch
+                if torch.cuda.is_available():
+                    from . import ops
+                    if ops.available():
+                        return "bf16"
+            except Exception:
+                pass
+        return "fp32"
 
 
 def add_arguments(p: argparse.ArgumentParser, mode: str) -> argparse.ArgumentParser:

@@ -276,8 +276,7 @@ class NativeResNetEngine:
             return float(dist.get_world_size())
         return 1.0
 
-    def _conv_bn(self, cv: _ConvPlan, bn: _BNPlan, x: torch.Tensor, *, residual=None, relu=True, train=True,
-                 x2d_lda: int = 0):
+    def _conv_bn(self, cv: _ConvPlan, bn: _BNPlan, x: torch.Tensor, *, residual=None, relu=True, train=True):
         N, H, W, _ = x.shape
         P, Q = cv.out_hw(H, W)
         y = self._new(N, P, Q, cv.K)
