@@ -26,6 +26,11 @@ CASES = [
     ("fprop", 5, 7, 7, 512, 512, 3, 3, 1, 1, 256),      # 7x7 maps: tiles span images
     ("fprop", 400, 1, 1, 2048, 1000, 1, 1, 1, 0, 128),  # fc
     ("fprop", 2, 112, 112, 152, 64, 1, 1, 1, 0, 64),    # stem as GEMM over the im2col buffer (K tail)
+    ("fprop", 3, 14, 14, 256, 1024, 1, 1, 1, 0, 512),   # 512 = 256-wide tile on a CTA pair (cta_group::2); 5 M blocks (odd)
+    ("fprop", 3, 14, 14, 256, 256, 3, 3, 1, 1, 512),
+    ("fprop", 5, 7, 7, 512, 512, 3, 3, 1, 1, 512),
+    ("fprop", 2, 56, 56, 256, 512, 1, 1, 2, 0, 512),
+    ("fprop", 16, 14, 14, 1024, 256, 1, 1, 1, 0, 512),
     ("dgrad", 2, 28, 28, 128, 128, 3, 3, 1, 1, 0),
     ("dgrad", 2, 14, 14, 256, 1024, 1, 1, 1, 0, 0),
     ("wgrad", 2, 16, 16, 64, 64, 1, 1, 1, 0, 64),
@@ -59,7 +64,10 @@ def main():
     only = sys.argv[1] if len(sys.argv) > 1 else None
     bad = 0
     for case in CASES:
-        if only and case[0] != only:
+        if only == "pair":
+            if case[-1] != 512:
+                continue
+        elif only and case[0] != only:
             continue
         try:
             r = subprocess.run([sys.executable, __file__, "one", json.dumps(case)], capture_output=True, text=True,

@@ -45,7 +45,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="gpurun_out/conv_tune.json")
     ap.add_argument("--batch", type=int, default=400)
+    ap.add_argument("--pair", action="store_true", help="fprop only: compare the 256-wide tile on one CTA vs a CTA pair")
     args = ap.parse_args()
+    only_pair = args.pair
     N, dt = args.batch, torch.bfloat16
     out = {"fprop": [], "wgrad": []}
     for (H, C, K, R, stride) in FPROP:
@@ -58,8 +60,8 @@ def main():
         sh = ConvShape(N, H, H, C, K, R, R, stride, pad)
         flops = 2.0 * N * P * P * K * C * R * R
         rec = {"shape": [H, C, K, R, stride], "variants": {}}
-        for bn in (64, 128, 256):
-            if bn > max(64, K):
+        for bn in (64, 128, 256, 512):            # 512 = 256-wide tile on a CTA pair (cta_group::2)
+            if (bn if bn < 512 else 256) > max(64, K) or (only_pair and bn < 256):
                 continue
             ms = timeit(lambda: ops.conv_fprop(x, w, y, sh, stats=st, block_n=bn))
             rec["variants"][f"bn{bn}"] = {"ms": round(ms, 4), "tflops": round(flops / ms / 1e9, 1)}
@@ -69,7 +71,7 @@ def main():
         print("fprop", rec, flush=True)
         del x, w, y
     sms = torch.cuda.get_device_properties(0).multi_processor_count
-    for (H, C, K, R, stride) in WGRAD:
+    for (H, C, K, R, stride) in ([] if only_pair else WGRAD):
         pad = 1 if R == 3 else 0
         P = (H + 2 * pad - R) // stride + 1
         x = torch.randn(N, H, H, C, device="cuda", dtype=dt)

@@ -71,12 +71,13 @@ struct FpropParams {
   const float* bias;   // [N]; may be null
 };
 
-template <int BLOCK_N>
+// kPair: the CTA is one half of a cta_group::2 pair working on a 256-row tile; it stages only HALF of the B tile.
+template <int BLOCK_N, bool kPair = false>
 struct FpropSmem {
-  static constexpr uint32_t B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
+  static constexpr uint32_t B_STAGE_BYTES = (kPair ? BLOCK_N / 2 : BLOCK_N) * BLOCK_K * 2;
   static constexpr uint32_t STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int PASS_N = BLOCK_N < 128 ? BLOCK_N : 128;        // columns staged per epilogue pass
-  static constexpr int kStages = BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8);
+  static constexpr int kStages = kPair ? (BLOCK_N == 256 ? 6 : 8) : (BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8));
   static constexpr uint32_t OUT_BYTES = (PASS_N / 64) * 16384;        // 128 rows x 128 B per 64-col chunk
   static constexpr uint32_t BAR_OFFSET = kStages * STAGE_BYTES + OUT_BYTES;
   static constexpr uint32_t TOTAL = BAR_OFFSET + 256 + 1024;           // barriers + alignment slack
@@ -98,11 +99,16 @@ __device__ __forceinline__ float2 unpack2(uint32_t w) {
   return __half22float2(*reinterpret_cast<__half2*>(&w));
 }
 
-template <int BLOCK_N, bool kBf16>
+template <int BLOCK_N, bool kBf16, bool kPair>
 __global__ void __launch_bounds__(kNumThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmD, const FpropParams p) {
-  using L = FpropSmem<BLOCK_N>;
+  using L = FpropSmem<BLOCK_N, kPair>;
+  // pair mode: rank 0 is the leader (issues the MMAs, owns the full / tmem-empty barriers that are waited on)
+  const uint32_t rank = kPair ? cluster_ctarank() : 0u;
+  const int unit = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;        // tile-walking unit: CTA or CTA pair
+  const int num_units = kPair ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int m_units = kPair ? (p.num_m_blocks + 1) / 2 : p.num_m_blocks;    // M blocks per unit column
   constexpr int kStages = L::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -121,22 +127,26 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     prefetch_tmap(&tmB);
     prefetch_tmap(&tmD);
     for (int i = 0; i < kStages; ++i) {
-      mbar_init(full + i, 1);
+      mbar_init(full + i, kPair ? 2 : 1);        // pair: leader's expect_tx arrive + the peer's remote arrive
       mbar_init(empty + i, 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull + i, 1);
-      mbar_init(tempty + i, kEpiThreads / 32);   // one arrive per epilogue warp
+      mbar_init(tempty + i, (kPair ? 2 : 1) * (kEpiThreads / 32));   // one arrive per epilogue warp (of both CTAs)
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<2 * BLOCK_N>(tmem_slot);
+  if (warp == 1) {
+    if (kPair) tmem_alloc_2sm<2 * BLOCK_N>(tmem_slot);
+    else tmem_alloc<2 * BLOCK_N>(tmem_slot);
+  }
   fence_before_thread_sync();
-  __syncthreads();
+  if (kPair) cluster_sync_all();                 // the peer's barriers must exist before anything arrives on them
+  else __syncthreads();
   fence_after_thread_sync();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+  const int num_tiles = m_units * p.num_n_blocks;
   const int num_kb = p.taps * p.cin_blocks;
 
   if (warp == 0) {
@@ -144,8 +154,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_blk = tile % p.num_m_blocks, n_blk = tile / p.num_m_blocks;
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
+        const int m_blk = (tile % m_units) * (kPair ? 2 : 1) + (int)rank, n_blk = tile / m_units;
         int base_w = 0, base_h = 0, n_img = 0;
         if (p.a_im2col) {
           const int m0 = m_blk * BLOCK_M;
@@ -161,13 +171,24 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           mbar_wait(empty + stage, phase ^ 1);
           uint8_t* sA = smem + stage * L::STAGE_BYTES;
           uint8_t* sB = sA + A_STAGE_BYTES;
-          mbar_arrive_expect_tx(full + stage, L::STAGE_BYTES);
-          if (p.a_im2col) {
-            tma_load_im2col_4d(sA, &tmA, full + stage, cb * BLOCK_K, base_w, base_h, n_img, (uint16_t)sx, (uint16_t)r);
+          if (kPair) {
+            // both CTAs' bytes are credited to the leader's barrier; the peer only announces itself
+            if (rank == 0) mbar_arrive_expect_tx(full + stage, 2 * L::STAGE_BYTES);
+            else mbar_arrive_cluster(full + stage, 0);
+            if (p.a_im2col)
+              tma_load_im2col_4d_2sm(sA, &tmA, full + stage, cb * BLOCK_K, base_w, base_h, n_img, (uint16_t)sx, (uint16_t)r);
+            else
+              tma_load_2d_2sm(sA, &tmA, full + stage, kb * BLOCK_K, m_blk * BLOCK_M);
+            tma_load_2d_2sm(sB, &tmB, full + stage, kb * BLOCK_K, n_blk * BLOCK_N + (int)rank * (BLOCK_N / 2));
           } else {
-            tma_load_2d(sA, &tmA, full + stage, kb * BLOCK_K, m_blk * BLOCK_M);
+            mbar_arrive_expect_tx(full + stage, L::STAGE_BYTES);
+            if (p.a_im2col) {
+              tma_load_im2col_4d(sA, &tmA, full + stage, cb * BLOCK_K, base_w, base_h, n_img, (uint16_t)sx, (uint16_t)r);
+            } else {
+              tma_load_2d(sA, &tmA, full + stage, kb * BLOCK_K, m_blk * BLOCK_M);
+            }
+            tma_load_2d(sB, &tmB, full + stage, kb * BLOCK_K, n_blk * BLOCK_N);
           }
-          tma_load_2d(sB, &tmB, full + stage, kb * BLOCK_K, n_blk * BLOCK_N);
           if (++cb == p.cin_blocks) {
             cb = 0;
             if (++sx == p.S) sx = 0, ++r;
@@ -176,13 +197,13 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
       }
     }
-  } else if (warp == 1) {
-    // ================================ MMA issuer ==================================
-    constexpr uint32_t idesc = umma_idesc_f16(kBf16 ? 1 : 0, BLOCK_M, BLOCK_N, 0, 0);
+  } else if (warp == 1 && rank == 0) {
+    // ================================ MMA issuer (pair mode: leader CTA only) ======
+    constexpr uint32_t idesc = umma_idesc_f16(kBf16 ? 1 : 0, kPair ? 2 * BLOCK_M : BLOCK_M, BLOCK_N, 0, 0);
     constexpr uint64_t desc_base = umma_desc_base(0, 1024);        // K-major SW128: SBO = 8 rows x 128 B
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = unit; tile < num_tiles; tile += num_units) {
       mbar_wait(tempty + acc, acc_phase ^ 1);                       // epilogue has drained this accumulator
       fence_after_thread_sync();
       const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
@@ -194,18 +215,24 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const uint32_t b_addr = a_addr + A_STAGE_BYTES;
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            umma_f16(d_tmem, umma_desc(desc_base, a_addr + k * UMMA_K * 2), umma_desc(desc_base, b_addr + k * UMMA_K * 2),
-                     idesc, (kb | k) != 0);
+            const uint64_t da = umma_desc(desc_base, a_addr + k * UMMA_K * 2), db = umma_desc(desc_base, b_addr + k * UMMA_K * 2);
+            if (kPair) umma_f16_2sm(d_tmem, da, db, idesc, (kb | k) != 0);
+            else umma_f16(d_tmem, da, db, idesc, (kb | k) != 0);
           }
-          umma_commit(empty + stage);                               // smem slot free once these MMAs retire
-          if (kb == num_kb - 1) umma_commit(tfull + acc);           // accumulator complete
+          if (kPair) {
+            umma_commit_2sm(empty + stage, 3);                      // frees the slot in BOTH CTAs
+            if (kb == num_kb - 1) umma_commit_2sm(tfull + acc, 3);  // wakes both epilogues
+          } else {
+            umma_commit(empty + stage);                             // smem slot free once these MMAs retire
+            if (kb == num_kb - 1) umma_commit(tfull + acc);         // accumulator complete
+          }
         }
         __syncwarp();
         if (++stage == kStages) stage = 0, phase ^= 1;
       }
       if ((acc ^= 1) == 0) acc_phase ^= 1;
     }
-  } else {
+  } else if (warp >= 2) {
     // ================================ epilogue ====================================
     const int quarter = warp & 3;                     // TMEM lanes [32*quarter, +32) are visible to this warp
     const int half = (warp - 2) >> 2;                 // the two warps of a quarter take alternate 32-column groups
@@ -250,8 +277,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     };
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m_blk = tile % p.num_m_blocks, n_blk = tile / p.num_m_blocks;
+    for (int tile = unit; tile < num_tiles; tile += num_units) {
+      const int m_blk = (tile % m_units) * (kPair ? 2 : 1) + (int)rank, n_blk = tile / m_units;
       const int n0 = n_blk * BLOCK_N;
       if (p.stats && st_nblk != n_blk) {
         if (st_nblk >= 0) flush_stats();
@@ -275,7 +302,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           // accumulator fully read: hand the TMEM stage back to the MMA warp
           fence_before_thread_sync();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty + acc);
+          if (lane == 0) {
+            if (kPair) mbar_arrive_cluster(tempty + acc, 0);       // the MMA warp lives in the leader CTA
+            else mbar_arrive(tempty + acc);
+          }
         }
 #pragma unroll
         for (int b = 0; b < GPP; ++b) {
@@ -353,8 +383,13 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (leader) tma_store_wait0();
   }
   fence_before_thread_sync();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc<2 * BLOCK_N>(tmem_base);
+  if (kPair) {
+    cluster_sync_all();            // neither CTA may leave while the other can still signal its barriers / read its smem
+    if (warp == 1) tmem_dealloc_2sm<2 * BLOCK_N>(tmem_base);
+  } else {
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<2 * BLOCK_N>(tmem_base);
+  }
 }
 
 // ================================================================================================
@@ -629,13 +664,42 @@ static int set_smem(K kernel, uint32_t bytes) {
   return 0;
 }
 
+template <bool kBf16>
+static int launch_fprop_pair(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const FpropParams& p,
+                             cudaStream_t st) {
+  constexpr int BN = 256;
+  static bool configured[64] = {};
+  auto kernel = conv_fprop_kernel<BN, kBf16, true>;
+  int dev = 0;
+  PDB_CUDA(cudaGetDevice(&dev));
+  const uint32_t smem = FpropSmem<BN, true>::TOTAL;
+  if (!configured[dev & 63]) {
+    if (int e = set_smem(kernel, smem)) return e;
+    configured[dev & 63] = true;
+  }
+  const int pair_tiles = ((p.num_m_blocks + 1) / 2) * p.num_n_blocks;
+  int pairs = num_sms() / 2;
+  if (pair_tiles < pairs) pairs = pair_tiles;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(kNumThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2, attr[0].val.clusterDim.y = 1, attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr, cfg.numAttrs = 1;
+  PDB_CUDA(cudaLaunchKernelEx(&cfg, kernel, a, b, d, p));
+  return 0;
+}
+
 template <int BLOCK_N, bool kBf16>
 static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const FpropParams& p,
                         cudaStream_t st) {
   // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute (the single-process
   // DataParallel mode launches from one process on every GPU)
   static bool configured[64] = {};
-  auto kernel = conv_fprop_kernel<BLOCK_N, kBf16>;
+  auto kernel = conv_fprop_kernel<BLOCK_N, kBf16, false>;
   int dev = 0;
   PDB_CUDA(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
@@ -686,8 +750,10 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
   if (lda <= 0) lda = s->C;
   if (ldd <= 0) ldd = s->K;
   int bn = block_n;
+  const bool pair = bn == 512;            // 512: a 256-wide tile computed by a CTA pair (cta_group::2, M = 256)
+  if (pair) bn = 256;
   if (bn <= 0) bn = s->K <= 64 ? 64 : (s->K <= 128 ? 128 : 256);
-  PDB_CHECK_ARG(bn == 64 || bn == 128 || bn == 256, "pdb_conv_fprop: block_n must be 64, 128 or 256");
+  PDB_CHECK_ARG(bn == 64 || bn == 128 || bn == 256, "pdb_conv_fprop: block_n must be 64, 128, 256 or 512 (pair)");
 
   FpropParams p{};
   p.M = (int)M, p.N = s->K;
@@ -707,10 +773,11 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
     if (int e = make_im2col_4d(&tmA, x, dtype, s->N, s->H, s->W, s->C, s->R, s->S, s->stride, s->pad, BLOCK_M)) return e;
   }
   const uint64_t ktot = (uint64_t)p.taps * s->C;
-  if (int e = make_tiled_2d(&tmB, w, dtype, (uint64_t)s->K, ktot, ktot, (uint32_t)bn, BLOCK_K)) return e;
+  if (int e = make_tiled_2d(&tmB, w, dtype, (uint64_t)s->K, ktot, ktot, (uint32_t)(pair ? bn / 2 : bn), BLOCK_K)) return e;
   if (int e = make_tiled_2d(&tmD, y, dtype, (uint64_t)M, (uint64_t)s->K, (uint64_t)ldd, BLOCK_M, 64)) return e;
 
   cudaStream_t st = (cudaStream_t)stream;
+  if (pair) return dtype == PDB_BF16 ? launch_fprop_pair<true>(tmA, tmB, tmD, p, st) : launch_fprop_pair<false>(tmA, tmB, tmD, p, st);
 #define GO(BN)                                                              \
   (dtype == PDB_BF16 ? launch_fprop<BN, true>(tmA, tmB, tmD, p, st) : launch_fprop<BN, false>(tmA, tmB, tmD, p, st))
   if (bn == 64) return GO(64);
