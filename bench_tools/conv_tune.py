@@ -65,6 +65,8 @@ def main():
                 continue
             ms = timeit(lambda: ops.conv_fprop(x, w, y, sh, stats=st, block_n=bn))
             rec["variants"][f"bn{bn}"] = {"ms": round(ms, 4), "tflops": round(flops / ms / 1e9, 1)}
+        if not rec["variants"]:
+            continue
         best = min(rec["variants"].items(), key=lambda kv: kv[1]["ms"])
         rec["best"] = best[0]
         out["fprop"].append(rec)

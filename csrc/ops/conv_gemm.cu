@@ -750,9 +750,16 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
   if (lda <= 0) lda = s->C;
   if (ldd <= 0) ldd = s->K;
   int bn = block_n;
-  const bool pair = bn == 512;            // 512: a 256-wide tile computed by a CTA pair (cta_group::2, M = 256)
+  bool pair = bn == 512;                  // 512: a 256-wide tile computed by a CTA pair (cta_group::2, M = 256)
   if (pair) bn = 256;
-  if (bn <= 0) bn = s->K <= 64 ? 64 : (s->K <= 128 ? 128 : 256);
+  if (bn <= 0) {
+    bn = s->K <= 64 ? 64 : (s->K <= 128 ? 128 : 256);
+    // Measured on the ResNet-50 shapes (profiles/conv_tune_pair.json): the pair halves each CTA's weight traffic and
+    // wins 3-20 % once every CTA has six or more tiles to pipeline; on two-to-three-tile grids (7x7 maps) the coupled
+    // pipelines of the two CTAs lose 6-11 % to the single-CTA tile.
+    const int64_t tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((s->K + 255) / 256);
+    pair = bn == 256 && tiles >= 6ll * num_sms();
+  }
   PDB_CHECK_ARG(bn == 64 || bn == 128 || bn == 256, "pdb_conv_fprop: block_n must be 64, 128, 256 or 512 (pair)");
 
   FpropParams p{};

@@ -15,6 +15,11 @@ TOL = 1.2e-2       # 16-bit output rounding (2^-8 relative) on top of fp32 accum
     (2, 28, 28, 128, 128, 3, 3, 1, 1, 128), (2, 56, 56, 128, 128, 3, 3, 2, 1, 128),
     (2, 56, 56, 256, 512, 1, 1, 2, 0, 256), (5, 7, 7, 512, 512, 3, 3, 1, 1, 256),
     (400, 1, 1, 2048, 1000, 1, 1, 1, 0, 128), (2, 112, 112, 152, 64, 1, 1, 1, 0, 64),
+    # block_n 512: the 256-wide tile on a CTA pair (cta_group::2, M = 256); odd M-block counts included
+    (3, 14, 14, 256, 1024, 1, 1, 1, 0, 512), (3, 14, 14, 256, 256, 3, 3, 1, 1, 512),
+    (5, 7, 7, 512, 512, 3, 3, 1, 1, 512), (2, 56, 56, 256, 512, 1, 1, 2, 0, 512),
+    # enough tiles that block_n=0 picks the pair kernel by itself
+    (80, 14, 14, 512, 2048, 1, 1, 1, 0, 0),
 ])
 def test_fprop(case):
     N, H, W, C, K, R, S, stride, pad, bn = case
@@ -42,7 +47,8 @@ def test_wgrad(case):
     assert wgrad_case(N, H, W, C, K, R, S, stride, pad, block_n=bn) < 5e-3
 
 
-def test_fprop_accumulate_epilogue():
+@pytest.mark.parametrize("block_n", [0, 512])
+def test_fprop_accumulate_epilogue(block_n):
     """y += conv(x, w) through the TMA reduction store (how residual gradients are summed)."""
     import torch.nn.functional as F
     from pytorch_distributed_b200 import ops
@@ -54,7 +60,7 @@ def test_fprop_accumulate_epilogue():
     w = (torch.randn(K, 1, 1, C, device="cuda", generator=g) / C ** 0.5).bfloat16()
     y0 = torch.randn(N, H, H, K, device="cuda", generator=g).bfloat16()
     y = y0.clone()
-    ops.conv_fprop(x, w, y, ConvShape(N, H, H, C, K, 1, 1, 1, 0), accumulate=True)
+    ops.conv_fprop(x, w, y, ConvShape(N, H, H, C, K, 1, 1, 1, 0), accumulate=True, block_n=block_n)
     torch.cuda.synchronize()
     ref = y0.float() + (x.float().reshape(-1, C) @ w.float().reshape(K, C).t()).reshape(N, H, H, K)
     assert rel_err(y, ref) < TOL
