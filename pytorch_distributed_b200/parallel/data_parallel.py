@@ -23,6 +23,7 @@ from __future__ import annotations
 
 import copy
 import threading
+import warnings
 from typing import List, Optional, Sequence
 
 import torch
@@ -91,6 +92,24 @@ class _null:
         return False
 
 
+def check_balance(devices: Sequence[torch.device], threshold: float = 0.75) -> Optional[str]:
+    """Warns when the replicas would sit on unequal GPUs: smallest / largest total memory or SM count below
+    ``threshold`` (same rule and threshold as torch:nn/parallel/data_parallel.py:24-48).  Returns the message."""
+    cuda = [d for d in devices if d.type == "cuda"]
+    if len(cuda) < 2 or not torch.cuda.is_available():
+        return None
+    props = [torch.cuda.get_device_properties(d) for d in cuda]
+    for what, vals in (("memory", [p.total_memory for p in props]), ("SM count", [p.multi_processor_count for p in props])):
+        lo, hi = min(vals), max(vals)
+        if hi > 0 and lo / hi < threshold:
+            msg = (f"DataParallel: {what} is unbalanced across {[str(d) for d in cuda]} "
+                   f"(min/max = {lo / hi:.2f} < {threshold}); the slowest device paces every step — "
+                   f"exclude {cuda[vals.index(lo)]} via device_ids or CUDA_VISIBLE_DEVICES")
+            warnings.warn(msg)
+            return msg
+    return None
+
+
 class DataParallel(nn.Module):
     def __init__(self, module: nn.Module, device_ids: Optional[Sequence] = None, output_device=None,
                  dim: int = 0):
@@ -103,6 +122,7 @@ class DataParallel(nn.Module):
         self.device_ids = list(device_ids)
         self.output_device = _dev(output_device) if output_device is not None else self.devices[0]
         root = self.devices[0]
+        check_balance(self.devices)
         for t in list(module.parameters()) + list(module.buffers()):
             if t.device != root:
                 raise RuntimeError(f"module must have its parameters and buffers on device {root} "

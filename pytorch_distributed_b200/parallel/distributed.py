@@ -40,6 +40,33 @@ _WIRE = {None: None, "fp32": None, "fp16": torch.float16, "bf16": torch.bfloat16
          "allreduce": None, "fp16_compress": torch.float16, "bf16_compress": torch.bfloat16}
 
 
+class GradBucket:
+    """What a Python comm hook sees (subset of ``torch.distributed.GradBucket``): a view, never a copy."""
+
+    def __init__(self, ddp: "DistributedDataParallel", index: int):
+        self._ddp, self._index = ddp, index
+
+    def index(self) -> int:
+        return self._index
+
+    def is_last(self) -> bool:
+        return self._index == len(self._ddp.bucket_ranges) - 1
+
+    def buffer(self) -> torch.Tensor:
+        s, e = self._ddp.bucket_ranges[self._index]
+        return self._ddp.arena.grads[s:e]
+
+    def set_buffer(self, t: torch.Tensor) -> None:
+        self.buffer().copy_(t.reshape(-1))
+
+    def parameters(self):
+        ps = list(self._ddp.arena.parameters())
+        return [ps[i] for i, b in enumerate(self._ddp._param_bucket) if b == self._index]
+
+    def gradients(self):
+        return [p.grad for p in self.parameters()]
+
+
 class DistributedDataParallel(nn.Module):
     def __init__(self, module: nn.Module, device_ids=None, output_device=None, dim: int = 0,
                  broadcast_buffers: bool = True, process_group=None, bucket_cap_mb: float = 25.0,
@@ -65,6 +92,8 @@ class DistributedDataParallel(nn.Module):
         self.rank = dist.get_rank(process_group)
         self.grad_scaler = None
         self._wire_dtype = _WIRE[comm_dtype]
+        self._py_hook = None
+        self._hook_results = []
 
         params = [p for p in module.parameters() if p.requires_grad]
         if not params:
@@ -153,6 +182,13 @@ class DistributedDataParallel(nn.Module):
 
     def _launch_bucket(self, b: int) -> None:
         s, e = self.bucket_ranges[b]
+        if self._py_hook is not None:
+            # user callback (torch:nn/parallel/distributed.py:1987): it owns the whole reduction of this range,
+            # averaging included, and returns a tensor or a Future of one
+            state, fn = self._py_hook
+            bucket = GradBucket(self, b)
+            self._hook_results.append((bucket, fn(state, bucket)))
+            return
         sc = self.grad_scaler if (self.grad_scaler is not None and self.comm.fuses_unscale) else None
         self.comm.allreduce_range(
             self.arena.grads, s, e, average=True, wire_dtype=self._wire_dtype,
@@ -162,16 +198,21 @@ class DistributedDataParallel(nn.Module):
     def _finalize_backward(self) -> None:
         try:
             if not self.reducer.done():
-                if not self.find_unused_parameters:
-                    missing = [self.arena.entries[i].name for i in range(len(self._param_bucket))
-                               if self.reducer.pending(self._param_bucket[i]) > 0][:4]
-                    # Parameters that received no gradient keep a zero gradient in the arena; their
-                    # buckets still have to be reduced so that all ranks issue the same collectives.
-                    del missing
+                # Parameters that received no gradient keep a zero gradient in the arena; their buckets still
+                # have to be reduced so that all ranks issue the same collectives.
                 for b in self.reducer.flush():
                     self._launch_bucket(b)
+            for bucket, res in self._hook_results:
+                if not torch.is_tensor(res) and hasattr(res, "wait"):      # torch.futures.Future / torch._C.Future
+                    res = res.wait()
+                if isinstance(res, (list, tuple)):
+                    res = res[0]
+                buf = bucket.buffer()
+                if res.data_ptr() != buf.data_ptr():
+                    buf.copy_(res.reshape(-1))
+            self._hook_results.clear()
             self.comm.wait_all()
-            if self.grad_scaler is not None and self.comm.fuses_unscale:
+            if self.grad_scaler is not None and self.comm.fuses_unscale and self._py_hook is None:
                 self.grad_scaler.mark_unscaled_by_comm()
         finally:
             self._pass_open = False
@@ -182,14 +223,20 @@ class DistributedDataParallel(nn.Module):
         self.grad_scaler = scaler
 
     def register_comm_hook(self, state, hook) -> None:
-        """Built-in hooks by name: 'allreduce', 'fp16_compress', 'bf16_compress'
-        (default_comm_hooks.hpp:9-34); they are compile-time variants of the fused kernel, not
-        Python callbacks."""
+        """Built-in hooks — by name or by passing torch's ``allreduce_hook`` / ``fp16_compress_hook`` /
+        ``bf16_compress_hook`` (default_comm_hooks.hpp:9-34, default_hooks.py:18-134) — are compile-time variants of
+        the fused all-reduce kernel, not Python callbacks.  Any other callable is run as
+        ``hook(state, bucket) -> Tensor | Future[Tensor]`` once per bucket with a :class:`GradBucket` whose
+        ``buffer()`` is the bucket's range of the gradient arena; the result lands back in that range."""
         name = hook if isinstance(hook, str) else getattr(hook, "__name__", str(hook))
         name = name.replace("_hook", "")
-        if name not in _WIRE:
-            raise ValueError(f"unsupported comm hook {name!r}; choose from allreduce, fp16_compress, bf16_compress")
-        self._wire_dtype = _WIRE[name]
+        if name in _WIRE:
+            self._wire_dtype, self._py_hook = _WIRE[name], None
+        elif callable(hook):
+            self._py_hook = (state, hook)
+        else:
+            raise ValueError(f"unsupported comm hook {name!r}; choose from allreduce, fp16_compress, bf16_compress "
+                             "or pass a callable")
 
     @contextlib.contextmanager
     def no_sync(self):

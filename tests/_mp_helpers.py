@@ -37,7 +37,16 @@ def child_suspends(rank):
     time.sleep(30)
 
 
-def ddp_worker(rank, world, port, out_dir, use_ours, steps, sync_bn=False):
+def avg_hook(state, bucket):
+    """A user comm hook in the delegate's calling convention: averages the bucket with an async all-reduce."""
+    import torch.distributed as dist
+    state["calls"] += 1
+    t = bucket.buffer()
+    t.div_(dist.get_world_size())
+    return dist.all_reduce(t, async_op=True).get_future().then(lambda f: f.value()[0])
+
+
+def ddp_worker(rank, world, port, out_dir, use_ours, steps, sync_bn=False, hook=None):
     import torch.distributed as dist
     from pytorch_distributed_b200.models import ResNet
     from pytorch_distributed_b200.optim import SGD
@@ -50,6 +59,9 @@ def ddp_worker(rank, world, port, out_dir, use_ours, steps, sync_bn=False):
         model = convert_sync_batchnorm(model) if use_ours else torch.nn.SyncBatchNorm.convert_sync_batchnorm(model)
     if use_ours:
         ddp = DistributedDataParallel(model)
+        hook_state = {"calls": 0}
+        if hook == "py":
+            ddp.register_comm_hook(hook_state, avg_hook)
         opt = SGD(ddp.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
     else:
         ddp = torch.nn.parallel.DistributedDataParallel(model)
@@ -67,8 +79,10 @@ def ddp_worker(rank, world, port, out_dir, use_ours, steps, sync_bn=False):
         losses.append(loss.item())
     flat = torch.cat([p.detach().reshape(-1) for p in ddp.module.parameters()])
     bufs = torch.cat([b.detach().float().reshape(-1) for b in ddp.module.buffers()])
-    torch.save({"losses": losses, "params": flat.clone(), "bufs": bufs.clone()},
-               os.path.join(out_dir, f"{'ours' if use_ours else 'torch'}_{rank}.pt"))
+    if use_ours and hook == "py":
+        assert hook_state["calls"] == steps * len(ddp.bucket_ranges), hook_state
+    tag = ("ours" if use_ours else "torch") + (f"_{hook}" if hook else "")
+    torch.save({"losses": losses, "params": flat.clone(), "bufs": bufs.clone()}, os.path.join(out_dir, f"{tag}_{rank}.pt"))
     dist.destroy_process_group()
 
 

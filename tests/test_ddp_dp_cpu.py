@@ -22,6 +22,11 @@ def test_ddp_gloo_matches_torch_ddp(tmp_path, free_port):
     for r in range(world):
         assert ours[r]["losses"] == pytest.approx(ref[r]["losses"], rel=2e-3, abs=1e-4)
     assert torch.allclose(ours[0]["params"], ref[0]["params"], rtol=5e-3, atol=5e-4)
+    # a user-supplied Python comm hook (hook(state, bucket) -> Future) replaces the built-in reduction
+    launcher.spawn(H.ddp_worker, args=(world, free_port + 2, str(tmp_path), True, steps, False, "py"), nprocs=world)
+    hooked = [torch.load(tmp_path / f"ours_py_{r}.pt") for r in range(world)]
+    assert torch.equal(hooked[0]["params"], hooked[1]["params"])
+    assert torch.allclose(hooked[0]["params"], ours[0]["params"], rtol=1e-4, atol=1e-6)
 
 
 @pytest.mark.timeout(600)
@@ -85,3 +90,22 @@ def test_data_parallel_module_on_wrong_device_message():
     m = ResNet((1, 1, 1, 1), num_classes=10, width=8)
     dp = DataParallel(m, device_ids=["cpu"])
     assert dp(torch.randn(2, 3, 32, 32)).shape == (2, 10)
+
+
+def test_data_parallel_balance_warning(monkeypatch):
+    """min/max memory or SM count below 0.75 across the replicas' GPUs warns (torch:nn/parallel/data_parallel.py:24-48)."""
+    import types
+    import warnings
+    from pytorch_distributed_b200.parallel import data_parallel as dpm
+    props = {0: types.SimpleNamespace(total_memory=180 << 30, multi_processor_count=148),
+             1: types.SimpleNamespace(total_memory=80 << 30, multi_processor_count=132)}
+    monkeypatch.setattr(torch.cuda, "is_available", lambda: True)
+    monkeypatch.setattr(torch.cuda, "get_device_properties", lambda d: props[torch.device(d).index])
+    devs = [torch.device("cuda", 0), torch.device("cuda", 1)]
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        msg = dpm.check_balance(devs)
+    assert msg and "memory" in msg and len(w) == 1
+    props[1] = props[0]
+    assert dpm.check_balance(devs) is None
+    assert dpm.check_balance([torch.device("cpu"), torch.device("cpu")]) is None
