@@ -84,3 +84,17 @@ def test_ddp_suspend_only_rank0_saves(tmp_path, free_port):
     assert r.returncode == 0, r.stderr[-2000:]                  # suspend tears the group down cleanly
     assert (tmp_path / "out" / "latest.pt").exists()
     assert "cost time per epoch" not in r.stdout
+
+
+def test_config_defaults_are_the_reference_literals():
+    """No flags == the hyper-parameter block at the top of each reference main() (ref:restnet_ddp.py:76-84 etc.)."""
+    from pytorch_distributed_b200 import config
+    want_dirs = {"single": "output/resnet_single", "dp": "output/resnet_dp", "ddp": "output/resnet_ddp",
+                 "ddp_amp": "output/resnet_ddp_amp"}
+    for mode in config.MODES:
+        c = config.from_args(mode, [])
+        assert (c.epochs, c.batch_size, c.num_workers, c.lr, c.momentum, c.weight_decay) == (100, 400, 4, 0.1, 0.9, 1e-4)
+        assert (c.step_size, c.gamma) == (30, 0.1)
+        assert str(c.save_dir).endswith(want_dirs[mode])
+        assert (c.image_size, c.num_classes, c.train_samples, c.val_samples) == (224, 1000, 1_281_167, 50_000)
+    assert config.from_args("ddp", ["--lr", "0.2", "--batch-size", "64"]).lr == 0.2
