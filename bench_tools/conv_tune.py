@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--out", default="gpurun_out/conv_tune.json")
     ap.add_argument("--batch", type=int, default=400)
     ap.add_argument("--pair", action="store_true", help="fprop only: compare the 256-wide tile on one CTA vs a CTA pair")
+    ap.add_argument("--fprop-only", action="store_true")
     args = ap.parse_args()
     only_pair = args.pair
     N, dt = args.batch, torch.bfloat16
@@ -73,7 +74,7 @@ def main():
         print("fprop", rec, flush=True)
         del x, w, y
     sms = torch.cuda.get_device_properties(0).multi_processor_count
-    for (H, C, K, R, stride) in ([] if only_pair else WGRAD):
+    for (H, C, K, R, stride) in ([] if (only_pair or args.fprop_only) else WGRAD):
         pad = 1 if R == 3 else 0
         P = (H + 2 * pad - R) // stride + 1
         x = torch.randn(N, H, H, C, device="cuda", dtype=dt)

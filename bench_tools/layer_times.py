@@ -11,6 +11,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+os.environ["PDB200_GRAPHS"] = "0"     # every kernel must be an eager launch to get its own event pair
 
 import torch  # noqa: E402
 

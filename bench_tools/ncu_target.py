@@ -21,8 +21,9 @@ def main():
         w = torch.randn(K, 1, 1, C, device="cuda", dtype=dt) * 0.05
         y = torch.empty(N, H, H, K, device="cuda", dtype=dt)
         st = torch.zeros(2 * K, device="cuda")
+        bn = int(sys.argv[2]) if len(sys.argv) > 2 else 0
         for _ in range(6):
-            ops.conv_fprop(x, w, y, ConvShape(N, H, H, C, K, 1, 1, 1, 0), stats=st)
+            ops.conv_fprop(x, w, y, ConvShape(N, H, H, C, K, 1, 1, 1, 0), stats=st, block_n=bn)
     elif what in ("fprop", "wgrad"):
         H, C, K, R = 14, 256, 256, 3
         x = torch.randn(N, H, H, C, device="cuda", dtype=dt)

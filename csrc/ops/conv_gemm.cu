@@ -56,9 +56,33 @@ struct FastDiv {
 
 constexpr int kStatReplicas = 16;
 
+// Order in which a persistent CTA (or CTA pair) walks the output tiles.  Tiles are numbered n-fastest
+// (tile = m_unit * num_n_blocks + n_blk) and unit u takes u, u + G, u + 2G, ...: at any moment the grid works on
+// G / num_n_blocks activation tiles, each read by num_n_blocks CTAs at about the same time, so the activation
+// matrix comes from DRAM once.  The column block of unit u's k-th tile is (u + k G) mod num_n_blocks, which cycles
+// with period P = num_n_blocks / gcd(G, num_n_blocks); the walk visits k = 0, P, 2P, ... then k = 1, P+1, ... so
+// a unit changes column block at most P times and the per-channel statistics stay in registers in between.
+struct TileWalk {
+  int unit, num_units, num_tiles, period, phase, k;
+  __device__ __forceinline__ TileWalk(int u, int g, int t, int p) : unit(u), num_units(g), num_tiles(t), period(p), phase(0), k(0) {}
+  __device__ __forceinline__ bool next(int& tile) {
+    while (phase < period) {
+      tile = unit + k * num_units;
+      if (tile < num_tiles) {
+        k += period;
+        return true;
+      }
+      k = ++phase;
+    }
+    return false;
+  }
+};
+
 struct FpropParams {
   int M, N;
   int num_m_blocks, num_n_blocks;
+  int tile_period;     // see TileWalk
+  FastDiv div_nb;      // tile -> (m unit, column block)
   int taps, cin_blocks, S;
   int P, Q, stride, pad;
   int a_im2col;
@@ -154,8 +178,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = unit; tile < num_tiles; tile += num_units) {
-        const int m_blk = (tile % m_units) * (kPair ? 2 : 1) + (int)rank, n_blk = tile / m_units;
+      TileWalk walk(unit, num_units, num_tiles, p.tile_period);
+      for (int tile; walk.next(tile);) {
+        const int m_unit = (int)p.div_nb.div((uint32_t)tile), n_blk = tile - m_unit * p.num_n_blocks;
+        const int m_blk = m_unit * (kPair ? 2 : 1) + (int)rank;
         int base_w = 0, base_h = 0, n_img = 0;
         if (p.a_im2col) {
           const int m0 = m_blk * BLOCK_M;
@@ -203,7 +229,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     constexpr uint64_t desc_base = umma_desc_base(0, 1024);        // K-major SW128: SBO = 8 rows x 128 B
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
-    for (int tile = unit; tile < num_tiles; tile += num_units) {
+    TileWalk walk(unit, num_units, num_tiles, p.tile_period);
+    for (int tile; walk.next(tile);) {
       mbar_wait(tempty + acc, acc_phase ^ 1);                       // epilogue has drained this accumulator
       fence_after_thread_sync();
       const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
@@ -261,24 +288,26 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         st_off[i] = out_stage_s + (col >> 6) * 16384 + ((col & 7) << 1) + r * 128 + ((chunk ^ (r & 7)) << 4);
       }
     }
-    float st_sum[PASSES][2], st_sq[PASSES][2];
+    float2 st_sum[PASSES], st_sq[PASSES];            // packed: add.f32x2 / fma.rn.f32x2 halve the FP32 issue slots
 #pragma unroll
-    for (int ps = 0; ps < PASSES; ++ps) st_sum[ps][0] = st_sum[ps][1] = st_sq[ps][0] = st_sq[ps][1] = 0.f;
+    for (int ps = 0; ps < PASSES; ++ps) st_sum[ps] = st_sq[ps] = make_float2(0.f, 0.f);
     int st_nblk = -1;
     float* const st_tgt = p.stats_rep ? p.stats_rep + (size_t)(blockIdx.x % kStatReplicas) * 2 * p.N : p.stats;
     auto flush_stats = [&]() {
 #pragma unroll
       for (int ps = 0; ps < PASSES; ++ps) {
         const int c = st_nblk * BLOCK_N + ps * PASS_N + pair * 2;
-        if (c < p.N) atomicAdd(st_tgt + c, st_sum[ps][0]), atomicAdd(st_tgt + p.N + c, st_sq[ps][0]);
-        if (c + 1 < p.N) atomicAdd(st_tgt + c + 1, st_sum[ps][1]), atomicAdd(st_tgt + p.N + c + 1, st_sq[ps][1]);
-        st_sum[ps][0] = st_sum[ps][1] = st_sq[ps][0] = st_sq[ps][1] = 0.f;
+        if (c < p.N) atomicAdd(st_tgt + c, st_sum[ps].x), atomicAdd(st_tgt + p.N + c, st_sq[ps].x);
+        if (c + 1 < p.N) atomicAdd(st_tgt + c + 1, st_sum[ps].y), atomicAdd(st_tgt + p.N + c + 1, st_sq[ps].y);
+        st_sum[ps] = st_sq[ps] = make_float2(0.f, 0.f);
       }
     };
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = unit; tile < num_tiles; tile += num_units) {
-      const int m_blk = (tile % m_units) * (kPair ? 2 : 1) + (int)rank, n_blk = tile / m_units;
+    TileWalk walk(unit, num_units, num_tiles, p.tile_period);
+    for (int tile; walk.next(tile);) {
+      const int m_unit = (int)p.div_nb.div((uint32_t)tile), n_blk = tile - m_unit * p.num_n_blocks;
+      const int m_blk = m_unit * (kPair ? 2 : 1) + (int)rank;
       const int n0 = n_blk * BLOCK_N;
       if (p.stats && st_nblk != n_blk) {
         if (st_nblk >= 0) flush_stats();
@@ -286,17 +315,17 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
       mbar_wait(tfull + acc, acc_phase);
       fence_after_thread_sync();
-#pragma unroll
-      for (int ps = 0; ps < PASSES; ++ps) {
-        // the previous TMA store must have finished reading the staging buffer
-        if (leader) tma_store_wait_read0();
-        named_bar_sync(1, kEpiThreads);
-        uint32_t v[GPP][32];
+      uint32_t v[GPP][32];
+      auto issue_ld = [&](int ps) {
 #pragma unroll
         for (int b = 0; b < GPP; ++b) {
           const int g = ps * (PASS_N / 32) + half + 2 * b;          // 32-column group of the tile
           tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BLOCK_N + g * 32, v[b]);
         }
+      };
+      issue_ld(0);
+#pragma unroll
+      for (int ps = 0; ps < PASSES; ++ps) {
         tmem_ld_wait();
         if (ps == PASSES - 1) {
           // accumulator fully read: hand the TMEM stage back to the MMA warp
@@ -307,6 +336,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             else mbar_arrive(tempty + acc);
           }
         }
+        // the previous TMA store must have finished reading the staging buffer
+        if (leader) tma_store_wait_read0();
+        named_bar_sync(1, kEpiThreads);
 #pragma unroll
         for (int b = 0; b < GPP; ++b) {
           const int lg = half + 2 * b;                               // group within the pass
@@ -343,6 +375,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
           tma_store_commit();
         }
+        // the next pass's accumulator columns travel TMEM -> registers while the statistics below are computed
+        if (ps + 1 < PASSES) issue_ld(ps + 1);
         if (p.stats) {
           // per-channel sum / sum of squares of the ROUNDED outputs, read back from the staged columns
           // (rows past M are exact zeros: their A rows were zero-filled by TMA)
@@ -351,8 +385,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
             for (int i = 0; i < SWZ; ++i) {
               const float2 f = unpack2<kBf16>(lds32(st_off[i] + rb * (8 * 128)));
-              st_sum[ps][0] += f.x, st_sum[ps][1] += f.y;
-              st_sq[ps][0] = fmaf(f.x, f.x, st_sq[ps][0]), st_sq[ps][1] = fmaf(f.y, f.y, st_sq[ps][1]);
+              st_sum[ps] = __fadd2_rn(st_sum[ps], f);
+              st_sq[ps] = __ffma2_rn(f, f, st_sq[ps]);
             }
           }
         }
@@ -664,8 +698,17 @@ static int set_smem(K kernel, uint32_t bytes) {
   return 0;
 }
 
+static int walk_period(int units, int n_blocks) {
+  int a = units, b = n_blocks;
+  while (b) {
+    const int t = a % b;
+    a = b, b = t;
+  }
+  return n_blocks / a;          // n_blocks / gcd(units, n_blocks)
+}
+
 template <bool kBf16>
-static int launch_fprop_pair(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const FpropParams& p,
+static int launch_fprop_pair(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, FpropParams p,
                              cudaStream_t st) {
   constexpr int BN = 256;
   static bool configured[64] = {};
@@ -680,6 +723,7 @@ static int launch_fprop_pair(const CUtensorMap& a, const CUtensorMap& b, const C
   const int pair_tiles = ((p.num_m_blocks + 1) / 2) * p.num_n_blocks;
   int pairs = num_sms() / 2;
   if (pair_tiles < pairs) pairs = pair_tiles;
+  p.tile_period = walk_period(pairs, p.num_n_blocks);
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(2 * pairs);
   cfg.blockDim = dim3(kNumThreads);
@@ -694,7 +738,7 @@ static int launch_fprop_pair(const CUtensorMap& a, const CUtensorMap& b, const C
 }
 
 template <int BLOCK_N, bool kBf16>
-static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const FpropParams& p,
+static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, FpropParams p,
                         cudaStream_t st) {
   // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute (the single-process
   // DataParallel mode launches from one process on every GPU)
@@ -708,6 +752,7 @@ static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtens
   }
   const int tiles = p.num_m_blocks * p.num_n_blocks;
   const int grid = tiles < num_sms() ? tiles : num_sms();
+  p.tile_period = walk_period(grid, p.num_n_blocks);
   kernel<<<grid, kNumThreads, FpropSmem<BLOCK_N>::TOTAL, st>>>(a, b, d, p);
   PDB_LAUNCH_CHECK();
   return 0;
@@ -770,7 +815,7 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
   p.P = P, p.Q = Q, p.stride = s->stride, p.pad = s->pad;
   p.a_im2col = plain ? 0 : 1;
   p.accumulate = accumulate ? 1 : 0;
-  p.div_pq.init((uint32_t)(P * Q)), p.div_q.init((uint32_t)Q);
+  p.div_pq.init((uint32_t)(P * Q)), p.div_q.init((uint32_t)Q), p.div_nb.init((uint32_t)p.num_n_blocks);
   p.stats = stats, p.stats_rep = stats ? stats_scratch : nullptr, p.bias = bias;
 
   CUtensorMap tmA, tmB, tmD;
