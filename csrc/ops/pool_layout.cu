@@ -12,19 +12,18 @@ static int ew_grid(int64_t n, int threads = 256) {
 // ---- MaxPool 3x3 / stride 2 / pad 1 -------------------------------------------------------------
 // argmax stores the window position 0..8 (kh*3+kw) of the first maximum, like cuDNN/ATen, so the
 // backward pass routes the gradient to exactly one input even when 16-bit values tie.
+// One block per output row (n, ho): the index arithmetic is one 32-bit division per element instead of the chain of
+// 64-bit divisions a flat index needs (those, not memory, bounded the first version: 0.37 ms for 0.9 GB).
 template <typename T>
 __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y,
-                                                          uint8_t* __restrict__ argmax, int N, int H, int W, int C,
+                                                          uint8_t* __restrict__ argmax, int H, int W, int C,
                                                           int Ho, int Wo) {
   const int cvec = C / 8;
-  const int64_t total = (int64_t)N * Ho * Wo * cvec, stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int cg = (int)(i % cvec);
-    int64_t t = i / cvec;
-    const int wo = (int)(t % Wo);
-    t /= Wo;
-    const int ho = (int)(t % Ho);
-    const int n = (int)(t / Ho);
+  const int n = blockIdx.x / Ho, ho = blockIdx.x - n * Ho;
+  const T* xn = x + (int64_t)n * H * W * C;
+  const int64_t orow = ((int64_t)n * Ho + ho) * Wo * C;
+  for (int j = threadIdx.x; j < Wo * cvec; j += blockDim.x) {
+    const int wo = j / cvec, cg = j - wo * cvec;
     float best[8];
     int idx[8];
 #pragma unroll
@@ -38,52 +37,66 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const T* __restrict__ 
         const int w = 2 * wo - 1 + kw;
         if (w < 0 || w >= W) continue;
         float f[8];
-        unpack8<T>(ldg128(x + (((int64_t)n * H + h) * W + w) * C + cg * 8), f);
+        unpack8<T>(ldg128(xn + ((int64_t)h * W + w) * C + cg * 8), f);
 #pragma unroll
         for (int k = 0; k < 8; ++k)
           if (f[k] > best[k]) best[k] = f[k], idx[k] = kh * 3 + kw;
       }
     }
-    stg128(y + i * 8, pack8<T>(best));
+    const int64_t o = orow + (int64_t)j * 8;
+    stg128(y + o, pack8<T>(best));
     uint2 packed;
     packed.x = idx[0] | (idx[1] << 8) | (idx[2] << 16) | (idx[3] << 24);
     packed.y = idx[4] | (idx[5] << 8) | (idx[6] << 16) | (idx[7] << 24);
-    *reinterpret_cast<uint2*>(argmax + i * 8) = packed;
+    *reinterpret_cast<uint2*>(argmax + o) = packed;
   }
 }
 
 // Gather form: every input pixel collects from the (at most 2x2) windows that contain it — no atomics.
+// One block per input row (n, h).
 template <typename T>
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ argmax,
-                                                          T* __restrict__ dx, int N, int H, int W, int C, int Ho,
-                                                          int Wo) {
+                                                          T* __restrict__ dx, int H, int W, int C, int Ho, int Wo) {
   const int cvec = C / 8;
-  const int64_t total = (int64_t)N * H * W * cvec, stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int cg = (int)(i % cvec);
-    int64_t t = i / cvec;
-    const int w = (int)(t % W);
-    t /= W;
-    const int h = (int)(t % H);
-    const int n = (int)(t / H);
-    float acc[8] = {0};
-    // windows with 2*ho-1 <= h <= 2*ho+1  <=>  ho in [ceil((h-1)/2) .. floor((h+1)/2)] = [h/2 .. (h+1)/2]
-    const int ho0 = h / 2, ho1 = min((h + 1) / 2, Ho - 1);
+  const int n = blockIdx.x / H, h = blockIdx.x - n * H;
+  // windows with 2*ho-1 <= h <= 2*ho+1  <=>  ho in [ceil((h-1)/2) .. floor((h+1)/2)] = [h/2 .. (h+1)/2]
+  const int ho0 = h / 2, ho1 = min((h + 1) / 2, Ho - 1);
+  const int64_t obase = (int64_t)n * Ho * Wo * C;
+  T* dxrow = dx + ((int64_t)n * H + h) * W * C;
+  for (int j = threadIdx.x; j < W * cvec; j += blockDim.x) {
+    const int w = j / cvec, cg = j - w * cvec;
     const int wo0 = w / 2, wo1 = min((w + 1) / 2, Wo - 1);
-    for (int ho = ho0; ho <= ho1; ++ho)
-      for (int wo = wo0; wo <= wo1; ++wo) {
-        const int pos = (h - (2 * ho - 1)) * 3 + (w - (2 * wo - 1));
-        const int64_t o = (((int64_t)n * Ho + ho) * Wo + wo) * C + cg * 8;
-        const uint2 a = *reinterpret_cast<const uint2*>(argmax + o);
-        float g[8];
-        unpack8<T>(ldg128(dy + o), g);
+    // the (up to) four windows are loaded up front — independent loads in flight instead of a dependent loop — and
+    // the argmax bytes are compared four at a time
+    uint2 a[4];
+    uint4 g[4];
+    uint32_t pos4[4];
+    bool live[4];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const int id = ((k < 4 ? a.x : a.y) >> (8 * (k & 3))) & 0xff;
-          acc[k] += id == pos ? g[k] : 0.f;
-        }
+    for (int t = 0; t < 4; ++t) {
+      const int ho = (t >> 1) ? ho1 : ho0, wo = (t & 1) ? wo1 : wo0;
+      live[t] = !((t >> 1) && ho1 == ho0) && !((t & 1) && wo1 == wo0);
+      pos4[t] = (uint32_t)((h - (2 * ho - 1)) * 3 + (w - (2 * wo - 1))) * 0x01010101u;
+      if (live[t]) {
+        const int64_t o = obase + ((int64_t)ho * Wo + wo) * C + cg * 8;
+        a[t] = __ldg(reinterpret_cast<const uint2*>(argmax + o));
+        g[t] = ldg128(dy + o);
       }
-    stg128(dx + i * 8, pack8<T>(acc));
+    }
+    float acc[8] = {0};
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      if (!live[t]) continue;
+      const uint32_t m0 = __vcmpeq4(a[t].x, pos4[t]), m1 = __vcmpeq4(a[t].y, pos4[t]);   // 0xff per matching byte
+      uint4 v = g[t];
+      v.x &= __byte_perm(m0, 0, 0x1100), v.y &= __byte_perm(m0, 0, 0x3322);
+      v.z &= __byte_perm(m1, 0, 0x1100), v.w &= __byte_perm(m1, 0, 0x3322);
+      float f[8];
+      unpack8<T>(v, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+    }
+    stg128(dxrow + (int64_t)j * 8, pack8<T>(acc));
   }
 }
 
@@ -149,13 +162,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restrict__ x, T* __restrict__ col, int N,
                                                           int H, int W, int Ho, int Wo, int Kpad) {
   extern __shared__ float srows[];                 // [7*3][pitch] input rows with a zero halo of 3 on both sides
-  __shared__ short off_tab[160];                   // column kk -> (kh*3 + c)*pitch + kw
   const int pitch = W + 2 * kStemHalo + 2;
   const int n = blockIdx.x / Ho, ho = blockIdx.x - n * Ho;
-  for (int kk = threadIdx.x; kk < 160; kk += blockDim.x) {
-    const int c = kk % 3, tap = kk / 3, kw = tap % kStemTaps, kh = tap / kStemTaps;
-    off_tab[kk] = kk < kStemK ? (short)((kh * 3 + c) * pitch + kw) : (short)-1;
-  }
   const int64_t HW = (int64_t)H * W;
   for (int i = threadIdx.x; i < kStemTaps * 3 * pitch; i += blockDim.x) {
     const int rc = i / pitch, wp = i - rc * pitch;           // rc = kh*3 + c
@@ -165,19 +173,28 @@ __global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restric
     if (h >= 0 && h < H && w >= 0 && w < W) v = __ldg(x + ((int64_t)n * 3 + c) * HW + (int64_t)h * W + w);
     srows[i] = v;
   }
-  __syncthreads();
+  // a thread keeps ONE 8-column group of the output row for the whole block: its eight smem offsets live in
+  // registers, and it walks the pixels with a fixed stride (the first version looked the offsets up in a shared
+  // table for every vector: twice the shared-memory loads, 2-byte lanes that conflict)
   const int kvec = Kpad / 8;
+  const int wo_step = blockDim.x / kvec;
+  const int kv = threadIdx.x % kvec, wo_first = threadIdx.x / kvec;
+  int off[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int kk = kv * 8 + k;
+    const int c = kk % 3, tap = kk / 3, kw = tap % kStemTaps, kh = tap / kStemTaps;
+    off[k] = kk < kStemK ? (kh * 3 + c) * pitch + kw : -1;
+  }
+  __syncthreads();
+  if (wo_first >= wo_step) return;
   T* out = col + ((int64_t)n * Ho + ho) * Wo * Kpad;
-  for (int i = threadIdx.x; i < Wo * kvec; i += blockDim.x) {
-    const int wo = i / kvec, kv = i - wo * kvec;
+  for (int wo = wo_first; wo < Wo; wo += wo_step) {
     const float* base = srows + 2 * wo;                      // window of pixel wo starts at smem column 2*wo
     float f[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int o = off_tab[kv * 8 + k];
-      f[k] = o >= 0 ? base[o] : 0.f;
-    }
-    stg128(out + (int64_t)i * 8, pack8<T>(f));
+    for (int k = 0; k < 8; ++k) f[k] = off[k] >= 0 ? base[off[k]] : 0.f;
+    stg128(out + ((int64_t)wo * kvec + kv) * 8, pack8<T>(f));
   }
 }
 
@@ -205,47 +222,44 @@ __global__ void __launch_bounds__(256) add16_kernel(const T* __restrict__ a, con
   }
 }
 
-// dst[n, 2ho, 2wo] = src[n, ho, wo]; everything else zero.  One thread per destination vector.
+// dst[n, 2ho, 2wo] = src[n, ho, wo]; everything else zero.  One block per destination row (n, h).
 template <typename T>
-__global__ void __launch_bounds__(256) upsample2_kernel(const T* __restrict__ src, T* __restrict__ dst, int N, int Ho,
-                                                        int Wo, int C) {
+__global__ void __launch_bounds__(256) upsample2_kernel(const T* __restrict__ src, T* __restrict__ dst, int Ho, int Wo,
+                                                        int C) {
   const int cvec = C / 8, H = 2 * Ho, W = 2 * Wo;
-  const int64_t total = (int64_t)N * H * W * cvec, stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int cg = (int)(i % cvec);
-    int64_t t = i / cvec;
-    const int w = (int)(t % W);
-    t /= W;
-    const int h = (int)(t % H);
-    const int n = (int)(t / H);
+  const int n = blockIdx.x / H, h = blockIdx.x - n * H;
+  T* drow = dst + ((int64_t)n * H + h) * W * C;
+  const T* srow = src + ((int64_t)n * Ho + h / 2) * Wo * C;
+  const bool live = (h & 1) == 0;
+  for (int j = threadIdx.x; j < W * cvec; j += blockDim.x) {
+    const int w = j / cvec, cg = j - w * cvec;
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (((h | w) & 1) == 0) v = ldg128_stream(src + (((int64_t)n * Ho + h / 2) * Wo + w / 2) * C + cg * 8);
-    stg128(dst + i * 8, v);
+    if (live && (w & 1) == 0) v = ldg128_stream(srow + ((int64_t)(w / 2) * cvec + cg) * 8);
+    stg128(drow + (int64_t)j * 8, v);
   }
 }
 
+// o = a, plus b at the even (h, w) positions (b has half the resolution).  One block per row (n, h).
 template <typename T>
 __global__ void __launch_bounds__(256) add_strided2_kernel(const T* __restrict__ a, const T* __restrict__ b,
-                                                           T* __restrict__ o, int N, int H, int W, int C) {
+                                                           T* __restrict__ o, int H, int W, int C) {
   const int cvec = C / 8, Ho = H / 2, Wo = W / 2;
-  const int64_t total = (int64_t)N * H * W * cvec, stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int cg = (int)(i % cvec);
-    int64_t t = i / cvec;
-    const int w = (int)(t % W);
-    t /= W;
-    const int h = (int)(t % H);
-    const int n = (int)(t / H);
-    uint4 va = ldg128_stream(a + i * 8);
-    if (((h | w) & 1) == 0) {
+  const int n = blockIdx.x / H, h = blockIdx.x - n * H;
+  const int64_t row = ((int64_t)n * H + h) * W * C;
+  const T* brow = b + ((int64_t)n * Ho + h / 2) * Wo * C;
+  const bool live = (h & 1) == 0;
+  for (int j = threadIdx.x; j < W * cvec; j += blockDim.x) {
+    const int w = j / cvec, cg = j - w * cvec;
+    uint4 va = ldg128_stream(a + row + (int64_t)j * 8);
+    if (live && (w & 1) == 0) {
       float fa[8], fb[8];
       unpack8<T>(va, fa);
-      unpack8<T>(ldg128_stream(b + (((int64_t)n * Ho + h / 2) * Wo + w / 2) * C + cg * 8), fb);
+      unpack8<T>(ldg128_stream(brow + ((int64_t)(w / 2) * cvec + cg) * 8), fb);
 #pragma unroll
       for (int k = 0; k < 8; ++k) fa[k] += fb[k];
       va = pack8<T>(fa);
     }
-    stg128(o + i * 8, va);
+    stg128(o + row + (int64_t)j * 8, va);
   }
 }
 
@@ -258,9 +272,8 @@ extern "C" int pdb_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int
                                     void* stream) {
   PDB_CHECK_ARG(x && y && argmax && N > 0 && H > 0 && W > 0 && C % 8 == 0, "pdb_maxpool3x3s2_fwd: bad arguments");
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
-  const int64_t total = (int64_t)N * Ho * Wo * (C / 8);
-  PDB_DISPATCH_16(dtype, T, (maxpool_fwd_kernel<T><<<ew_grid(total), 256, 0, ST>>>((const T*)x, (T*)y, argmax, N, H, W,
-                                                                                    C, Ho, Wo)));
+  PDB_CHECK_ARG((int64_t)N * Ho < (1ll << 31), "pdb_maxpool3x3s2_fwd: too many rows");
+  PDB_DISPATCH_16(dtype, T, (maxpool_fwd_kernel<T><<<N * Ho, 256, 0, ST>>>((const T*)x, (T*)y, argmax, H, W, C, Ho, Wo)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -269,9 +282,8 @@ extern "C" int pdb_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void*
                                     int C, void* stream) {
   PDB_CHECK_ARG(dy && dx && argmax && N > 0 && H > 0 && W > 0 && C % 8 == 0, "pdb_maxpool3x3s2_bwd: bad arguments");
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
-  const int64_t total = (int64_t)N * H * W * (C / 8);
-  PDB_DISPATCH_16(dtype, T, (maxpool_bwd_kernel<T><<<ew_grid(total), 256, 0, ST>>>((const T*)dy, argmax, (T*)dx, N, H,
-                                                                                    W, C, Ho, Wo)));
+  PDB_CHECK_ARG((int64_t)N * H < (1ll << 31), "pdb_maxpool3x3s2_bwd: too many rows");
+  PDB_DISPATCH_16(dtype, T, (maxpool_bwd_kernel<T><<<N * H, 256, 0, ST>>>((const T*)dy, argmax, (T*)dx, H, W, C, Ho, Wo)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -319,8 +331,8 @@ extern "C" int pdb_add16(const void* a, const void* b, void* out, int dtype, int
 
 extern "C" int pdb_upsample2_zero(const void* src, void* dst, int dtype, int N, int Ho, int Wo, int C, void* stream) {
   PDB_CHECK_ARG(src && dst && N > 0 && Ho > 0 && Wo > 0 && C % 8 == 0, "pdb_upsample2_zero: bad arguments");
-  const int64_t total = (int64_t)N * Ho * Wo * 4 * (C / 8);
-  PDB_DISPATCH_16(dtype, T, (upsample2_kernel<T><<<ew_grid(total), 256, 0, ST>>>((const T*)src, (T*)dst, N, Ho, Wo, C)));
+  PDB_CHECK_ARG((int64_t)N * Ho * 2 < (1ll << 31), "pdb_upsample2_zero: too many rows");
+  PDB_DISPATCH_16(dtype, T, (upsample2_kernel<T><<<N * Ho * 2, 256, 0, ST>>>((const T*)src, (T*)dst, Ho, Wo, C)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -328,9 +340,8 @@ extern "C" int pdb_upsample2_zero(const void* src, void* dst, int dtype, int N, 
 extern "C" int pdb_add_strided2(const void* a, const void* b, void* out, int dtype, int N, int H, int W, int C,
                                 void* stream) {
   PDB_CHECK_ARG(a && b && out && N > 0 && H % 2 == 0 && W % 2 == 0 && C % 8 == 0, "pdb_add_strided2: bad arguments");
-  const int64_t total = (int64_t)N * H * W * (C / 8);
-  PDB_DISPATCH_16(dtype, T, (add_strided2_kernel<T><<<ew_grid(total), 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out,
-                                                                                     N, H, W, C)));
+  PDB_CHECK_ARG((int64_t)N * H < (1ll << 31), "pdb_add_strided2: too many rows");
+  PDB_DISPATCH_16(dtype, T, (add_strided2_kernel<T><<<N * H, 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out, H, W, C)));
   PDB_LAUNCH_CHECK();
   return 0;
 }

@@ -16,8 +16,10 @@ def _load() -> Optional[ctypes.CDLL]:
     global _lib, _err
     if _lib is not None or _err is not None:
         return _lib
+    from pathlib import Path
     from ..build import LIB
-    path = LIB / "libpdb200.so"
+    # PDB200_LIB: load another build of the kernel library (same C ABI) — for A/B timing of kernel variants
+    path = Path(os.environ["PDB200_LIB"]) if os.environ.get("PDB200_LIB") else LIB / "libpdb200.so"
     if not path.exists():
         _err = f"{path} not built (run: python -m pytorch_distributed_b200.build)"
         return None
