@@ -38,6 +38,8 @@ CASES = [
     ("wgrad", 2, 28, 28, 64, 64, 3, 3, 1, 1, 256),
     ("wgrad", 2, 28, 28, 128, 256, 3, 3, 1, 1, 256),
     ("wgrad", 2, 56, 56, 128, 128, 3, 3, 2, 1, 256),
+    ("stem", 4, 64, 64, 3, 64, 7, 7, 2, 3, 0),          # space-to-depth stem: fprop + statistics + wgrad
+    ("stem", 3, 224, 224, 3, 64, 7, 7, 2, 3, 0),
     ("wgrad", 2, 56, 56, 256, 512, 1, 1, 2, 0, 256),
     ("wgrad", 400, 1, 1, 2048, 1000, 1, 1, 1, 0, 256),  # fc
     ("wgrad", 3, 7, 7, 512, 512, 3, 3, 1, 1, 256),
@@ -46,11 +48,14 @@ CASES = [
 
 def run_one(case):
     import torch  # noqa: F401
-    from tests._gpu_helpers import conv_case, dgrad_case, wgrad_case
+    from tests._gpu_helpers import conv_case, dgrad_case, stem_case, wgrad_case
     kind, N, H, W, C, K, R, S, stride, pad, bn = case
     if kind == "fprop":
         e = conv_case(N, H, W, C, K, R, S, stride, pad, block_n=bn)
         return {"y": e[0], "stats": e[1]}
+    if kind == "stem":
+        e = stem_case(N, H, W)
+        return {"y": e[0], "stats": e[1], "dw": e[2]}
     if kind == "dgrad":
         return {"dx": dgrad_case(N, H, W, C, K, R, S, pad)}
     return {"dw": wgrad_case(N, H, W, C, K, R, S, stride, pad, block_n=bn)}

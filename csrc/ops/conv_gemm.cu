@@ -123,7 +123,10 @@ __device__ __forceinline__ float2 unpack2(uint32_t w) {
   return __half22float2(*reinterpret_cast<__half2*>(&w));
 }
 
-template <int BLOCK_N, bool kBf16, bool kPair>
+// kStem: the 7x7/2 stem as a 4x4/1 convolution over the space-to-depth input (16 channels per pixel, see
+// pdb_stem_fprop): a pipeline stage holds one row of four filter taps, each tap a [128 pixels x 32 B] block (A) and a
+// [64 couts x 32 B] block (B) in 32-byte-swizzled K-major layout; one MMA (K = 16) consumes one tap.
+template <int BLOCK_N, bool kBf16, bool kPair, bool kStem = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmD, const FpropParams p) {
@@ -176,7 +179,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0) {
     // ================================ TMA producer ================================
     if (elect_one()) {
-      int stage = 0;
+      int stage = 0, stem_loaded = 0;
       uint32_t phase = 0;
       TileWalk walk(unit, num_units, num_tiles, p.tile_period);
       for (int tile; walk.next(tile);) {
@@ -197,7 +200,20 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           mbar_wait(empty + stage, phase ^ 1);
           uint8_t* sA = smem + stage * L::STAGE_BYTES;
           uint8_t* sB = sA + A_STAGE_BYTES;
-          if (kPair) {
+          if (kStem) {
+            // stage kb = filter row kb of the 4x4 window: four taps, four loads.  kStages is a multiple of 4, so
+            // ring slot s only ever holds filter row s % 4: its weight block is loaded on the slot's first use and
+            // stays there for every later tile (the whole filter is 32 KB) — half the TMA operations per tile.
+            static_assert(!kStem || L::kStages % 4 == 0, "stem: ring slots must map to fixed filter rows");
+            const bool first_use = stem_loaded < kStages;
+            mbar_arrive_expect_tx(full + stage, first_use ? L::STAGE_BYTES : A_STAGE_BYTES);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              tma_load_im2col_4d(sA + t * (BLOCK_M * 32), &tmA, full + stage, 0, base_w, base_h, n_img, (uint16_t)t, (uint16_t)kb);
+              if (first_use) tma_load_2d(sB + t * (BLOCK_N * 32), &tmB, full + stage, (kb * 4 + t) * 16, n_blk * BLOCK_N);
+            }
+            stem_loaded += first_use ? 1 : 0;
+          } else if (kPair) {
             // both CTAs' bytes are credited to the leader's barrier; the peer only announces itself
             if (rank == 0) mbar_arrive_expect_tx(full + stage, 2 * L::STAGE_BYTES);
             else mbar_arrive_cluster(full + stage, 0);
@@ -226,7 +242,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   } else if (warp == 1 && rank == 0) {
     // ================================ MMA issuer (pair mode: leader CTA only) ======
     constexpr uint32_t idesc = umma_idesc_f16(kBf16 ? 1 : 0, kPair ? 2 * BLOCK_M : BLOCK_M, BLOCK_N, 0, 0);
-    constexpr uint64_t desc_base = umma_desc_base(0, 1024);        // K-major SW128: SBO = 8 rows x 128 B
+    // K-major SW128: SBO = 8 rows x 128 B.  Stem: K-major SW32, 8 rows x 32 B.
+    constexpr uint64_t desc_base = kStem ? umma_desc_base(0, 256, kLayoutSw32) : umma_desc_base(0, 1024);
+    constexpr uint32_t kStepA = kStem ? BLOCK_M * 32 : UMMA_K * 2, kStepB = kStem ? BLOCK_N * 32 : UMMA_K * 2;
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
     TileWalk walk(unit, num_units, num_tiles, p.tile_period);
@@ -242,7 +260,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const uint32_t b_addr = a_addr + A_STAGE_BYTES;
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            const uint64_t da = umma_desc(desc_base, a_addr + k * UMMA_K * 2), db = umma_desc(desc_base, b_addr + k * UMMA_K * 2);
+            const uint64_t da = umma_desc(desc_base, a_addr + k * kStepA), db = umma_desc(desc_base, b_addr + k * kStepB);
             if (kPair) umma_f16_2sm(d_tmem, da, db, idesc, (kb | k) != 0);
             else umma_f16(d_tmem, da, db, idesc, (kb | k) != 0);
           }
@@ -454,7 +472,9 @@ struct WgradSmem {
   static constexpr uint32_t TOTAL = BAR_OFFSET + 256 + 1024;
 };
 
-template <int BLOCK_N, bool kBf16>
+// kStem: X is the space-to-depth stem input (16 channels per pixel): the 256 output columns are 16 taps x 16
+// channels, loaded as sixteen [64 pixels x 32 B] blocks per stage in 32-byte-swizzled MN-major layout.
+template <int BLOCK_N, bool kBf16, bool kStem = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
                   const __grid_constant__ CUtensorMap tmB /* X: tiled [Mpix, C] or im2col (C,W,H,N) */,
@@ -529,7 +549,15 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
           // A: two boxes of [64 pixels][64 couts]; couts past Cout are zero-filled
           tma_load_2d(sA, &tmA, full + stage, m_blk * BLOCK_M, pix0);
           tma_load_2d(sA + CHUNK_BYTES, &tmA, full + stage, m_blk * BLOCK_M + 64, pix0);
-          if (p.b_im2col) {
+          if (kStem) {
+            const int n_img = (int)p.div_pq.div((uint32_t)pix0);
+            const int rem = pix0 - n_img * p.P * p.Q;
+            const int pp = (int)p.div_q.div((uint32_t)rem), qq = rem - pp * p.Q;
+#pragma unroll
+            for (int t = 0; t < 16; ++t)
+              tma_load_im2col_4d(sB + t * 2048, &tmB, full + stage, 0, qq - p.pad, pp - p.pad, n_img, (uint16_t)(t & 3),
+                                 (uint16_t)(t >> 2));
+          } else if (p.b_im2col) {
             const int n_img = (int)p.div_pq.div((uint32_t)pix0);
             const int rem = pix0 - n_img * p.P * p.Q;
             const int pp = (int)p.div_q.div((uint32_t)rem), qq = rem - pp * p.Q;
@@ -551,6 +579,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
     constexpr uint32_t idesc = umma_idesc_f16(kBf16 ? 1 : 0, BLOCK_M, BLOCK_N, 1, 1);
     // MN-major SW128: LBO = distance between 64-element MN atoms (one TMA box), SBO = 8 K-rows x 128 B
     constexpr uint64_t desc_base = umma_desc_base(CHUNK_BYTES, 1024);
+    // stem B operand, MN-major SW32: LBO = one [64 pixels x 32 B] tap block, SBO = 8 pixel rows x 32 B
+    constexpr uint64_t desc_base_b = kStem ? umma_desc_base(2048, 256, kLayoutSw32) : desc_base;
+    constexpr uint32_t kStepB = kStem ? UMMA_K * 32 : UMMA_K * 128;
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
@@ -568,7 +599,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
           const uint32_t b_addr = a_addr + L::A_BYTES;
 #pragma unroll
           for (int k = 0; k < 64 / UMMA_K; ++k) {       // 16 pixel rows x 128 B per MMA
-            umma_f16(d_tmem, umma_desc(desc_base, a_addr + k * UMMA_K * 128), umma_desc(desc_base, b_addr + k * UMMA_K * 128),
+            umma_f16(d_tmem, umma_desc(desc_base, a_addr + k * UMMA_K * 128), umma_desc(desc_base_b, b_addr + k * kStepB),
                      idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           umma_commit(empty + stage);
@@ -658,7 +689,7 @@ static CUtensorMapDataType tm_dtype(int dtype) {
 
 // 2-D row-major [rows, cols] 16-bit matrix with row pitch ld (elements); box = [box_rows, box_cols]
 static int make_tiled_2d(CUtensorMap* m, const void* ptr, int dtype, uint64_t rows, uint64_t cols, uint64_t ld,
-                         uint32_t box_rows, uint32_t box_cols) {
+                         uint32_t box_rows, uint32_t box_cols, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {ld * 2};
   cuuint32_t box[2] = {box_cols, box_rows};
@@ -667,7 +698,7 @@ static int make_tiled_2d(CUtensorMap* m, const void* ptr, int dtype, uint64_t ro
                 "tensor map: base must be 16-byte aligned and the row pitch a multiple of 16 bytes (ld=%llu)",
                 (unsigned long long)ld);
   CUresult r = g_tiled(m, tm_dtype(dtype), 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   PDB_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (rows=%llu cols=%llu ld=%llu box=%ux%u)",
                 (int)r, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows, box_cols);
@@ -675,17 +706,21 @@ static int make_tiled_2d(CUtensorMap* m, const void* ptr, int dtype, uint64_t ro
 }
 
 // NHWC activation as (C, W, H, N) in im2col mode; `pixels` consecutive output positions per load.
+// pad_hi < 0: symmetric padding.  cbox / swz: channels per load and the matching shared-memory swizzle (64 / 128B for
+// the regular layers, 16 / 32B for the space-to-depth stem).
 static int make_im2col_4d(CUtensorMap* m, const void* ptr, int dtype, int N, int H, int W, int C, int R, int S,
-                          int stride, int pad, uint32_t pixels) {
+                          int stride, int pad, uint32_t pixels, int pad_hi = -1, uint32_t cbox = 64,
+                          CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  if (pad_hi < 0) pad_hi = pad;
   int lower[2] = {-pad, -pad};
-  int upper[2] = {pad - (S - 1), pad - (R - 1)};
+  int upper[2] = {pad_hi - (S - 1), pad_hi - (R - 1)};
   cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
   PDB_CHECK_ARG((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (C * 2) % 16 == 0,
                 "im2col tensor map: base must be 16-byte aligned and C a multiple of 8");
-  CUresult r = g_im2col(m, tm_dtype(dtype), 4, const_cast<void*>(ptr), dims, strides, lower, upper, 64, pixels, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  CUresult r = g_im2col(m, tm_dtype(dtype), 4, const_cast<void*>(ptr), dims, strides, lower, upper, cbox, pixels, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   PDB_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeIm2col failed with %d (N=%d H=%d W=%d C=%d R=%d S=%d stride=%d pad=%d)",
                 (int)r, N, H, W, C, R, S, stride, pad);
@@ -737,13 +772,13 @@ static int launch_fprop_pair(const CUtensorMap& a, const CUtensorMap& b, const C
   return 0;
 }
 
-template <int BLOCK_N, bool kBf16>
+template <int BLOCK_N, bool kBf16, bool kStem = false>
 static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, FpropParams p,
                         cudaStream_t st) {
   // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute (the single-process
   // DataParallel mode launches from one process on every GPU)
   static bool configured[64] = {};
-  auto kernel = conv_fprop_kernel<BLOCK_N, kBf16, false>;
+  auto kernel = conv_fprop_kernel<BLOCK_N, kBf16, false, kStem>;
   int dev = 0;
   PDB_CUDA(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
@@ -758,10 +793,10 @@ static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtens
   return 0;
 }
 
-template <int BLOCK_N, bool kBf16>
+template <int BLOCK_N, bool kBf16, bool kStem = false>
 static int launch_wgrad(const CUtensorMap& a, const CUtensorMap& b, const WgradParams& p, cudaStream_t st) {
   static bool configured[64] = {};
-  auto kernel = conv_wgrad_kernel<BLOCK_N, kBf16>;
+  auto kernel = conv_wgrad_kernel<BLOCK_N, kBf16, kStem>;
   int dev = 0;
   PDB_CUDA(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
@@ -894,4 +929,61 @@ extern "C" int pdb_conv_wgrad(const void* x, const void* dy, float* dw, int dtyp
   if (bn == 128) return GO(128);
   return GO(256);
 #undef GO
+}
+
+// ---- the 7x7 / stride-2 / pad-3 stem on the space-to-depth input ---------------------------------------------------
+// xs: [N, Hs, Ws, 16] 16-bit (Hs = H/2, Ws = W/2; channel (dy*2 + dx)*3 + c holds x[c][2h+dy][2w+dx], 12..15 zero), so
+// the stem becomes a 4x4 / stride-1 convolution with padding 2 before and 1 after: output (p, q) reads rows
+// p-2 .. p+1.  ws: [64, 256] 16-bit, column (r*4 + s)*16 + ch (pdb_stem_weight_s2d).  No im2col matrix exists: TMA
+// im2col mode gathers the taps straight from xs (ref delegate: cuDNN's 7x7 stem on NCHW input).
+extern "C" int pdb_stem_fprop(const void* xs, const void* ws, void* y, int dtype, int N, int Hs, int Ws, float* stats,
+                              float* stats_scratch, void* stream) {
+  PDB_CHECK_ARG(xs && ws && y && N > 0 && Hs > 0 && Ws > 0, "pdb_stem_fprop: bad arguments");
+  PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16, "pdb_stem_fprop: dtype must be PDB_BF16 or PDB_FP16");
+  if (int e = load_driver_fns()) return e;
+  const int64_t M = (int64_t)N * Hs * Ws;
+  PDB_CHECK_ARG(M < (1ll << 31), "pdb_stem_fprop: too many pixels");
+  FpropParams p{};
+  p.M = (int)M, p.N = 64;
+  p.num_m_blocks = (int)((M + BLOCK_M - 1) / BLOCK_M), p.num_n_blocks = 1;
+  p.taps = 4, p.cin_blocks = 1, p.S = 4;         // four k-blocks: one filter row each
+  p.P = Hs, p.Q = Ws, p.stride = 1, p.pad = 2;
+  p.a_im2col = 1, p.accumulate = 0;
+  p.div_pq.init((uint32_t)(Hs * Ws)), p.div_q.init((uint32_t)Ws), p.div_nb.init(1u);
+  p.stats = stats, p.stats_rep = stats ? stats_scratch : nullptr, p.bias = nullptr;
+  CUtensorMap tmA, tmB, tmD;
+  if (int e = make_im2col_4d(&tmA, xs, dtype, N, Hs, Ws, 16, 4, 4, 1, 2, BLOCK_M, 1, 16, CU_TENSOR_MAP_SWIZZLE_32B)) return e;
+  if (int e = make_tiled_2d(&tmB, ws, dtype, 64, 256, 256, 64, 16, CU_TENSOR_MAP_SWIZZLE_32B)) return e;
+  if (int e = make_tiled_2d(&tmD, y, dtype, (uint64_t)M, 64, 64, BLOCK_M, 64)) return e;
+  cudaStream_t st = (cudaStream_t)stream;
+  return dtype == PDB_BF16 ? launch_fprop<64, true, true>(tmA, tmB, tmD, p, st)
+                           : launch_fprop<64, false, true>(tmA, tmB, tmD, p, st);
+}
+
+// dws[64, 256] (fp32, same column order as ws) += dY[M, 64]^T * im2col(xs); unpack with pdb_stem_dw_unpack.
+extern "C" int pdb_stem_wgrad(const void* xs, const void* dy, float* dws, int dtype, int N, int Hs, int Ws, int splits,
+                              void* stream) {
+  PDB_CHECK_ARG(xs && dy && dws && N > 0 && Hs > 0 && Ws > 0, "pdb_stem_wgrad: bad arguments");
+  PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16, "pdb_stem_wgrad: dtype must be PDB_BF16 or PDB_FP16");
+  if (int e = load_driver_fns()) return e;
+  const int64_t M = (int64_t)N * Hs * Ws;
+  PDB_CHECK_ARG(M < (1ll << 31), "pdb_stem_wgrad: too many pixels");
+  WgradParams p{};
+  p.Mpix = (int)M, p.Cout = 64, p.Ktot = 256, p.Kvalid = 256, p.ldw = 256;
+  p.num_m_blocks = 1, p.num_n_blocks = 1;
+  p.num_kb = (int)((M + 63) / 64);
+  if (splits <= 0) splits = num_sms();
+  if (splits > p.num_kb) splits = p.num_kb;
+  p.kb_per_split = (p.num_kb + splits - 1) / splits;
+  p.num_splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.cin_blocks = 1, p.S = 4;
+  p.P = Hs, p.Q = Ws, p.stride = 1, p.pad = 2;
+  p.b_im2col = 1;
+  p.div_pq.init((uint32_t)(Hs * Ws)), p.div_q.init((uint32_t)Ws), p.div_cin.init(1u);
+  p.dw = dws;
+  CUtensorMap tmA, tmB;
+  if (int e = make_tiled_2d(&tmA, dy, dtype, (uint64_t)M, 64, 64, 64, 64)) return e;
+  if (int e = make_im2col_4d(&tmB, xs, dtype, N, Hs, Ws, 16, 4, 4, 1, 2, 64, 1, 16, CU_TENSOR_MAP_SWIZZLE_32B)) return e;
+  cudaStream_t st = (cudaStream_t)stream;
+  return dtype == PDB_BF16 ? launch_wgrad<256, true, true>(tmA, tmB, p, st) : launch_wgrad<256, false, true>(tmA, tmB, p, st);
 }

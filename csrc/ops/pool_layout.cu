@@ -263,6 +263,56 @@ __global__ void __launch_bounds__(256) add_strided2_kernel(const T* __restrict__
   }
 }
 
+// ---- space-to-depth stem helpers (see pdb_stem_fprop) -------------------------------------------------------------
+// xs[n, p, q, (dy*2 + dx)*3 + c] = x[n, c, 2p + dy, 2q + dx]; channels 12..15 are zero.  One block per output row.
+template <typename T>
+__global__ void __launch_bounds__(128) stem_s2d_kernel(const float* __restrict__ x, T* __restrict__ xs, int H, int W) {
+  const int Hs = H / 2, Ws = W / 2;
+  const int n = blockIdx.x / Hs, p = blockIdx.x - n * Hs;
+  const int64_t HW = (int64_t)H * W;
+  const float* xn = x + (int64_t)n * 3 * HW + (int64_t)(2 * p) * W;
+  T* out = xs + ((int64_t)n * Hs + p) * Ws * 16;
+  for (int q = threadIdx.x; q < Ws; q += blockDim.x) {
+    float f[16];
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float2 v = __ldg(reinterpret_cast<const float2*>(xn + c * HW + dy * W + 2 * q));
+        f[(dy * 2 + 0) * 3 + c] = v.x, f[(dy * 2 + 1) * 3 + c] = v.y;
+      }
+    f[12] = f[13] = f[14] = f[15] = 0.f;
+    float lo[8], hi[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) lo[k] = f[k], hi[k] = f[8 + k];
+    stg128(out + q * 16, pack8<T>(lo));
+    stg128(out + q * 16 + 8, pack8<T>(hi));
+  }
+}
+
+// ws[k, (r*4 + s)*16 + (dy*2 + dx)*3 + c] = w[k, kh, kw, c] with kh = 2r + dy - 1, kw = 2s + dx - 1 (zero outside 0..6)
+template <typename T>
+__global__ void stem_weight_s2d_kernel(const T* __restrict__ w, T* __restrict__ ws, int K) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= K * 256) return;
+  const int k = i >> 8, col = i & 255, tap = col >> 4, ch = col & 15;
+  const int r = tap >> 2, s = tap & 3, d = ch / 3, c = ch - d * 3;
+  const int kh = 2 * r + (d >> 1) - 1, kw = 2 * s + (d & 1) - 1;
+  T v = Elem<T>::from_f(0.f);
+  if (ch < 12 && kh >= 0 && kh < 7 && kw >= 0 && kw < 7) v = w[k * 147 + (kh * 7 + kw) * 3 + c];
+  ws[i] = v;
+}
+
+// dw[k, kh, kw, c] (+)= dws[k, column of (kh, kw, c)]
+__global__ void stem_dw_unpack_kernel(const float* __restrict__ dws, float* __restrict__ dw, int K, int accumulate) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= K * 147) return;
+  const int k = i / 147, j = i - k * 147, tapc = j / 3, c = j - tapc * 3, kh = tapc / 7, kw = tapc - kh * 7;
+  const int r = (kh + 1) >> 1, dy = (kh + 1) & 1, s = (kw + 1) >> 1, dx = (kw + 1) & 1;
+  const float v = dws[k * 256 + (r * 4 + s) * 16 + (dy * 2 + dx) * 3 + c];
+  dw[i] = accumulate ? dw[i] + v : v;
+}
+
 }  // namespace pdb
 using namespace pdb;
 
@@ -438,6 +488,28 @@ extern "C" int pdb_weight_dgrad_layout_batched(const void* w_base, void* wt_base
   PDB_CHECK_ARG(w_base && wt_base && table_dev && n > 0 && n <= 65535, "pdb_weight_dgrad_layout_batched: bad arguments");
   dim3 grid(64, n);
   PDB_DISPATCH_16(dtype, T, (weight_dgrad_batched_kernel<T><<<grid, 256, 0, ST>>>((const T*)w_base, (T*)wt_base, table_dev)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_stem_s2d(const float* x, void* xs, int dtype, int N, int H, int W, void* stream) {
+  PDB_CHECK_ARG(x && xs && N > 0 && H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0, "pdb_stem_s2d: H and W must be even");
+  PDB_CHECK_ARG((reinterpret_cast<uintptr_t>(x) & 7) == 0, "pdb_stem_s2d: input must be 8-byte aligned");
+  PDB_DISPATCH_16(dtype, T, (stem_s2d_kernel<T><<<N * (H / 2), 128, 0, ST>>>(x, (T*)xs, H, W)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_stem_weight_s2d(const void* w, void* ws, int dtype, int K, void* stream) {
+  PDB_CHECK_ARG(w && ws && K > 0, "pdb_stem_weight_s2d: bad arguments");
+  PDB_DISPATCH_16(dtype, T, (stem_weight_s2d_kernel<T><<<(K * 256 + 255) / 256, 256, 0, ST>>>((const T*)w, (T*)ws, K)));
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_stem_dw_unpack(const float* dws, float* dw, int K, int accumulate, void* stream) {
+  PDB_CHECK_ARG(dws && dw && K > 0, "pdb_stem_dw_unpack: bad arguments");
+  stem_dw_unpack_kernel<<<(K * 147 + 255) / 256, 256, 0, ST>>>(dws, dw, K, accumulate);
   PDB_LAUNCH_CHECK();
   return 0;
 }

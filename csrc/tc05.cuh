@@ -123,9 +123,11 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 // ---- UMMA descriptors -----------------------------------------------------------------------
 // Shared-memory matrix descriptor (64 bit): [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4,
 // [46,48) version = 1 on sm_100, [49,52) base offset, [61,64) layout (2 = SWIZZLE_128B).
-__host__ __device__ constexpr uint64_t umma_desc_base(uint32_t lbo_bytes, uint32_t sbo_bytes) {
+constexpr uint32_t kLayoutSw128 = 2, kLayoutSw64 = 4, kLayoutSw32 = 6;       // descriptor bits [61,64)
+__host__ __device__ constexpr uint64_t umma_desc_base(uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                      uint32_t layout = kLayoutSw128) {
   return ((uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16) | ((uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32) |
-         ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+         ((uint64_t)1 << 46) | ((uint64_t)layout << 61);
 }
 __device__ __forceinline__ uint64_t umma_desc(uint64_t base, uint32_t smem_addr) {
   return base | (uint64_t)((smem_addr >> 4) & 0x3fff);

@@ -138,6 +138,18 @@ int pdb_nchw_f32_to_nhwc16(const float* x, void* y, int dtype, int N, int C, int
 /* Stem im2col: NCHW fp32 [N,3,H,W] -> [N*Ho*Wo, Kpad] 16-bit patches for the 7x7/2 pad-3 stem conv
  * (K = 147, columns ordered (kh, kw, c), zero padded to Kpad). */
 int pdb_stem_im2col(const float* x, void* col, int dtype, int N, int H, int W, int Kpad, void* stream);
+/* The 7x7 / stride-2 / pad-3 stem WITHOUT an im2col matrix: a 4x4 / stride-1 convolution over the space-to-depth
+ * input.  pdb_stem_s2d: x [N,3,H,W] fp32 -> xs [N,H/2,W/2,16] 16-bit, channel (dy*2+dx)*3+c = x[c][2h+dy][2w+dx],
+ * 12..15 zero.  pdb_stem_weight_s2d: w [K,7,7,3] 16-bit -> ws [K,256], column (r*4+s)*16 + channel.
+ * pdb_stem_fprop: y [N*Hs*Ws, 64] = conv (+ BatchNorm sums like pdb_conv_fprop).  pdb_stem_wgrad: dws [64,256] fp32
+ * += dY^T im2col(xs) (zero it first), then pdb_stem_dw_unpack folds it into dw [K,7,7,3] (accumulate != 0: add). */
+int pdb_stem_s2d(const float* x, void* xs, int dtype, int N, int H, int W, void* stream);
+int pdb_stem_weight_s2d(const void* w, void* ws, int dtype, int K, void* stream);
+int pdb_stem_fprop(const void* xs, const void* ws, void* y, int dtype, int N, int Hs, int Ws, float* stats,
+                   float* stats_scratch, void* stream);
+int pdb_stem_wgrad(const void* xs, const void* dy, float* dws, int dtype, int N, int Hs, int Ws, int splits,
+                   void* stream);
+int pdb_stem_dw_unpack(const float* dws, float* dw, int K, int accumulate, void* stream);
 /* out = a + b (16-bit), used where a residual sum is not fused into a producer. */
 int pdb_add16(const void* a, const void* b, void* out, int dtype, int64_t n, void* stream);
 /* dst[n, 2h, 2w, :] = src[n, h, w, :], zeros elsewhere: zero-upsample by 2 (stride-2 dgrad input). */

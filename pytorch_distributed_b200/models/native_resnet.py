@@ -154,6 +154,12 @@ class NativeResNetEngine:
         self.stem_conv = self._conv("conv1", model.conv1)
         self.stem_bn = self._bn("bn1", model.bn1)
         self.stem_w16 = torch.zeros(model.conv1.out_channels, STEM_KPAD, dtype=dtype, device=self.device)
+        # The standard 7x7/2 stem runs as a 4x4/1 convolution over the space-to-depth input, fed by TMA im2col loads
+        # (no patch matrix); any other stem geometry goes through the explicit im2col matrix.
+        c1 = self.stem_conv
+        self.stem_s2d = (c1.R, c1.S, c1.stride, c1.pad, c1.C, c1.K) == (7, 7, 2, 3, 3, 64)
+        self.stem_ws = torch.zeros(64, 256, dtype=dtype, device=self.device)
+        self.stem_dws = torch.zeros(64, 256, dtype=torch.float32, device=self.device)
         self.blocks: List[_BlockPlan] = []
         for li in range(1, 5):
             layer = getattr(model, f"layer{li}")
@@ -254,6 +260,8 @@ class NativeResNetEngine:
         """16-bit operand copies derived from the weight shadow: padded stem rows and, for training,
         the flipped/transposed layouts dgrad runs on."""
         c = self.stem_conv
+        if self.stem_s2d:
+            ops.stem_weight_s2d(c.w16, self.stem_ws)
         ops.pad_rows16(c.w16, self.stem_w16, c.K, c.R * c.S * c.C, STEM_KPAD)
         if need_dgrad:
             ops.weight_dgrad_layout_batched(self.arena.shadow, self.wt_all, self._wt_table, self._wt_table.shape[0])
@@ -303,12 +311,17 @@ class NativeResNetEngine:
         cv, bn = self.stem_conv, self.stem_bn
         P, Q = cv.out_hw(H, W)
         rows = N * P * Q
-        col = self._new(rows, STEM_KPAD)
-        ops.stem_im2col(x.contiguous().float(), col)
         y = self._new(N, P, Q, cv.K)
         sums = self.stats[bn.slot: bn.slot + 2 * bn.C] if train else None
-        ops.conv_fprop(col, self.stem_w16, y, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0), stats=sums,
-                       stats_scratch=self._fwd_scratch(bn) if train else None)
+        if self.stem_s2d and H % 2 == 0 and W % 2 == 0:
+            col = self._new(N, H // 2, W // 2, 16)          # space-to-depth input; also the wgrad operand
+            ops.stem_s2d(x.contiguous().float(), col)
+            ops.stem_fprop(col, self.stem_ws, y, stats=sums, stats_scratch=self._fwd_scratch(bn) if train else None)
+        else:
+            col = self._new(rows, STEM_KPAD)
+            ops.stem_im2col(x.contiguous().float(), col)
+            ops.conv_fprop(col, self.stem_w16, y, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0), stats=sums,
+                           stats_scratch=self._fwd_scratch(bn) if train else None)
         z = self._new(N, P, Q, cv.K)
         mask = None
         if train:
@@ -507,9 +520,14 @@ class NativeResNetEngine:
         dy0, _ = self._bn_bwd(self.stem_bn, dz0, m0, y0, want_dres=False)
         self._ready(*self.stem_bn.pindex)
         cv = self.stem_conv
-        rows = col.shape[0]
-        ops.conv_wgrad(col, dy0.view(rows, cv.K), cv.dw, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0),
-                       ldw=cv.R * cv.S * cv.C, kvalid=cv.R * cv.S * cv.C)
+        if col.dim() == 4:                                  # space-to-depth path
+            self.stem_dws.zero_()
+            ops.stem_wgrad(col, dy0, self.stem_dws)
+            ops.stem_dw_unpack(self.stem_dws, cv.dw, accumulate=True)
+        else:
+            rows = col.shape[0]
+            ops.conv_wgrad(col, dy0.view(rows, cv.K), cv.dw, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0),
+                           ldw=cv.R * cv.S * cv.C, kvalid=cv.R * cv.S * cv.C)
         self._ready(cv.pindex)
 
     def _segments(self):

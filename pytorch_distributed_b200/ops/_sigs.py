@@ -36,6 +36,11 @@ def declare(L):
     sig("pdb_avgpool_bwd", [P, P, c_int, c_int, c_int, c_int, P])
     sig("pdb_nchw_f32_to_nhwc16", [P, P, c_int, c_int, c_int, c_int, c_int, P])
     sig("pdb_stem_im2col", [P, P, c_int, c_int, c_int, c_int, c_int, P])
+    sig("pdb_stem_s2d", [P, P, c_int, c_int, c_int, c_int, P])
+    sig("pdb_stem_weight_s2d", [P, P, c_int, c_int, P])
+    sig("pdb_stem_fprop", [P, P, P, c_int, c_int, c_int, c_int, P, P, P])
+    sig("pdb_stem_wgrad", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])
+    sig("pdb_stem_dw_unpack", [P, P, c_int, c_int, P])
     sig("pdb_add16", [P, P, P, c_int, c_int64, P])
     sig("pdb_upsample2_zero", [P, P, c_int, c_int, c_int, c_int, c_int, P])
     sig("pdb_add_strided2", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])

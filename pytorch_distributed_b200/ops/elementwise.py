@@ -12,7 +12,8 @@ from ._sigs import ConvShape
 
 __all__ = ["dtype_tag", "sgd_step", "check_finite", "cast_to_16", "xent_fwd_bwd", "topk_correct", "bn_stats",
            "bn_apply", "bn_apply_eval", "bn_bwd_reduce", "bn_bwd_reduce_scratch_floats", "bn_bwd_apply", "maxpool_fwd", "maxpool_bwd",
-           "avgpool_fwd", "avgpool_bwd", "nchw_to_nhwc16", "stem_im2col", "add16", "upsample2_zero",
+           "avgpool_fwd", "avgpool_bwd", "nchw_to_nhwc16", "stem_im2col", "stem_s2d", "stem_weight_s2d", "stem_fprop",
+           "stem_wgrad", "stem_dw_unpack", "add16", "upsample2_zero",
            "add_strided2", "conv_fprop", "conv_wgrad", "weight_dgrad_layout", "weight_dgrad_layout_batched", "pad_rows16", "colsum16",
            "peer_copy", "peer_copy_", "reduce_to_root", "ConvShape"]
 
@@ -176,6 +177,46 @@ def stem_im2col(x: torch.Tensor, col: torch.Tensor) -> None:
     assert C == 3 and x.dtype == torch.float32 and x.is_contiguous()
     check(require().pdb_stem_im2col(ptr(x), ptr(col), dtype_tag(col.dtype), N, H, W, col.shape[-1], _st(x)),
           "pdb_stem_im2col")
+    count_launch()
+
+
+def stem_s2d(x: torch.Tensor, xs: torch.Tensor) -> None:
+    """x [N,3,H,W] fp32 -> xs [N,H/2,W/2,16] 16-bit space-to-depth (K7 stem without an im2col matrix)."""
+    N, C, H, W = x.shape
+    assert C == 3 and x.dtype == torch.float32 and x.is_contiguous() and xs.shape == (N, H // 2, W // 2, 16)
+    check(require().pdb_stem_s2d(ptr(x), ptr(xs), dtype_tag(xs.dtype), N, H, W, _st(x)), "pdb_stem_s2d")
+    count_launch()
+
+
+def stem_weight_s2d(w16: torch.Tensor, ws: torch.Tensor) -> None:
+    """w16: [K, 7, 7, 3] (physical order) 16-bit -> ws [K, 256]."""
+    K = ws.shape[0]
+    assert w16.numel() == K * 147 and ws.shape == (K, 256) and w16.dtype == ws.dtype
+    check(require().pdb_stem_weight_s2d(ptr(w16), ptr(ws), dtype_tag(ws.dtype), K, _st(ws)), "pdb_stem_weight_s2d")
+    count_launch()
+
+
+def stem_fprop(xs: torch.Tensor, ws: torch.Tensor, y: torch.Tensor, stats=None, stats_scratch=None) -> None:
+    N, Hs, Ws, C = xs.shape
+    assert C == 16 and ws.shape == (64, 256) and y.numel() == N * Hs * Ws * 64
+    check(require().pdb_stem_fprop(ptr(xs), ptr(ws), ptr(y), dtype_tag(xs.dtype), N, Hs, Ws, ptr(stats),
+                                   ptr(stats_scratch), _st(xs)), "pdb_stem_fprop")
+    count_launch()
+
+
+def stem_wgrad(xs: torch.Tensor, dy: torch.Tensor, dws: torch.Tensor, splits: int = 0) -> None:
+    """dws [64, 256] fp32 += dY^T im2col(xs); the caller zeroes dws."""
+    N, Hs, Ws, C = xs.shape
+    assert C == 16 and dws.shape == (64, 256) and dws.dtype == torch.float32 and dy.numel() == N * Hs * Ws * 64
+    check(require().pdb_stem_wgrad(ptr(xs), ptr(dy), ptr(dws), dtype_tag(xs.dtype), N, Hs, Ws, splits, _st(xs)),
+          "pdb_stem_wgrad")
+    count_launch()
+
+
+def stem_dw_unpack(dws: torch.Tensor, dw: torch.Tensor, accumulate: bool = True) -> None:
+    K = dws.shape[0]
+    assert dw.numel() == K * 147 and dw.dtype == torch.float32
+    check(require().pdb_stem_dw_unpack(ptr(dws), ptr(dw), K, int(accumulate), _st(dws)), "pdb_stem_dw_unpack")
     count_launch()
 
 

@@ -71,3 +71,37 @@ def dgrad_case(N, H, W, C, K, R, S, pad, dtype=torch.bfloat16, seed=0):
     xr = torch.zeros(N, C, H, W, device="cuda", requires_grad=True)
     F.conv2d(xr, w.float().permute(0, 3, 1, 2), padding=pad).backward(dy.float().permute(0, 3, 1, 2))
     return rel_err(dx, xr.grad.permute(0, 2, 3, 1))
+
+
+def stem_case(N=4, H=64, W=64, dtype=torch.bfloat16, seed=0):
+    """The 7x7/2 stem through the space-to-depth TMA path vs fp32 F.conv2d: (rel err y, stats, dW)."""
+    torch.backends.cudnn.allow_tf32 = False
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    x = torch.randn(N, 3, H, W, device="cuda", generator=g)
+    w = (torch.randn(64, 7, 7, 3, device="cuda", generator=g) / 147 ** 0.5)
+    w16 = w.to(dtype)
+    Hs, Ws = H // 2, W // 2
+    xs = torch.empty(N, Hs, Ws, 16, device="cuda", dtype=dtype)
+    ws = torch.empty(64, 256, device="cuda", dtype=dtype)
+    y = torch.full((N, Hs, Ws, 64), float("nan"), device="cuda", dtype=dtype)
+    st = torch.full((128,), float("nan"), device="cuda")
+    scratch = torch.zeros(16 * 128 + 32, device="cuda")
+    ops.stem_s2d(x, xs)
+    ops.stem_weight_s2d(w16, ws)
+    ops.stem_fprop(xs, ws, y, stats=st, stats_scratch=scratch)
+    torch.cuda.synchronize()
+    xr = x.to(dtype).float()
+    wr = w16.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)      # [64, 3, 7, 7]
+    ref = F.conv2d(xr, wr, stride=2, padding=3)
+    e_y = rel_err(y, ref.detach().permute(0, 2, 3, 1))
+    yf = y.float().reshape(-1, 64)
+    e_s = max(rel_err(st[:64], yf.sum(0)), rel_err(st[64:], (yf * yf).sum(0)))
+    dy = torch.randn(N, Hs, Ws, 64, device="cuda", generator=g).to(dtype)
+    dws = torch.zeros(64, 256, device="cuda")
+    dw = torch.full((64, 7, 7, 3), 1.0, device="cuda")
+    ops.stem_wgrad(xs, dy, dws)
+    ops.stem_dw_unpack(dws, dw, accumulate=True)
+    torch.cuda.synchronize()
+    ref.backward(dy.float().permute(0, 3, 1, 2))
+    e_w = rel_err(dw - 1.0, wr.grad.permute(0, 2, 3, 1))
+    return e_y, e_s, e_w

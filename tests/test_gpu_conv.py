@@ -64,3 +64,12 @@ def test_fprop_accumulate_epilogue(block_n):
     torch.cuda.synchronize()
     ref = y0.float() + (x.float().reshape(-1, C) @ w.float().reshape(K, C).t()).reshape(N, H, H, K)
     assert rel_err(y, ref) < TOL
+
+
+@pytest.mark.parametrize("shape", [(4, 64, 64), (2, 224, 224)])
+def test_stem_space_to_depth_path(shape):
+    """7x7/2 stem as a 4x4/1 conv over the space-to-depth input, operands gathered by TMA im2col loads with
+    32-byte swizzle (fprop + BN sums + wgrad) vs fp32 F.conv2d(stride=2, padding=3)."""
+    from ._gpu_helpers import stem_case
+    e_y, e_s, e_w = stem_case(*shape)
+    assert e_y < TOL and e_s < 1e-3 and e_w < 5e-3, (e_y, e_s, e_w)
