@@ -144,7 +144,10 @@ class NativeResNetEngine:
         self._scratch_floats = 0
         self.ddp = None
         import os
-        self.graphs = os.environ.get("PDB200_GRAPHS", "1") != "0" and not sync_bn
+        # SyncBN: the per-layer statistics exchange is one of our peer-memory kernels (stateless flag protocol), so
+        # it is captured and replayed like every other launch; with a torch.distributed fallback exchange the capture
+        # aborts (see _sync_stats) and the step stays eager.
+        self.graphs = os.environ.get("PDB200_GRAPHS", "1") != "0"
         self.graph_warmup = 2                     # eager steps per shape before capture
         self._plans: Dict[tuple, _StepPlan] = {}
         self._plan: Optional[_StepPlan] = None
@@ -280,6 +283,8 @@ class NativeResNetEngine:
             if comm is not None and hasattr(comm, "allreduce_small_"):
                 comm.allreduce_small_(buf)        # K6: peer-memory exchange, no NCCL call per BN layer
             else:
+                if buf.is_cuda and torch.cuda.is_current_stream_capturing():
+                    raise RuntimeError("SyncBN statistics go through torch.distributed here: not captured")
                 dist.all_reduce(buf)
             return float(dist.get_world_size())
         return 1.0
@@ -394,6 +399,7 @@ class NativeResNetEngine:
                     import warnings
                     warnings.warn(f"pdb200: CUDA-graph capture of the forward pass failed, staying eager: {e}")
                     plan.fwd_graph, plan.graphs_failed = None, True
+                    plan.cursor = 0               # the aborted capture consumed buffer slots: hand them out again
             if plan.fwd_graph is not None:
                 plan.x_static.copy_(x, non_blocking=True)
                 self._replay(plan.fwd_graph)

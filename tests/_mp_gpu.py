@@ -117,11 +117,12 @@ def ddp_native_worker(rank, world, port, out_dir, backend, sync_bn):
     ddp.attach_grad_scaler(sc)
     crit = CrossEntropyLoss()
     g = torch.Generator(device=dev).manual_seed(5)          # same stream on all ranks; each takes its slice
-    xs = torch.randn(3, world, 16, 3, 64, 64, device=dev, generator=g)
-    ys = torch.randint(0, 1000, (3, world, 16), device=dev, generator=g)
+    steps = 5              # two eager steps, then the captured forward / backward graphs are replayed
+    xs = torch.randn(steps, world, 16, 3, 64, 64, device=dev, generator=g)
+    ys = torch.randint(0, 1000, (steps, world, 16), device=dev, generator=g)
     ddp.train()
     losses = []
-    for s in range(3):
+    for s in range(steps):
         losses.append(float(harness.train_step(ddp, crit, opt, xs[s, rank], ys[s, rank], cfg, dev, sc, False)))
     torch.cuda.synchronize()
     arena = model._pdb200_arena
