@@ -65,6 +65,28 @@ __global__ void __launch_bounds__(256) check_finite_kernel(const float* __restri
   if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) *found_inf = 1.0f;
 }
 
+// K13: the amp scale update (torch:amp/grad_scaler.py:484-559, ATen amp_update_scale) as one thread on the device:
+// back off on a non-finite step, grow after `interval` clean steps (never to a non-finite scale), refresh 1/scale
+// (computed in double like torch's unscale_), clear the flag for the next step.  No host round trip.
+__global__ void scaler_update_kernel(float* scale, int* tracker, float* found_inf, float* inv_scale, float growth,
+                                     float backoff, int interval) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  float s = *scale;
+  int t = *tracker;
+  if (*found_inf > 0.f) {
+    s *= backoff;
+    t = 0;
+  } else if (++t >= interval) {
+    const float grown = s * growth;
+    if (isfinite(grown)) s = grown;
+    t = 0;
+  }
+  *scale = s;
+  *tracker = t;
+  *inv_scale = (float)(1.0 / (double)s);
+  *found_inf = 0.f;
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ src, T* __restrict__ dst, int64_t n4) {
   using T2 = typename Elem<T>::T2;
@@ -115,6 +137,16 @@ extern "C" int pdb_check_finite(const float* g, int64_t n, float* found_inf, voi
   using namespace pdb;
   PDB_CHECK_ARG(g && found_inf && n > 0 && n % 4 == 0, "pdb_check_finite: bad arguments");
   check_finite_kernel<<<flat_grid(n / 4), 256, 0, (cudaStream_t)stream>>>(g, n / 4, found_inf);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_scaler_update(float* scale, int* growth_tracker, float* found_inf, float* inv_scale, float growth,
+                                 float backoff, int interval, void* stream) {
+  using namespace pdb;
+  PDB_CHECK_ARG(scale && growth_tracker && found_inf && inv_scale && interval > 0, "pdb_scaler_update: bad arguments");
+  scaler_update_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(scale, growth_tracker, found_inf, inv_scale, growth, backoff,
+                                                           interval);
   PDB_LAUNCH_CHECK();
   return 0;
 }

@@ -41,6 +41,11 @@ int pdb_sgd_step(float* p, float* g, float* buf, void* shadow16, int shadow_dtyp
  * (torch:amp/grad_scaler.py:349-361 _amp_foreach_non_finite_check_and_unscale_; the un-scale itself
  * is folded into pdb_sgd_step / the all-reduce epilogue). */
 int pdb_check_finite(const float* g, int64_t n, float* found_inf, void* stream);
+/* amp scale update on the device (one thread): scale *= backoff and tracker = 0 if *found_inf > 0; otherwise
+ * ++tracker and, when it reaches `interval`, scale *= growth (kept if that would overflow) and tracker = 0.
+ * Also writes *inv_scale = 1/scale and clears *found_inf.  Delegate: torch GradScaler.update / amp_update_scale. */
+int pdb_scaler_update(float* scale, int* growth_tracker, float* found_inf, float* inv_scale, float growth,
+                      float backoff, int interval, void* stream);
 
 /* fp32 -> 16-bit copy of a flat range (weight shadow refresh after load_state_dict). */
 int pdb_cast_f32_to_16(const float* src, void* dst, int dtype, int64_t n, void* stream);

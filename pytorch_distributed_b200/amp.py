@@ -57,6 +57,12 @@ def autocast(dtype="fp16", enabled: bool = True, device_type: Optional[str] = No
         _state.dtype = prev
 
 
+def _native_ops():
+    """The kernel library when it can be used in this process, else None."""
+    from . import ops
+    return ops if ops.available() else None
+
+
 class GradScaler:
     def __init__(self, init_scale: float = 65536.0, growth_factor: float = 2.0,
                  backoff_factor: float = 0.5, growth_interval: int = 2000, enabled: bool = True,
@@ -165,6 +171,12 @@ class GradScaler:
 
     def update(self, new_scale: Optional[float] = None) -> None:
         if not self._enabled or self._scale is None:
+            return
+        if new_scale is None and self._scale.is_cuda and _native_ops() is not None:
+            # K13: one device thread does the whole update (scale, tracker, 1/scale, flag reset)
+            _native_ops().scaler_update(self._scale, self._growth_tracker, self._found_inf, self._inv_scale,
+                                        self._growth_factor, self._backoff_factor, self._growth_interval)
+            self._unscaled = False
             return
         if new_scale is not None:
             self._scale.fill_(float(new_scale))

@@ -10,7 +10,7 @@ from . import _lib
 from ._lib import check, count_launch, ptr, require, stream_ptr
 from ._sigs import ConvShape
 
-__all__ = ["dtype_tag", "sgd_step", "check_finite", "cast_to_16", "xent_fwd_bwd", "topk_correct", "bn_stats",
+__all__ = ["dtype_tag", "sgd_step", "check_finite", "scaler_update", "cast_to_16", "xent_fwd_bwd", "topk_correct", "bn_stats",
            "bn_apply", "bn_apply_eval", "bn_bwd_reduce", "bn_bwd_reduce_scratch_floats", "bn_bwd_apply", "maxpool_fwd", "maxpool_bwd",
            "avgpool_fwd", "avgpool_bwd", "nchw_to_nhwc16", "stem_im2col", "stem_s2d", "stem_weight_s2d", "stem_fprop",
            "stem_wgrad", "stem_dw_unpack", "add16", "upsample2_zero",
@@ -38,6 +38,14 @@ def sgd_step(p, g, buf, shadow, *, lr, momentum, dampening, weight_decay, nester
         check(L.pdb_sgd_step(ptr(p), ptr(g), ptr(buf), ptr(shadow), dtype_tag(shadow.dtype) if shadow is not None else 0,
                              p.numel(), lr, momentum, dampening, weight_decay, int(nesterov), int(maximize),
                              int(first_step), ptr(inv_scale), ptr(found_inf), int(zero_grad), _st(p)), "pdb_sgd_step")
+    count_launch()
+
+
+def scaler_update(scale, tracker, found_inf, inv_scale, growth: float, backoff: float, interval: int) -> None:
+    """GradScaler.update() as one device thread (K13): no tensor-select chain, no host sync."""
+    assert scale.dtype == torch.float32 and tracker.dtype == torch.int32
+    check(require().pdb_scaler_update(ptr(scale), ptr(tracker), ptr(found_inf), ptr(inv_scale), growth, backoff,
+                                      interval, _st(scale)), "pdb_scaler_update")
     count_launch()
 
 

@@ -212,3 +212,25 @@ def test_layout_helpers(dt):
     cs = torch.zeros(16, device="cuda")
     ops.colsum16(a.reshape(-1, 16), cs)
     assert rel_err(cs, a.float().reshape(-1, 16).sum(0)) < 1e-5
+
+
+def test_scaler_update_kernel_matches_tensor_path():
+    """The one-thread amp scale update (K13) against the tensor-select implementation the CPU path uses."""
+    from pytorch_distributed_b200 import amp
+    dev = torch.device("cuda")
+    events = [0, 0, 1, 0, 0, 0, 1, 1, 0, 0, 0, 0, 0]          # found_inf per step
+    a = amp.GradScaler(init_scale=1024.0, growth_interval=3, device=dev)
+    b = amp.GradScaler(init_scale=1024.0, growth_interval=3, device=torch.device("cpu"))
+    a._lazy_init(dev), b._lazy_init(torch.device("cpu"))
+    for inf in events:
+        a._found_inf.fill_(float(inf)), b._found_inf.fill_(float(inf))
+        a.update(), b.update()
+        assert a.get_scale() == b.get_scale()
+        assert int(a._growth_tracker.item()) == int(b._growth_tracker.item())
+        assert float(a._found_inf.item()) == 0.0
+        assert float(a._inv_scale.item()) == pytest.approx(1.0 / a.get_scale(), rel=1e-7)
+    # growth saturates instead of overflowing
+    c = amp.GradScaler(init_scale=3.0e38, growth_interval=1, device=dev)
+    c._lazy_init(dev)
+    c.update()
+    assert c.get_scale() == pytest.approx(3.0e38)
