@@ -24,6 +24,20 @@ def main():
         bn = int(sys.argv[2]) if len(sys.argv) > 2 else 0
         for _ in range(6):
             ops.conv_fprop(x, w, y, ConvShape(N, H, H, C, K, 1, 1, 1, 0), stats=st, block_n=bn)
+    elif what == "stem":
+        x = torch.randn(N, 3, 224, 224, device="cuda")
+        w16 = (torch.randn(64, 7, 7, 3, device="cuda") * 0.08).to(dt)
+        xs = torch.empty(N, 112, 112, 16, device="cuda", dtype=dt)
+        ws = torch.empty(64, 256, device="cuda", dtype=dt)
+        y = torch.empty(N, 112, 112, 64, device="cuda", dtype=dt)
+        dy = torch.randn(N, 112, 112, 64, device="cuda").to(dt)
+        st, scr = torch.zeros(128, device="cuda"), torch.zeros(16 * 128 + 32, device="cuda")
+        dws = torch.zeros(64, 256, device="cuda")
+        ops.stem_s2d(x, xs)
+        ops.stem_weight_s2d(w16, ws)
+        for _ in range(4):
+            ops.stem_fprop(xs, ws, y, stats=st, stats_scratch=scr)
+            ops.stem_wgrad(xs, dy, dws)
     elif what in ("fprop", "wgrad"):
         H, C, K, R = 14, 256, 256, 3
         x = torch.randn(N, H, H, C, device="cuda", dtype=dt)
