@@ -71,6 +71,9 @@ class NativeComm:
         self._events: List[torch.cuda.Event] = []
         self._pass_started = False
         self._found_inf: Optional[torch.Tensor] = None
+        # --profile: an event pair around every bucket's kernel (per-bucket bus GB/s in the JSONL log)
+        self.profile = False
+        self._bucket_marks: List[tuple] = []
         torch.cuda.synchronize(self.device)
         dist.barrier(group)
 
@@ -145,6 +148,10 @@ class NativeComm:
                 self.flag.zero_()
             self._found_inf = found_inf
             n = end - start
+            t0 = None
+            if self.profile:
+                t0 = torch.cuda.Event(enable_timing=True)
+                t0.record(self.stream)
             if wire_dtype in (torch.float16, torch.bfloat16) and n % 8 == 0:
                 wm, half = self._wire_staging(wire_dtype, n)
                 check(require().pdb_allreduce_inplace_wire16(
@@ -153,9 +160,11 @@ class NativeComm:
                     (1.0 / self.world) if average else 1.0, ptr(inv_scale), self._blocks(m, n),
                     ctypes.c_void_p(self.stream.cuda_stream)), "pdb_allreduce_inplace_wire16")
                 count_launch()
-                done = torch.cuda.Event()
+                done = torch.cuda.Event(enable_timing=t0 is not None)
                 done.record(self.stream)
                 self._events.append(done)
+                if t0 is not None:
+                    self._bucket_marks.append((4 * n, t0, done))
                 return
             check(require().pdb_allreduce_inplace(
                 m.bufs, m.pads, self._flag_ptrs if found_inf is not None else None,
@@ -163,9 +172,25 @@ class NativeComm:
                 (1.0 / self.world) if average else 1.0, ptr(inv_scale), self._blocks(m, n),
                 ctypes.c_void_p(self.stream.cuda_stream)), "pdb_allreduce_inplace")
             count_launch()
-            done = torch.cuda.Event()
+            done = torch.cuda.Event(enable_timing=t0 is not None)
             done.record(self.stream)
+            if t0 is not None:
+                self._bucket_marks.append((4 * n, t0, done))
         self._events.append(done)
+
+    def bucket_times(self, link_gbs: float = 770.0):
+        """Device time of every bucket all-reduce since the last call (needs ``profile = True`` and a completed
+        step): bytes, microseconds, bus bandwidth 2(w-1)/w * bytes / t, and its fraction of the NVLink roofline.
+        In-step numbers include waiting for the slowest rank at the kernel's first cross-rank barrier."""
+        out = []
+        for nbytes, t0, t1 in self._bucket_marks:
+            t1.synchronize()
+            us = 1e3 * t0.elapsed_time(t1)
+            bus = 2.0 * (self.world - 1) / self.world * nbytes / max(us, 1e-3) / 1e3        # GB/s
+            out.append({"bytes": nbytes, "us": round(us, 1), "bus_gbs": round(bus, 1),
+                        "roofline_frac": round(bus / link_gbs, 3)})
+        self._bucket_marks.clear()
+        return out
 
     def wait_all(self) -> None:
         cur = torch.cuda.current_stream(self.device)

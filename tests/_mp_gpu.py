@@ -122,11 +122,14 @@ def ddp_native_worker(rank, world, port, out_dir, backend, sync_bn):
     ys = torch.randint(0, 1000, (steps, world, 16), device=dev, generator=g)
     ddp.train()
     losses = []
+    if hasattr(ddp.comm, "bucket_times"):
+        ddp.comm.profile = True                 # event pair around every bucket all-reduce
     for s in range(steps):
         losses.append(float(harness.train_step(ddp, crit, opt, xs[s, rank], ys[s, rank], cfg, dev, sc, False)))
     torch.cuda.synchronize()
     arena = model._pdb200_arena
-    torch.save({"losses": losses, "params": arena.params.detach().cpu().clone(), "comm": ddp.comm.name,
+    buckets = ddp.comm.bucket_times() if hasattr(ddp.comm, "bucket_times") else None
+    torch.save({"losses": losses, "params": arena.params.detach().cpu().clone(), "comm": ddp.comm.name, "buckets": buckets,
                 "bufs": model._pdb200_buffer_arena.floats.detach().cpu().clone(), "scale": sc.get_scale()},
                os.path.join(out_dir, f"ddp_{backend}_{int(sync_bn)}_{rank}.pt"))
     dist.barrier()

@@ -42,6 +42,9 @@ def test_ddp_native_comm_matches_nccl_backend(tmp_path, free_port, sync_bn):
     nat = [torch.load(tmp_path / f"ddp_native_{int(sync_bn)}_{r}.pt") for r in range(world)]
     ref = [torch.load(tmp_path / f"ddp_nccl_{int(sync_bn)}_{r}.pt") for r in range(world)]
     assert nat[0]["comm"] == "native" and ref[0]["comm"] == "torch"
+    # --profile bookkeeping: one timed entry per bucket and step, with a sane bandwidth figure
+    bt = nat[0]["buckets"]
+    assert bt and len(bt) % 5 == 0 and all(b["us"] > 0 and b["bus_gbs"] > 0 and b["bytes"] > 0 for b in bt)
     for r in range(1, world):
         assert torch.equal(nat[0]["params"], nat[r]["params"])        # replicas stay bit-identical
     for r in range(world):
