@@ -42,6 +42,12 @@ def avg_hook(state, bucket):
     import torch.distributed as dist
     state["calls"] += 1
     t = bucket.buffer()
+    # the view a hook gets: parameters of this bucket, their gradients aliasing the bucket's address range
+    ps, gs = bucket.parameters(), bucket.gradients()
+    assert len(ps) == len(gs) > 0 and sum(g.numel() for g in gs) <= t.numel()
+    lo, hi = t.data_ptr(), t.data_ptr() + 4 * t.numel()
+    assert all(lo <= g.data_ptr() < hi for g in gs)
+    assert isinstance(bucket.index(), int) and isinstance(bucket.is_last(), bool)
     t.div_(dist.get_world_size())
     return dist.all_reduce(t, async_op=True).get_future().then(lambda f: f.value()[0])
 
