@@ -6,6 +6,8 @@ backward launches of cuDNN / ATen kernels per step, NCHW tensors, autograd bookk
 
   conv  : tcgen05/TMA implicit GEMM (csrc/ops/conv_gemm.cu); its epilogue also produces the
           per-channel sum / sum-of-squares the following BatchNorm needs;
+  stem  : the 7x7/2 convolution as a 4x4/1 convolution over the space-to-depth input, operands gathered by
+          TMA im2col loads (no patch matrix; any other stem geometry falls back to an explicit im2col);
   BN    : one fused normalise(+residual)+ReLU pass forward, one reduce + one apply pass backward
           (csrc/ops/batchnorm.cu);
   dgrad : the same GEMM kernel on dY with flipped/transposed weights (stride-2 layers run on a
