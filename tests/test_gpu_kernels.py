@@ -234,3 +234,24 @@ def test_scaler_update_kernel_matches_tensor_path():
     c._lazy_init(dev)
     c.update()
     assert c.get_scale() == pytest.approx(3.0e38)
+
+
+def test_weight_dgrad_layout_batched_matches_permute():
+    """wt[c][r][s][k] = w[k][R-1-r][S-1-s][c] for a table of layers in one launch (tiled transpose), incl. sizes that
+    are not multiples of the 32 x 32 tile."""
+    layers = [(40, 3, 3, 24), (64, 1, 1, 64), (1000, 1, 1, 2048), (128, 3, 3, 128), (8, 7, 7, 8)]
+    g = torch.Generator(device="cuda").manual_seed(3)
+    n = sum(K * R * S * C for K, R, S, C in layers)
+    w = torch.randn(n, device="cuda", generator=g).bfloat16()
+    wt = torch.full((n,), float("nan"), device="cuda", dtype=torch.bfloat16)
+    rows, off = [], 0
+    for K, R, S, C in layers:
+        rows.append([off, off, K, R, S, C])
+        off += K * R * S * C
+    table = torch.tensor(rows, dtype=torch.int64, device="cuda")
+    ops.weight_dgrad_layout_batched(w, wt, table, len(layers))
+    torch.cuda.synchronize()
+    for o, _, K, R, S, C in rows:
+        src = w[o:o + K * R * S * C].view(K, R, S, C)
+        want = src.flip(1, 2).permute(3, 1, 2, 0).contiguous()          # [C, R, S, K]
+        assert torch.equal(wt[o:o + K * R * S * C].view(C, R, S, K), want), (K, R, S, C)
