@@ -150,7 +150,8 @@ def train(dataloader, model, criterion, optimizer, scheduler, epoch: int, start_
         samples, labels = to_device(batch, device)
         timer = None
         ddp_comm = getattr(model, "comm", None)
-        if getattr(cfg, "profile", False) and logger is not None and logger.enabled:
+        # every rank times the step (the max over ranks is a collective); only the main rank has a log to write to
+        if getattr(cfg, "profile", False) and cfg.log_jsonl:
             timer = metrics.DeviceTimer(device)
             timer.start()
             if hasattr(ddp_comm, "bucket_times"):
@@ -160,9 +161,10 @@ def train(dataloader, model, criterion, optimizer, scheduler, epoch: int, start_
         if timer is not None:
             ms = metrics.max_over_ranks(timer.stop(), device)       # device-timed, max over ranks
             extra = {"buckets": ddp_comm.bucket_times()} if hasattr(ddp_comm, "bucket_times") else {}
-            logger.log(event="step_time", epoch=epoch, step=step, ms=ms,
-                       images_per_s=samples.size(0) * max(1, comm.get_world_size() if cfg.mode in ("ddp", "ddp_amp") else 1) / (ms / 1e3),
-                       **extra)
+            if logger is not None and logger.enabled:
+                logger.log(event="step_time", epoch=epoch, step=step, ms=ms,
+                           images_per_s=samples.size(0) * max(1, comm.get_world_size() if cfg.mode in ("ddp", "ddp_amp") else 1) / (ms / 1e3),
+                           **extra)
 
         if cfg.empty_cache and device.type == "cuda" and cfg.mode != "single":
             torch.cuda.synchronize()

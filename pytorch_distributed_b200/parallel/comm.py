@@ -13,6 +13,7 @@ interchangeable backends for the arena collectives DDP needs:
 from __future__ import annotations
 
 import datetime
+import time
 from typing import List, Optional
 
 import torch
@@ -71,6 +72,8 @@ class TorchComm:
         self.world = dist.get_world_size(group) if is_initialized() else 1
         self.rank = dist.get_rank(group) if is_initialized() else 0
         self._works: List = []
+        self.profile = False                      # --profile: wall time per bucket (launch -> completion of its wait)
+        self._bucket_marks: List = []
 
     def register_arena(self, arena) -> None:      # nothing to map
         return None
@@ -84,6 +87,7 @@ class TorchComm:
         if self.world == 1:
             return
         seg = flat[start:end]
+        t0 = time.perf_counter() if self.profile else None
         if wire_dtype is not None and wire_dtype != seg.dtype:
             # fp16/bf16_compress_hook semantics (torch:distributed/algorithms/ddp_comm_hooks/
             # default_hooks.py:57-134): cast, pre-divide, reduce, copy back.
@@ -91,19 +95,33 @@ class TorchComm:
             if average:
                 wire.div_(self.world)
             work = dist.all_reduce(wire, group=self.group, async_op=True)
-            self._works.append((work, seg, wire))
+            self._works.append((work, seg, wire, t0))
         else:
             if average:
                 seg.div_(self.world)
             work = dist.all_reduce(seg, group=self.group, async_op=True)
-            self._works.append((work, None, None))
+            self._works.append((work, None, seg, t0))
 
     def wait_all(self) -> None:
-        for work, seg, wire in self._works:
+        for work, seg, wire, t0 in self._works:
             work.wait()
             if seg is not None:
                 seg.copy_(wire)
+            if t0 is not None:
+                self._bucket_marks.append((wire.numel() * 4, time.perf_counter() - t0))
         self._works.clear()
+
+    def bucket_times(self, link_gbs: float = 770.0):
+        """Same record layout as NativeComm.bucket_times, but HOST-timed (launch to completed wait), which is all a
+        torch.distributed work handle offers; bytes are counted as fp32 gradients."""
+        out = []
+        for nbytes, sec in self._bucket_marks:
+            us = 1e6 * sec
+            bus = 2.0 * (self.world - 1) / self.world * nbytes / max(us, 1e-3) / 1e3
+            out.append({"bytes": nbytes, "us": round(us, 1), "bus_gbs": round(bus, 3),
+                        "roofline_frac": round(bus / link_gbs, 4), "timed": "host"})
+        self._bucket_marks.clear()
+        return out
 
 
 _active_native = None        # the NativeComm of the default group, once one exists (used by reduce())

@@ -45,10 +45,20 @@ def test_shims_import():
     ("resnet_ddp_apex.py", ["--gpus", "2"]),
 ])
 def test_entry_points_run(script, extra, tmp_path, free_port):
+    log = tmp_path / "steps.jsonl"
+    if script == "restnet_ddp.py":
+        extra = [*extra, "--profile", "--log-jsonl", str(log)]
     r = _run(script, [*extra, "--save-path", str(tmp_path)], env={"MASTER_PORT": str(free_port)})
     assert r.returncode == 0, r.stderr[-2000:]
     assert "cost time per epoch:" in r.stdout and "Acc1:" in r.stdout
     assert r.stdout.count("cost time per epoch:") == 1          # rank-0-only print in the DDP modes
+    if script == "restnet_ddp.py":
+        # --profile: per-step time (max over ranks) and one record per gradient bucket
+        import json
+        recs = [json.loads(l) for l in log.read_text().splitlines()]
+        steps = [x for x in recs if x.get("event") == "step_time"]
+        assert steps and all(x["ms"] > 0 and x["images_per_s"] > 0 for x in steps)
+        assert all(x["buckets"] and all(b["bytes"] > 0 and b["us"] > 0 for b in x["buckets"]) for x in steps)
 
 
 def test_suspend_writes_latest_once_and_resume_continues(tmp_path):
