@@ -376,6 +376,16 @@ def main():
     p.add_argument("--sync-bn", action="store_true")
     args = p.parse_args()
     args.warmup = max(3, args.warmup)
+    import torch
+    if not torch.cuda.is_available():
+        # the metric is device-timed on B200s; without a GPU there is nothing to measure — say so in one line
+        if int(os.environ.get("RANK", "0")) == 0:
+            if args.impl == "reference":
+                print(json.dumps({"impl": "reference", "unavailable": "no CUDA device on this machine"}))
+            else:
+                print(json.dumps({"impl": "ours", "error": "no CUDA device on this machine: bench.py times the training "
+                                  "step on B200 GPUs (run it through gpurun)"}))
+        sys.exit(0 if args.impl == "reference" else 1)
     if args.impl == "reference":
         run_reference(args)
     else:
