@@ -73,3 +73,27 @@ def test_spawn_reports_signal():
 def test_spawn_suspend_is_not_a_failure():
     pc = launcher.spawn(H.child_suspends, nprocs=2, grace_period=5)
     assert pc.suspended
+
+
+def test_c_header_and_ctypes_signatures_cover_the_same_entry_points():
+    """Every kernel entry point declared in include/pdb200.h has a ctypes signature (ops/_sigs.py) with the same
+    number of parameters, and nothing is declared to ctypes that the header does not have."""
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "pdb200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    decl = {}
+    for m in re.finditer(r"\b(?:int|size_t|const char\*)\s+(pdb_\w+)\s*\(([^;{]*?)\)\s*;", header, flags=re.S):
+        args = m.group(2).strip()
+        decl[m.group(1)] = 0 if args in ("", "void") else len([a for a in args.split(",") if a.strip()])
+    sigs_src = open(os.path.join(root, "pytorch_distributed_b200", "ops", "_sigs.py")).read()
+    sigs = {}
+    for m in re.finditer(r'sig\(\s*"(pdb_\w+)"\s*,\s*\[(.*?)\]', sigs_src, flags=re.S):
+        body = m.group(2).strip()
+        sigs[m.group(1)] = 0 if not body else len([a for a in re.split(r",(?![^()]*\))", body) if a.strip()])
+    assert len(decl) > 40 and len(sigs) > 30
+    missing = sorted(set(sigs) - set(decl))
+    assert not missing, f"ctypes signatures without a declaration in pdb200.h: {missing}"
+    for name, n in sigs.items():
+        assert decl[name] == n, f"{name}: header has {decl[name]} parameters, _sigs.py has {n}"
