@@ -39,6 +39,7 @@ class TrainConfig:
     save_path: Optional[str] = None
     # -- bench / portability knobs (not in the reference) ------------------------
     synthetic: bool = True         # no ImageNet on this box; data.py makes ImageNet-shaped tensors
+    data_root: Optional[str] = None   # <root>/{train,val}/<class>/<image>: real data through data/folder.py
     image_size: int = 224
     num_classes: int = 1000
     train_samples: int = 1_281_167
@@ -64,6 +65,8 @@ class TrainConfig:
             raise ValueError(f"mode must be one of {MODES}, got {self.mode!r}")
         if self.save_path is None:
             self.save_path = _SAVE_DIRS[self.mode]
+        if self.data_root:
+            self.synthetic = False
 
     @property
     def save_dir(self) -> Path:
@@ -100,6 +103,8 @@ def add_arguments(p: argparse.ArgumentParser, mode: str) -> argparse.ArgumentPar
     p.add_argument("--weight-decay", type=float, default=d.weight_decay)
     p.add_argument("--save-path", type=str, default=d.save_path)
     p.add_argument("--synthetic", action=argparse.BooleanOptionalAction, default=True)
+    p.add_argument("--data-root", type=str, default=None,
+                   help="image-folder ImageNet (<root>/{train,val}/<class>/<image>); implies --no-synthetic")
     p.add_argument("--image-size", type=int, default=d.image_size)
     p.add_argument("--num-classes", type=int, default=d.num_classes)
     p.add_argument("--train-samples", type=int, default=d.train_samples)

@@ -16,6 +16,7 @@ Two assembly strategies:
 from __future__ import annotations
 
 import math
+import os
 import queue
 import threading
 from typing import Iterator, Optional, Tuple
@@ -81,11 +82,17 @@ class SyntheticImageNet:
                            prefetch=prefetch)
 
 
-def ImageNet(split: str = "train", transform=None, synthetic: bool = True, **kw):
-    """``hfai.datasets.ImageNet`` call shape (ref:restnet_ddp.py:107,117)."""
+def ImageNet(split: str = "train", transform=None, synthetic: bool = True, root: Optional[str] = None, **kw):
+    """``hfai.datasets.ImageNet`` call shape (ref:restnet_ddp.py:107,117).  ``synthetic=False`` reads an image-folder
+    tree ``root/{train,val}/<class>/<image>`` (data/folder.py); the reference's own ffrecord files need the
+    High-Flyer cluster file system and are not readable here."""
     if not synthetic:
-        raise RuntimeError("the ffrecord ImageNet reader of the reference (hfai.datasets) needs the "
-                           "High-Flyer cluster file system; only synthetic=True is available here")
+        root = root or os.environ.get("PDB200_DATA_ROOT")
+        if not root:
+            raise RuntimeError("real data needs --data-root (or PDB200_DATA_ROOT) pointing at <root>/{train,val}/<class>/"
+                               "<image>; the reference's ffrecord reader (hfai.datasets) is closed")
+        from .folder import ImageFolder
+        return ImageFolder(root, split=split, transform=transform, seed=kw.get("seed", 0))
     return SyntheticImageNet(split=split, transform=transform, **kw)
 
 

@@ -25,9 +25,13 @@ def _as_float_chw(img: torch.Tensor) -> torch.Tensor:
 
 
 def _resize(img: torch.Tensor, size) -> torch.Tensor:
+    """Antialiased bilinear resize.  uint8 in -> uint8 out (rounded), like torchvision on uint8 tensors / PIL images,
+    so that the ToTensor that follows still sees 8-bit pixels and rescales them to [0, 1]."""
     x = _as_float_chw(img).unsqueeze(0)
-    x = F.interpolate(x, size=size, mode="bilinear", align_corners=False, antialias=True)
-    return x.squeeze(0)
+    x = F.interpolate(x, size=size, mode="bilinear", align_corners=False, antialias=True).squeeze(0)
+    if img.dtype == torch.uint8:
+        x = x.round_().clamp_(0, 255).to(torch.uint8)
+    return x
 
 
 class Compose:

@@ -278,15 +278,18 @@ def main(cfg: TrainConfig, local_rank: int = 0) -> float:
 
     S = cfg.image_size
     train_dataset = ImageNet(split="train", transform=None if cfg.synthetic else transforms.train_transform(S),
-                             synthetic=cfg.synthetic, num_samples=cfg.train_samples, image_size=S,
+                             synthetic=cfg.synthetic, root=cfg.data_root, num_samples=cfg.train_samples, image_size=S,
                              num_classes=cfg.num_classes, seed=cfg.seed)
     val_dataset = ImageNet(split="val", transform=None if cfg.synthetic else transforms.val_transform(S),
-                           synthetic=cfg.synthetic, num_samples=cfg.val_samples, image_size=S,
+                           synthetic=cfg.synthetic, root=cfg.data_root, num_samples=cfg.val_samples, image_size=S,
                            num_classes=cfg.num_classes, seed=cfg.seed)
     train_sampler = DistributedSampler(train_dataset) if distributed else None
     val_sampler = DistributedSampler(val_dataset) if distributed else None
+    # real data without a sampler (single / dp): the reference's loader call carries no shuffle argument
+    # (ref:resnet_single_gpu.py:95) — training on class-sorted folders needs one, so it is on for real data
+    extra = {} if cfg.synthetic else {"shuffle": True}
     train_loader = train_dataset.loader(batch_size=loader_batch, sampler=train_sampler,
-                                        num_workers=cfg.num_workers, pin_memory=True)
+                                        num_workers=cfg.num_workers, pin_memory=True, **extra)
     val_loader = val_dataset.loader(batch_size=loader_batch, sampler=val_sampler,
                                     num_workers=cfg.num_workers, pin_memory=True)
 
@@ -313,6 +316,8 @@ def main(cfg: TrainConfig, local_rank: int = 0) -> float:
             t1 = time.time()
             if train_sampler is not None:
                 train_sampler.set_epoch(epoch)
+            if hasattr(train_dataset, "set_epoch"):
+                train_dataset.set_epoch(epoch)          # fresh augmentation draws / permutation (real data)
             train(train_loader, wrapped, criterion, optimizer, scheduler, epoch, start_step, best_acc,
                   save_path, cfg, device, local_rank, loss_scaler, logger)
             start_step = 0

@@ -43,7 +43,7 @@ def topk_correct(logits: torch.Tensor, labels: torch.Tensor, ks=(1, 5)) -> torch
         from . import ops
         if ops.available():
             return ops.topk_correct(logits, labels, ks)
-    kmax = max(ks)
+    kmax = min(max(ks), logits.size(-1))      # fewer than five classes: top-5 is "any class" (torch.topk would raise)
     _, preds = logits.topk(kmax, -1, True, True)
     hit = torch.eq(preds, labels.unsqueeze(1))
     return torch.stack([hit[:, :k].sum() for k in ks]).to(torch.float32)
