@@ -70,8 +70,14 @@ class SyntheticImageNet:
             raise IndexError(idx)
         img = self._pool_images()[idx % self.pool]
         if self.transform is not None:
-            g = torch.Generator().manual_seed(self.seed * 1_000_003 + idx)
-            img = self.transform(img, g)
+            from . import transforms as T
+            if isinstance(self.transform, T.Compose):
+                g = torch.Generator().manual_seed(self.seed * 1_000_003 + idx)
+                img = self.transform(img, g)
+            else:
+                # a torchvision-style (PIL) pipeline handed in by a reference-style script (ref:restnet_ddp.py:100-107)
+                from PIL import Image
+                img = self.transform(Image.fromarray(img.permute(1, 2, 0).numpy()))
         label = int(_label_of(torch.tensor(idx), self.num_classes))
         return img, label
 

@@ -124,3 +124,12 @@ def test_image_folder_accepts_torchvision_transforms(tmp_path):
     assert x.shape == (3, 16, 16) and x.dtype == torch.float32 and y == 1
     xb, yb = next(iter(ds.loader(batch_size=4, num_workers=2, pin_memory=False)))
     assert xb.shape == (4, 3, 16, 16) and yb.tolist() == [0, 0, 1, 1]
+
+
+def test_hfai_shim_reads_real_data_when_a_root_is_configured(tmp_path, monkeypatch):
+    import hfai
+    _make_image_tree(tmp_path, classes=2, per_class=2)
+    assert type(hfai.datasets.ImageNet("val", num_samples=4, image_size=8)).__name__ == "SyntheticImageNet"
+    monkeypatch.setenv("PDB200_DATA_ROOT", str(tmp_path))
+    ds = hfai.datasets.ImageNet("val", transform=transforms.val_transform(8))
+    assert type(ds).__name__ == "ImageFolder" and len(ds) == 4
