@@ -93,6 +93,7 @@ class FolderLoader:
         self.shuffle = bool(shuffle) and sampler is None
         self.num_workers, self.drop_last, self.prefetch = max(1, int(num_workers)), drop_last, max(1, int(prefetch))
         self.pin_memory = bool(pin_memory) and torch.cuda.is_available()
+        self._ring = None              # queue holds <= prefetch batches, the consumer one (plus one whose H2D copy may be in flight), the producer one
 
     def _indices(self) -> List[int]:
         if self.sampler is not None:
@@ -106,12 +107,22 @@ class FolderLoader:
         n = len(self.sampler) if self.sampler is not None else len(self.dataset)
         return n // self.batch_size if self.drop_last else -(-n // self.batch_size)
 
-    def _assemble(self, pool: ThreadPoolExecutor, idx: List[int]):
+    def _assemble(self, pool: ThreadPoolExecutor, idx: List[int], slot: int):
         items = list(pool.map(self.dataset.__getitem__, idx))
-        x = torch.stack([it[0] for it in items]).to(torch.float32)
-        y = torch.tensor([it[1] for it in items], dtype=torch.int64)
-        if self.pin_memory:
-            x, y = x.pin_memory(), y.pin_memory()
+        if not self.pin_memory:
+            return (torch.stack([it[0] for it in items]).to(torch.float32),
+                    torch.tensor([it[1] for it in items], dtype=torch.int64))
+        # a ring of pinned batch buffers, allocated once: pinning per batch costs a cudaHostAlloc every step
+        shape = tuple(items[0][0].shape)
+        if self._ring is None or self._ring[0][0].shape[1:] != shape:
+            self._ring = [(torch.empty((self.batch_size, *shape), dtype=torch.float32).pin_memory(),
+                           torch.empty(self.batch_size, dtype=torch.int64).pin_memory())
+                          for _ in range(self.prefetch + 3)]
+        x, y = self._ring[slot % len(self._ring)]
+        x, y = x[:len(items)], y[:len(items)]
+        for i, (img, label) in enumerate(items):
+            x[i].copy_(img)
+            y[i] = label
         return x, y
 
     def __iter__(self) -> Iterator:
@@ -125,10 +136,10 @@ class FolderLoader:
         def produce():
             try:
                 with ThreadPoolExecutor(self.num_workers, thread_name_prefix="pdb200-decode") as pool:
-                    for c in chunks:
+                    for slot, c in enumerate(chunks):
                         if stop.is_set():
                             return
-                        q.put(self._assemble(pool, c))
+                        q.put(self._assemble(pool, c, slot))
                 q.put(None)
             except BaseException as e:          # surface decode errors in the consumer
                 q.put(e)
