@@ -96,3 +96,46 @@ def harness_worker(rank, cfg):
     from pytorch_distributed_b200 import harness
     torch.set_num_threads(1)
     harness.main(cfg, rank)
+
+
+def reference_style_main(local_rank, port, out_dir):
+    """The body of the reference's DDP ``main(local_rank)`` (ref:restnet_ddp.py:75-150) written against the hfai shim
+    only — torchvision transforms, hfai datasets / DDP / distributed / client — on CPU + gloo, tiny sizes."""
+    import hf_env
+    hf_env.set_env("202111")
+    import hfai
+    import hfai.nccl.distributed as dist
+    from hfai.nn.parallel import DistributedDataParallel
+    from torch import nn
+    from torchvision import transforms as tv
+    from pytorch_distributed_b200.models import ResNet
+    torch.set_num_threads(1)
+    world_size, rank = 2, local_rank
+    dist.init_process_group(backend="gloo", init_method=f"tcp://127.0.0.1:{port}", world_size=world_size, rank=rank)
+    model = DistributedDataParallel(ResNet((1, 1, 1, 1), num_classes=10, width=8), device_ids=None)
+    tr = tv.Compose([tv.RandomResizedCrop(16), tv.RandomHorizontalFlip(), tv.ToTensor(),
+                     tv.Normalize(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225])])
+    train_dataset = hfai.datasets.ImageNet("train", transform=tr, num_samples=32, image_size=16, num_classes=10)
+    sampler = torch.utils.data.distributed.DistributedSampler(train_dataset, num_replicas=world_size, rank=rank)
+    loader = train_dataset.loader(batch_size=4, sampler=sampler, num_workers=2, pin_memory=True)
+    criterion = nn.CrossEntropyLoss()
+    optimizer = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
+    scheduler = torch.optim.lr_scheduler.StepLR(optimizer, step_size=30, gamma=0.1)
+    sampler.set_epoch(0)
+    model.train()
+    steps = 0
+    for step, (samples, labels) in enumerate(loader):
+        outputs = model(samples)
+        optimizer.zero_grad()
+        loss = criterion(outputs, labels)
+        loss.backward()
+        optimizer.step()
+        steps += 1
+        assert not hfai.client.receive_suspend_command()
+    scheduler.step()
+    acc = torch.tensor([float(loss), 1.0, 2.0, float(steps)])
+    dist.reduce(acc, 0)
+    if rank == 0 and local_rank == 0:
+        torch.save({"model": model.module.state_dict(), "optimizer": optimizer.state_dict(),
+                    "scheduler": scheduler.state_dict(), "acc": acc.tolist()}, os.path.join(out_dir, "latest.pt"))
+    dist.destroy_process_group()

@@ -108,3 +108,20 @@ def test_config_defaults_are_the_reference_literals():
         assert str(c.save_dir).endswith(want_dirs[mode])
         assert (c.image_size, c.num_classes, c.train_samples, c.val_samples) == (224, 1000, 1_281_167, 50_000)
     assert config.from_args("ddp", ["--lr", "0.2", "--batch-size", "64"]).lr == 0.2
+
+
+@pytest.mark.timeout(600)
+def test_reference_style_script_runs_on_the_shims(tmp_path, free_port):
+    """A script written the way the reference's are (hf_env, hfai.multiprocessing.spawn(..., bind_numa=True),
+    hfai.nccl.distributed, hfai.nn.parallel.DistributedDataParallel, hfai.datasets with a torchvision pipeline, stock
+    torch.optim / torch DistributedSampler) trains through this framework unchanged."""
+    import hfai
+    hfai.multiprocessing.spawn(H.reference_style_main, args=(free_port, str(tmp_path)), nprocs=2, bind_numa=True)
+    ck = torch.load(tmp_path / "latest.pt")
+    assert len(ck["model"]) == len(ResNetKeys()) and ck["acc"][3] == 8.0          # 4 steps per rank, summed over 2 ranks
+    assert ck["optimizer"]["param_groups"][0]["lr"] == 0.01 and ck["scheduler"]["last_epoch"] == 1
+
+
+def ResNetKeys():
+    from pytorch_distributed_b200.models import ResNet
+    return ResNet((1, 1, 1, 1), num_classes=10, width=8).state_dict().keys()
