@@ -61,9 +61,12 @@ template <> struct Elem<__half> {
   static __device__ __forceinline__ __half from_f(float v) { return __float2half_rn(v); }
 };
 
-// 8 x 16-bit = one 128-bit access
-struct alignas(16) Vec8 {
-  uint4 raw;
+template <> struct Elem<float> {      // fp32 storage (TF32 tensor-core math): the "conversions" are identities
+  using T2 = float2;
+  static __device__ __forceinline__ float2 to_f2(T2 v) { return v; }
+  static __device__ __forceinline__ T2 from_f2(float a, float b) { return make_float2(a, b); }
+  static __device__ __forceinline__ float to_f(float v) { return v; }
+  static __device__ __forceinline__ float from_f(float v) { return v; }
 };
 
 template <typename T>
@@ -99,6 +102,60 @@ __device__ __forceinline__ uint4 ldg128_stream(const void* p) {
 }
 __device__ __forceinline__ void stg128(void* p, const uint4& v) { *reinterpret_cast<uint4*>(p) = v; }
 
+// ---- 8 consecutive elements of any activation type: one 128-bit access (16-bit) or two (fp32) ----------------
+template <typename T>
+struct V8 {
+  uint4 q[sizeof(T) / 2];
+};
+template <typename T>
+__device__ __forceinline__ V8<T> ld8(const T* p) {
+  V8<T> v;
+#pragma unroll
+  for (int j = 0; j < (int)sizeof(T) / 2; ++j) v.q[j] = __ldg(reinterpret_cast<const uint4*>(p) + j);
+  return v;
+}
+template <typename T>
+__device__ __forceinline__ V8<T> ld8s(const T* p) {           // streaming (read-once) variant
+  V8<T> v;
+#pragma unroll
+  for (int j = 0; j < (int)sizeof(T) / 2; ++j) v.q[j] = ldg128_stream(reinterpret_cast<const uint4*>(p) + j);
+  return v;
+}
+template <typename T>
+__device__ __forceinline__ void st8(T* p, const V8<T>& v) {
+#pragma unroll
+  for (int j = 0; j < (int)sizeof(T) / 2; ++j) reinterpret_cast<uint4*>(p)[j] = v.q[j];
+}
+template <typename T>
+__device__ __forceinline__ V8<T> zero8() {
+  V8<T> v;
+#pragma unroll
+  for (int j = 0; j < (int)sizeof(T) / 2; ++j) v.q[j] = make_uint4(0, 0, 0, 0);
+  return v;
+}
+template <typename T>
+__device__ __forceinline__ void unpack8(const V8<T>& v, float (&f)[8]) {
+  if constexpr (sizeof(T) == 4) {
+    const float* s = reinterpret_cast<const float*>(&v);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) f[i] = s[i];
+  } else {
+    unpack8<T>(v.q[0], f);
+  }
+}
+template <typename T>
+__device__ __forceinline__ V8<T> pack8v(const float (&f)[8]) {
+  V8<T> v;
+  if constexpr (sizeof(T) == 4) {
+    float* s = reinterpret_cast<float*>(&v);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = f[i];
+  } else {
+    v.q[0] = pack8<T>(f);
+  }
+  return v;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -118,6 +175,24 @@ __device__ __forceinline__ float warp_max(float v) {
       __VA_ARGS__;                                             \
     } else if ((dtype) == PDB_FP16) {                          \
       using T = __half;                                        \
+      __VA_ARGS__;                                             \
+    } else {                                                   \
+      ::pdb::set_error("unsupported dtype tag %d", (int)(dtype)); \
+      return 1;                                                \
+    }                                                          \
+  } while (0)
+
+// dispatch on any activation dtype tag: the two 16-bit formats or fp32 storage (TF32 math in the GEMMs)
+#define PDB_DISPATCH_ACT(dtype, T, ...)                        \
+  do {                                                         \
+    if ((dtype) == PDB_BF16) {                                 \
+      using T = __nv_bfloat16;                                 \
+      __VA_ARGS__;                                             \
+    } else if ((dtype) == PDB_FP16) {                          \
+      using T = __half;                                        \
+      __VA_ARGS__;                                             \
+    } else if ((dtype) == PDB_FP32) {                          \
+      using T = float;                                         \
       __VA_ARGS__;                                             \
     } else {                                                   \
       ::pdb::set_error("unsupported dtype tag %d", (int)(dtype)); \

@@ -33,22 +33,22 @@ __device__ __forceinline__ void reduce_rows(const T* __restrict__ a, const T* __
   // what lets three blocks share an SM (this kernel needs bytes in flight, not arithmetic)
   (void)mean;
   (void)rstd;
-  constexpr int U = 4;                     // rows in flight per thread
+  constexpr int U = sizeof(T) == 4 ? 2 : 4;   // rows in flight per thread (same bytes in flight for fp32)
   // a block walks slabs of U*ry ADJACENT rows (U*ry*C*2 bytes contiguous per stream, >= 16 KB): DRAM likes
   // long contiguous bursts far better than U scattered 4 KB pieces
   const int64_t rstride = ry;
   for (int64_t r0 = (int64_t)blockIdx.x * ry * U + ty; r0 < rows; r0 += (int64_t)gridDim.x * ry * U) {
-    uint4 va[U], vx[U], vz[U];
+    V8<T> va[U], vx[U], vz[U];
     uint32_t vb[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t r = r0 + u * rstride;
       if (r < rows) {
         const int64_t off = r * C + (int64_t)cg * 8;
-        va[u] = ldg128_stream(a + off);
+        va[u] = ld8s<T>(a + off);
         if (MODE == 1) {
-          vx[u] = ldg128_stream(x + off);
-          if (kMask == 1) vz[u] = ldg128_stream(z + off);
+          vx[u] = ld8s<T>(x + off);
+          if (kMask == 1) vz[u] = ld8s<T>(z + off);
           if (kMask == 2) vb[u] = __ldg(bits + (off >> 3));
         }
       }
@@ -126,11 +126,12 @@ __global__ void __launch_bounds__(kThreads) bn_stats_kernel(const T* __restrict_
   const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
   float* partial = reinterpret_cast<float*>(scratch + 1) + (size_t)blockIdx.x * 2 * C;
   const int ncg = C / 8;
-  for (int cg = tx; cg < ncg; cg += cx) {
+  for (int cg0 = 0; cg0 < ncg; cg0 += cx) {        // uniform trip count: block_fold contains barriers
+    const int cg = cg0 + tx;
     float s0[8] = {0}, s1[8] = {0};
-    if (ty < ry) reduce_rows<T, 0, 0>(x, nullptr, nullptr, nullptr, rows, C, cg, cx, ry, ty, nullptr, nullptr, s0, s1);
+    if (ty < ry && cg < ncg) reduce_rows<T, 0, 0>(x, nullptr, nullptr, nullptr, rows, C, cg, cx, ry, ty, nullptr, nullptr, s0, s1);
     block_fold(s0, s1, tx, ty, cx, ry, smem);
-    if (ty == 0) {
+    if (ty == 0 && cg < ncg) {
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         partial[cg * 8 + k] = s0[k];
@@ -176,11 +177,12 @@ __global__ void __launch_bounds__(kThreads) bn_stats_sync_kernel(const T* __rest
   const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
   float* partial = reinterpret_cast<float*>(scratch + 1) + (size_t)blockIdx.x * 2 * C;
   const int ncg = C / 8;
-  for (int cg = tx; cg < ncg; cg += cx) {
+  for (int cg0 = 0; cg0 < ncg; cg0 += cx) {        // uniform trip count: block_fold contains barriers
+    const int cg = cg0 + tx;
     float s0[8] = {0}, s1[8] = {0};
-    if (ty < ry) reduce_rows<T, 0, 0>(x, nullptr, nullptr, nullptr, rows, C, cg, cx, ry, ty, nullptr, nullptr, s0, s1);
+    if (ty < ry && cg < ncg) reduce_rows<T, 0, 0>(x, nullptr, nullptr, nullptr, rows, C, cg, cx, ry, ty, nullptr, nullptr, s0, s1);
     block_fold(s0, s1, tx, ty, cx, ry, smem);
-    if (ty == 0) {
+    if (ty == 0 && cg < ncg) {
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         partial[cg * 8 + k] = s0[k];
@@ -253,11 +255,12 @@ __global__ void __launch_bounds__(kThreads, 3) bn_bwd_reduce_kernel(const T* __r
   const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
   const int ncg = C / 8;
   float* target = rep ? rep + (size_t)(blockIdx.x % kReduceReplicas) * 2 * C : dsums;
-  for (int cg = tx; cg < ncg; cg += cx) {
+  for (int cg0 = 0; cg0 < ncg; cg0 += cx) {        // uniform trip count: block_fold contains barriers
+    const int cg = cg0 + tx;
     float s0[8] = {0}, s1[8] = {0};
-    if (ty < ry) reduce_rows<T, 1, kMask>(dz, z, bits, x, rows, C, cg, cx, ry, ty, mean, rstd, s0, s1);
+    if (ty < ry && cg < ncg) reduce_rows<T, 1, kMask>(dz, z, bits, x, rows, C, cg, cx, ry, ty, mean, rstd, s0, s1);
     block_fold(s0, s1, tx, ty, cx, ry, smem);
-    if (ty == 0) {
+    if (ty == 0 && cg < ncg) {
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const int c = cg * 8 + k;
@@ -321,13 +324,13 @@ __global__ void __launch_bounds__(kThreads) bn_apply_kernel(const T* __restrict_
   constexpr int U = 4;                     // independent 128-bit requests in flight per thread and stream
   const int64_t tile = (int64_t)blockDim.x * U;
   for (int64_t base = (int64_t)blockIdx.x * tile; base < nvec; base += (int64_t)gridDim.x * tile) {
-    uint4 vx[U], vr[U];
+    V8<T> vx[U], vr[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
       if (i < nvec) {
-        vx[u] = ldg128_stream(x + i * 8);
-        if (kRes) vr[u] = ldg128_stream(res + i * 8);
+        vx[u] = ld8s<T>(x + i * 8);
+        if (kRes) vr[u] = ld8s<T>(res + i * 8);
       }
     }
 #pragma unroll
@@ -351,7 +354,7 @@ __global__ void __launch_bounds__(kThreads) bn_apply_kernel(const T* __restrict_
 #pragma unroll
         for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
       }
-      stg128(y + i * 8, pack8<T>(f));
+      st8<T>(y + i * 8, pack8v<T>(f));
     }
   }
 }
@@ -377,12 +380,12 @@ __global__ void __launch_bounds__(kThreads) bn_apply_eval_kernel(const T* __rest
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
     const int c0 = (int)(i % cvec) * 8;
     float f[8];
-    unpack8<T>(ldg128_stream(x + i * 8), f);
+    unpack8<T>(ld8s<T>(x + i * 8), f);
 #pragma unroll
     for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], scale[c0 + k], shift[c0 + k]);
     if (kRes) {
       float r[8];
-      unpack8<T>(ldg128_stream(res + i * 8), r);
+      unpack8<T>(ld8s<T>(res + i * 8), r);
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] += r[k];
     }
@@ -390,7 +393,7 @@ __global__ void __launch_bounds__(kThreads) bn_apply_eval_kernel(const T* __rest
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
     }
-    stg128(y + i * 8, pack8<T>(f));
+    st8<T>(y + i * 8, pack8v<T>(f));
   }
 }
 
@@ -430,14 +433,14 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const T* __restr
   constexpr int U = 2;
   const int64_t tile = (int64_t)blockDim.x * U;
   for (int64_t base = (int64_t)blockIdx.x * tile; base < nvec; base += (int64_t)gridDim.x * tile) {
-    uint4 vg[U], vx[U], vz[U];
+    V8<T> vg[U], vx[U], vz[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
       if (i < nvec) {
-        vg[u] = ldg128_stream(dz + i * 8);
-        vx[u] = ldg128_stream(x + i * 8);
-        if (kHasZ) vz[u] = ldg128_stream(z + i * 8);
+        vg[u] = ld8s<T>(dz + i * 8);
+        vx[u] = ld8s<T>(x + i * 8);
+        if (kHasZ) vz[u] = ld8s<T>(z + i * 8);
       }
     }
 #pragma unroll
@@ -454,11 +457,11 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const T* __restr
 #pragma unroll
         for (int k = 0; k < 8; ++k) g[k] = fz[k] > 0.f ? g[k] : 0.f;
       }
-      if (kDres) stg128(dres + i * 8, pack8<T>(g));
+      if (kDres) st8<T>(dres + i * 8, pack8v<T>(g));
       float o[8];
 #pragma unroll
       for (int k = 0; k < 8; ++k) o[k] = fmaf(A[c0 + k], g[k], fmaf(B[c0 + k], fx[k], Cc[c0 + k]));
-      stg128(dx + i * 8, pack8<T>(o));
+      st8<T>(dx + i * 8, pack8v<T>(o));
     }
   }
 }
@@ -511,7 +514,7 @@ extern "C" int pdb_bn_stats(const void* x, int dtype, int64_t rows, int C, float
   PDB_CHECK_ARG(scratch_bytes >= need, "pdb_bn_stats: scratch too small (%zu < %zu bytes)", scratch_bytes, need);
   PDB_CHECK_ARG(((uintptr_t)scratch) % 256 == 0, "pdb_bn_stats: scratch must be 256-byte aligned");
   const size_t smem = (size_t)kThreads * 16 * sizeof(float);
-  PDB_DISPATCH_16(dtype, T, (bn_stats_kernel<T><<<grid, kThreads, smem, (cudaStream_t)stream>>>(
+  PDB_DISPATCH_ACT(dtype, T, (bn_stats_kernel<T><<<grid, kThreads, smem, (cudaStream_t)stream>>>(
                                 (const T*)x, rows, C, cx, ry, sums, (StatsScratch*)scratch)));
   PDB_LAUNCH_CHECK();
   return 0;
@@ -535,7 +538,7 @@ extern "C" int pdb_bn_stats_sync(const void* x, int dtype, int64_t rows, int C, 
     sp.pad[i] = i < world ? static_cast<uint32_t*>(pads[i]) : nullptr;
   }
   const size_t smem = (size_t)kThreads * 16 * sizeof(float);
-  PDB_DISPATCH_16(dtype, T, (bn_stats_sync_kernel<T><<<grid, kThreads, smem, (cudaStream_t)stream>>>(
+  PDB_DISPATCH_ACT(dtype, T, (bn_stats_sync_kernel<T><<<grid, kThreads, smem, (cudaStream_t)stream>>>(
                                 (const T*)x, rows, C, cx, ry, sums, (StatsScratch*)scratch, sp, rank, world, slot_stride)));
   PDB_LAUNCH_CHECK();
   return 0;
@@ -558,7 +561,7 @@ extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* r
   if (cap == 0) cap = resident_blocks(bn_bwd_reduce_kernel<__nv_bfloat16, 2>, smem);
   const int grid = reduce_grid(rows, ry, cap);
   cudaStream_t st = (cudaStream_t)stream;
-  PDB_DISPATCH_16(dtype, T, {
+  PDB_DISPATCH_ACT(dtype, T, {
     if (relu_mask)
       bn_bwd_reduce_kernel<T, 2><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, relu_mask, (const T*)x, rows, C,
                                                                cx, ry, mean, rstd, dsums, rep, ticket);
@@ -585,13 +588,13 @@ extern "C" int pdb_bn_apply(const void* x, const void* residual, void* y, int dt
   const int64_t nvec = rows * C / 8;
   cudaStream_t st = (cudaStream_t)stream;
   if (bn_fast_ok(C)) {
-    const int fgrid = bn_fast_grid(nvec, kFastU);
+    const int fgrid = bn_fast_grid(nvec, kFastU, dtype);
     const float inv_count = (float)(1.0 / count), unbias = (float)(count > 1.0 ? count / (count - 1.0) : 1.0);
 #define FAST(RES, RELU)                                                                                            \
   bn_apply_fast_kernel<T, RES, RELU><<<fgrid, kFastThreads, 0, st>>>(                                              \
       (const T*)x, (const T*)residual, (T*)y, nvec, C, sums, inv_count, unbias, gamma, beta, eps, momentum,        \
       running_mean, running_var, num_batches_tracked, save_mean, save_rstd, relu_mask)
-    PDB_DISPATCH_16(dtype, T, {
+    PDB_DISPATCH_ACT(dtype, T, {
       if (residual && relu) FAST(true, true);
       else if (residual) FAST(true, false);
       else if (relu) FAST(false, true);
@@ -607,7 +610,7 @@ extern "C" int pdb_bn_apply(const void* x, const void* residual, void* y, int dt
   bn_apply_kernel<T, RES, RELU><<<grid, kThreads, smem, st>>>((const T*)x, (const T*)residual, (T*)y, nvec, C, sums, \
                                                               count, gamma, beta, eps, momentum, running_mean,    \
                                                               running_var, num_batches_tracked, save_mean, save_rstd)
-  PDB_DISPATCH_16(dtype, T, {
+  PDB_DISPATCH_ACT(dtype, T, {
     if (residual && relu) LAUNCH(true, true);
     else if (residual) LAUNCH(true, false);
     else if (relu) LAUNCH(false, true);
@@ -626,11 +629,11 @@ extern "C" int pdb_bn_apply_eval(const void* x, const void* residual, void* y, i
   const int64_t nvec = rows * C / 8;
   cudaStream_t st = (cudaStream_t)stream;
   if (bn_fast_ok(C)) {
-    const int fgrid = bn_fast_grid(nvec, kFastU);
+    const int fgrid = bn_fast_grid(nvec, kFastU, dtype);
 #define FAST(RES, RELU)                                                                                     \
   bn_apply_eval_fast_kernel<T, RES, RELU><<<fgrid, kFastThreads, 0, st>>>(                                  \
       (const T*)x, (const T*)residual, (T*)y, nvec, C, running_mean, running_var, gamma, beta, eps)
-    PDB_DISPATCH_16(dtype, T, {
+    PDB_DISPATCH_ACT(dtype, T, {
       if (residual && relu) FAST(true, true);
       else if (residual) FAST(true, false);
       else if (relu) FAST(false, true);
@@ -645,7 +648,7 @@ extern "C" int pdb_bn_apply_eval(const void* x, const void* residual, void* y, i
 #define LAUNCH(RES, RELU)                                                                                    \
   bn_apply_eval_kernel<T, RES, RELU><<<grid, kThreads, smem, st>>>((const T*)x, (const T*)residual, (T*)y, nvec, C, \
                                                                    running_mean, running_var, gamma, beta, eps)
-  PDB_DISPATCH_16(dtype, T, {
+  PDB_DISPATCH_ACT(dtype, T, {
     if (residual && relu) LAUNCH(true, true);
     else if (residual) LAUNCH(true, false);
     else if (relu) LAUNCH(false, true);
@@ -666,13 +669,13 @@ extern "C" int pdb_bn_bwd_apply(const void* dz, const void* z, const uint8_t* re
   const int64_t nvec = rows * C / 8;
   cudaStream_t st = (cudaStream_t)stream;
   if (bn_fast_ok(C)) {
-    const int fgrid = bn_fast_grid(nvec, kFastUBwd);
+    const int fgrid = bn_fast_grid(nvec, kFastUBwd, dtype);
     const float inv_count = (float)(1.0 / count);
 #define FAST(MK, DR)                                                                                              \
   bn_bwd_apply_fast_kernel<T, MK, DR><<<fgrid, kFastThreads, 0, st>>>(                                            \
       (const T*)dz, (const T*)z, relu_mask, (const T*)x, (T*)dx, (T*)dres, nvec, C, mean, rstd, gamma, dsums,     \
       inv_count, dgamma, dbeta)
-    PDB_DISPATCH_16(dtype, T, {
+    PDB_DISPATCH_ACT(dtype, T, {
       if (relu_mask && dres) FAST(2, true);
       else if (relu_mask) FAST(2, false);
       else if (z && dres) FAST(1, true);
@@ -690,7 +693,7 @@ extern "C" int pdb_bn_bwd_apply(const void* dz, const void* z, const uint8_t* re
   bn_bwd_apply_kernel<T, HZ, DR><<<grid, kThreads, smem, st>>>((const T*)dz, (const T*)z, (const T*)x, (T*)dx,     \
                                                                (T*)dres, nvec, C, mean, rstd, gamma, dsums, count, \
                                                                dgamma, dbeta)
-  PDB_DISPATCH_16(dtype, T, {
+  PDB_DISPATCH_ACT(dtype, T, {
     if (z && dres) LAUNCH(true, true);
     else if (z) LAUNCH(true, false);
     else if (dres) LAUNCH(false, true);
@@ -763,7 +766,7 @@ extern "C" int pdb_bn_stats_noalloc(const void* x, int dtype, int64_t rows, int 
   // aborted (or a racing one) could have left it non-zero.
   PDB_CUDA(cudaMemsetAsync(scratch, 0, sizeof(StatsScratch), st));
   const size_t smem = (size_t)kThreads * 16 * sizeof(float);
-  PDB_DISPATCH_16(dtype, T, (bn_stats_kernel<T><<<grid, kThreads, smem, st>>>((const T*)x, rows, C, cx, ry, sums, scratch)));
+  PDB_DISPATCH_ACT(dtype, T, (bn_stats_kernel<T><<<grid, kThreads, smem, st>>>((const T*)x, rows, C, cx, ry, sums, scratch)));
   PDB_LAUNCH_CHECK();
   return 0;
 }

@@ -13,6 +13,10 @@ namespace pdb {
 
 constexpr int kFastThreads = 256;
 constexpr int kFastU = 8;                 // 128-bit vectors per thread and tile
+// fp32 activations are two 128-bit vectors per 8 channels: half as many 8-channel groups per thread keeps the bytes
+// (and registers) in flight the same
+template <typename T>
+constexpr int fast_u(int u16) { return sizeof(T) == 4 ? u16 / 2 : u16; }
 
 __device__ __forceinline__ void load8f(const float* __restrict__ p, float (&v)[8]) {
   const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
@@ -59,18 +63,19 @@ __global__ void __launch_bounds__(kFastThreads) bn_apply_fast_kernel(
     }
     if (threadIdx.x == 0 && num_batches_tracked) *num_batches_tracked += 1;
   }
-  const int64_t base = (int64_t)blockIdx.x * (kFastThreads * kFastU) + threadIdx.x;
-  uint4 vx[kFastU], vr[kFastU];
+  constexpr int U = fast_u<T>(kFastU);
+  const int64_t base = (int64_t)blockIdx.x * (kFastThreads * U) + threadIdx.x;
+  V8<T> vx[U], vr[U];
 #pragma unroll
-  for (int u = 0; u < kFastU; ++u) {
+  for (int u = 0; u < U; ++u) {
     const int64_t i = base + (int64_t)u * kFastThreads;
     if (i < nvec) {
-      vx[u] = ldg128_stream(x + i * 8);
-      if (kRes) vr[u] = ldg128_stream(res + i * 8);
+      vx[u] = ld8s<T>(x + i * 8);
+      if (kRes) vr[u] = ld8s<T>(res + i * 8);
     }
   }
 #pragma unroll
-  for (int u = 0; u < kFastU; ++u) {
+  for (int u = 0; u < U; ++u) {
     const int64_t i = base + (int64_t)u * kFastThreads;
     if (i >= nvec) continue;
     float f[8];
@@ -93,7 +98,7 @@ __global__ void __launch_bounds__(kFastThreads) bn_apply_fast_kernel(
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
     }
-    stg128(y + i * 8, pack8<T>(f));
+    st8<T>(y + i * 8, pack8v<T>(f));
   }
 }
 
@@ -114,18 +119,19 @@ __global__ void __launch_bounds__(kFastThreads) bn_apply_eval_fast_kernel(
       sh[k] = fmaf(-m[k], sc[k], b[k]);
     }
   }
-  const int64_t base = (int64_t)blockIdx.x * (kFastThreads * kFastU) + threadIdx.x;
-  uint4 vx[kFastU], vr[kFastU];
+  constexpr int U = fast_u<T>(kFastU);
+  const int64_t base = (int64_t)blockIdx.x * (kFastThreads * U) + threadIdx.x;
+  V8<T> vx[U], vr[U];
 #pragma unroll
-  for (int u = 0; u < kFastU; ++u) {
+  for (int u = 0; u < U; ++u) {
     const int64_t i = base + (int64_t)u * kFastThreads;
     if (i < nvec) {
-      vx[u] = ldg128_stream(x + i * 8);
-      if (kRes) vr[u] = ldg128_stream(res + i * 8);
+      vx[u] = ld8s<T>(x + i * 8);
+      if (kRes) vr[u] = ld8s<T>(res + i * 8);
     }
   }
 #pragma unroll
-  for (int u = 0; u < kFastU; ++u) {
+  for (int u = 0; u < U; ++u) {
     const int64_t i = base + (int64_t)u * kFastThreads;
     if (i >= nvec) continue;
     float f[8];
@@ -142,7 +148,7 @@ __global__ void __launch_bounds__(kFastThreads) bn_apply_eval_fast_kernel(
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
     }
-    stg128(y + i * 8, pack8<T>(f));
+    st8<T>(y + i * 8, pack8v<T>(f));
   }
 }
 
@@ -174,21 +180,22 @@ __global__ void __launch_bounds__(kFastThreads) bn_bwd_apply_fast_kernel(
       if (dbeta) dbeta[c] += dsums[c];
     }
   }
-  const int64_t base = (int64_t)blockIdx.x * (kFastThreads * kFastUBwd) + threadIdx.x;
-  uint4 vg[kFastUBwd], vx[kFastUBwd], vz[kFastUBwd];
-  uint32_t vb[kFastUBwd];
+  constexpr int U = fast_u<T>(kFastUBwd);
+  const int64_t base = (int64_t)blockIdx.x * (kFastThreads * U) + threadIdx.x;
+  V8<T> vg[U], vx[U], vz[U];
+  uint32_t vb[U];
 #pragma unroll
-  for (int u = 0; u < kFastUBwd; ++u) {
+  for (int u = 0; u < U; ++u) {
     const int64_t i = base + (int64_t)u * kFastThreads;
     if (i < nvec) {
-      vg[u] = ldg128_stream(dz + i * 8);
-      vx[u] = ldg128_stream(x + i * 8);
-      if (kMask == 1) vz[u] = ldg128_stream(z + i * 8);
+      vg[u] = ld8s<T>(dz + i * 8);
+      vx[u] = ld8s<T>(x + i * 8);
+      if (kMask == 1) vz[u] = ld8s<T>(z + i * 8);
       if (kMask == 2) vb[u] = __ldg(bits + i);
     }
   }
 #pragma unroll
-  for (int u = 0; u < kFastUBwd; ++u) {
+  for (int u = 0; u < U; ++u) {
     const int64_t i = base + (int64_t)u * kFastThreads;
     if (i >= nvec) continue;
     float g[8], fx[8];
@@ -204,15 +211,17 @@ __global__ void __launch_bounds__(kFastThreads) bn_bwd_apply_fast_kernel(
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] = (vb[u] >> k) & 1u ? g[k] : 0.f;
     }
-    if (kDres) stg128(dres + i * 8, pack8<T>(g));
+    if (kDres) st8<T>(dres + i * 8, pack8v<T>(g));
     float o[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) o[k] = fmaf(A[k], g[k], fmaf(B[k], fx[k], Cc[k]));
-    stg128(dx + i * 8, pack8<T>(o));
+    st8<T>(dx + i * 8, pack8v<T>(o));
   }
 }
 
 inline bool bn_fast_ok(int C) { return C >= 8 && (C % 8) == 0 && (kFastThreads % (C / 8)) == 0; }
-inline int bn_fast_grid(int64_t nvec, int u) { return (int)((nvec + (int64_t)kFastThreads * u - 1) / ((int64_t)kFastThreads * u)); }
+inline int bn_fast_grid(int64_t nvec, int u16, int dtype) {
+  const int u = dtype == PDB_FP32 ? u16 / 2 : u16;
+  return (int)((nvec + (int64_t)kFastThreads * u - 1) / ((int64_t)kFastThreads * u)); }
 
 }  // namespace pdb

@@ -27,13 +27,21 @@ namespace pdb {
 using namespace tc05;
 
 constexpr int BLOCK_M = 128;
-constexpr int BLOCK_K = 64;                 // 64 x 16-bit = 128 B = one swizzle row
-constexpr int UMMA_K = 16;
+// Operand formats: kFmt is the dtype tag of the C ABI (0 = bf16, 1 = fp16 -> kind::f16; 2 = fp32 storage ->
+// kind::tf32).  Everything in the pipelines is sized in BYTES — a k-block is one 128-byte swizzle row per tile row, an
+// MMA consumes 32 bytes of K — so the 32-bit format changes element counts only: 32 instead of 64 elements per
+// k-block, K = 8 instead of 16 per MMA, and twice as many k-blocks for the same reduction length.
+constexpr int kFmtTf32 = 2;
+template <int kFmt>
+struct Fmt {
+  static constexpr int ES = kFmt == kFmtTf32 ? 4 : 2;        // bytes per element (operands and outputs)
+  static constexpr int BLOCK_K = 128 / ES;                   // elements per 128-byte swizzle row: 64 / 32
+  static constexpr int UMMA_K = 32 / ES;                     // 16 / 8
+};
 constexpr int kNumThreads = 320;            // 10 warps: producer, mma, 8 x epilogue
 constexpr int kEpiThreads = 256;            // two warps per TMEM lane quarter, splitting the columns:
                                             // with K <= 512 the epilogue, not the MMA, sets the tile rate
-constexpr uint32_t A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KB
-constexpr uint32_t CHUNK_BYTES = 64 * 128;                  // 64 rows x 128 B = 8 KB (wgrad boxes)
+constexpr uint32_t A_STAGE_BYTES = BLOCK_M * 128;           // 128 rows x one 128-byte swizzle row = 16 KB
 
 // Division by a runtime constant without the ~100-cycle integer divide: the TMA producer is ONE thread and
 // its address arithmetic sits on the critical path of every pipeline stage.  Valid for 0 <= n < 2^31.
@@ -96,20 +104,25 @@ struct FpropParams {
 };
 
 // kPair: the CTA is one half of a cta_group::2 pair working on a 256-row tile; it stages only HALF of the B tile.
-template <int BLOCK_N, bool kPair = false>
+// ES: bytes per output element.  The epilogue stages the tile in boxes of 128 rows x 128 B (64 16-bit or 32 fp32
+// columns); a pass is at most 32 KB of them (128 16-bit or 64 fp32 columns), so that a wide tile does not spend
+// pipeline stages on staging.
+template <int BLOCK_N, bool kPair = false, int ES = 2>
 struct FpropSmem {
-  static constexpr uint32_t B_STAGE_BYTES = (kPair ? BLOCK_N / 2 : BLOCK_N) * BLOCK_K * 2;
+  static constexpr uint32_t B_STAGE_BYTES = (kPair ? BLOCK_N / 2 : BLOCK_N) * 128;
   static constexpr uint32_t STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int PASS_N = BLOCK_N < 128 ? BLOCK_N : 128;        // columns staged per epilogue pass
+  static constexpr int BOX_N = 128 / ES;                               // columns per staging box: 64 / 32
+  static constexpr int PASS_MAX = 2 * BOX_N;                           // two boxes per pass
+  static constexpr int PASS_N = BLOCK_N < PASS_MAX ? BLOCK_N : PASS_MAX;   // columns staged per epilogue pass
   static constexpr int kStages = kPair ? (BLOCK_N == 256 ? 6 : 8) : (BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8));
-  static constexpr uint32_t OUT_BYTES = (PASS_N / 64) * 16384;        // 128 rows x 128 B per 64-col chunk
+  static constexpr uint32_t OUT_BYTES = (PASS_N / BOX_N) * 16384;      // 128 rows x 128 B per box
   static constexpr uint32_t BAR_OFFSET = kStages * STAGE_BYTES + OUT_BYTES;
   static constexpr uint32_t TOTAL = BAR_OFFSET + 256 + 1024;           // barriers + alignment slack
 };
 
-template <bool kBf16>
+template <int kFmt>
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
-  if (kBf16) {
+  if (kFmt == 0) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&v);
   } else {
@@ -117,20 +130,24 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&v);
   }
 }
-template <bool kBf16>
+template <int kFmt>
 __device__ __forceinline__ float2 unpack2(uint32_t w) {
-  if (kBf16) return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w));
+  if (kFmt == 0) return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&w));
   return __half22float2(*reinterpret_cast<__half2*>(&w));
 }
 
 // kStem: the 7x7/2 stem as a 4x4/1 convolution over the space-to-depth input (16 channels per pixel, see
 // pdb_stem_fprop): a pipeline stage holds one row of four filter taps, each tap a [128 pixels x 32 B] block (A) and a
 // [64 couts x 32 B] block (B) in 32-byte-swizzled K-major layout; one MMA (K = 16) consumes one tap.
-template <int BLOCK_N, bool kBf16, bool kPair, bool kStem = false>
+template <int BLOCK_N, int kFmt, bool kPair, bool kStem = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmD, const FpropParams p) {
-  using L = FpropSmem<BLOCK_N, kPair>;
+  using F = Fmt<kFmt>;
+  constexpr bool kTf32 = kFmt == kFmtTf32;
+  constexpr int BLOCK_K = F::BLOCK_K, UMMA_K = F::UMMA_K;
+  static_assert(!(kStem && kTf32), "the space-to-depth stem kernels are 16-bit only");
+  using L = FpropSmem<BLOCK_N, kPair, F::ES>;
   // pair mode: rank 0 is the leader (issues the MMAs, owns the full / tmem-empty barriers that are waited on)
   const uint32_t rank = kPair ? cluster_ctarank() : 0u;
   const int unit = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;        // tile-walking unit: CTA or CTA pair
@@ -241,10 +258,11 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else if (warp == 1 && rank == 0) {
     // ================================ MMA issuer (pair mode: leader CTA only) ======
-    constexpr uint32_t idesc = umma_idesc_f16(kBf16 ? 1 : 0, kPair ? 2 * BLOCK_M : BLOCK_M, BLOCK_N, 0, 0);
-    // K-major SW128: SBO = 8 rows x 128 B.  Stem: K-major SW32, 8 rows x 32 B.
+    constexpr int kM = kPair ? 2 * BLOCK_M : BLOCK_M;
+    constexpr uint32_t idesc = kTf32 ? umma_idesc_tf32(kM, BLOCK_N, 0, 0) : umma_idesc_f16(kFmt == 0 ? 1 : 0, kM, BLOCK_N, 0, 0);
+    // K-major SW128: SBO = 8 rows x 128 B; one MMA advances 32 bytes along K.  Stem: K-major SW32, 8 rows x 32 B.
     constexpr uint64_t desc_base = kStem ? umma_desc_base(0, 256, kLayoutSw32) : umma_desc_base(0, 1024);
-    constexpr uint32_t kStepA = kStem ? BLOCK_M * 32 : UMMA_K * 2, kStepB = kStem ? BLOCK_N * 32 : UMMA_K * 2;
+    constexpr uint32_t kStepA = kStem ? BLOCK_M * 32 : 32, kStepB = kStem ? BLOCK_N * 32 : 32;
     int stage = 0, acc = 0;
     uint32_t phase = 0, acc_phase = 0;
     TileWalk walk(unit, num_units, num_tiles, p.tile_period);
@@ -261,8 +279,13 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
             const uint64_t da = umma_desc(desc_base, a_addr + k * kStepA), db = umma_desc(desc_base, b_addr + k * kStepB);
-            if (kPair) umma_f16_2sm(d_tmem, da, db, idesc, (kb | k) != 0);
-            else umma_f16(d_tmem, da, db, idesc, (kb | k) != 0);
+            if (kTf32) {
+              if (kPair) umma_tf32_2sm(d_tmem, da, db, idesc, (kb | k) != 0);
+              else umma_tf32(d_tmem, da, db, idesc, (kb | k) != 0);
+            } else {
+              if (kPair) umma_f16_2sm(d_tmem, da, db, idesc, (kb | k) != 0);
+              else umma_f16(d_tmem, da, db, idesc, (kb | k) != 0);
+            }
           }
           if (kPair) {
             umma_commit_2sm(empty + stage, 3);                      // frees the slot in BOTH CTAs
@@ -288,7 +311,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     // instead of owning 64 KB, and the 32 KB saved buy one more pipeline stage — these kernels are bound by
     // TMA latency x bytes in flight (ncu: tensor pipe 30 % active, L2 and DRAM far from their limits).
     constexpr int PASS_N = L::PASS_N;
-    constexpr int PASSES = BLOCK_N / PASS_N;          // 1, 1, 2
+    constexpr int PASSES = BLOCK_N / PASS_N;          // 16-bit: 1, 1, 2; fp32: 1, 2, 4
+    constexpr int BOX_N = L::BOX_N;                   // columns per 128-byte staging box row (64 / 32)
     constexpr int PAIRS = PASS_N / 2;                 // column pairs per pass for the statistics
     constexpr int G = kEpiThreads / PAIRS;            // row groups (8 or 4)
     constexpr int GPP = PASS_N / 64;                  // 32-column groups per warp and pass (1 or 2)
@@ -299,11 +323,11 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     constexpr int SWZ = 8 / G;
     uint32_t st_off[SWZ];
     {
-      const int col = pair * 2, chunk = (col & 63) >> 3;
+      const int col = pair * 2, byte = (col % BOX_N) * F::ES, chunk = byte >> 4;
 #pragma unroll
       for (int i = 0; i < SWZ; ++i) {
         const int r = rg + i * G;
-        st_off[i] = out_stage_s + (col >> 6) * 16384 + ((col & 7) << 1) + r * 128 + ((chunk ^ (r & 7)) << 4);
+        st_off[i] = out_stage_s + (col / BOX_N) * 16384 + (byte & 15) + r * 128 + ((chunk ^ (r & 7)) << 4);
       }
     }
     float2 st_sum[PASSES], st_sq[PASSES];            // packed: add.f32x2 / fma.rn.f32x2 halve the FP32 issue slots
@@ -367,23 +391,33 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               v[b][c] = __float_as_uint(__uint_as_float(v[b][c]) + (n < p.N ? __ldg(p.bias + n) : 0.f));
             }
           }
-          const uint32_t dst = out_stage_s + (lg >> 1) * 16384 + row * 128;
+          if (kTf32) {
+            // fp32 output: this warp's 32 columns are one full 128-byte row of box lg
+            const uint32_t dst = out_stage_s + lg * 16384 + row * 128;
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {               // four 16-byte chunks of this group's half row
-            uint4 w;
-            w.x = pack2<kBf16>(__uint_as_float(v[b][8 * c + 0]), __uint_as_float(v[b][8 * c + 1]));
-            w.y = pack2<kBf16>(__uint_as_float(v[b][8 * c + 2]), __uint_as_float(v[b][8 * c + 3]));
-            w.z = pack2<kBf16>(__uint_as_float(v[b][8 * c + 4]), __uint_as_float(v[b][8 * c + 5]));
-            w.w = pack2<kBf16>(__uint_as_float(v[b][8 * c + 6]), __uint_as_float(v[b][8 * c + 7]));
-            sts128(dst + ((((lg & 1) * 4 + c) ^ (row & 7)) << 4), w);
+            for (int c = 0; c < 8; ++c) {
+              const uint4 w = make_uint4(v[b][4 * c], v[b][4 * c + 1], v[b][4 * c + 2], v[b][4 * c + 3]);
+              sts128(dst + ((c ^ (row & 7)) << 4), w);
+            }
+          } else {
+            const uint32_t dst = out_stage_s + (lg >> 1) * 16384 + row * 128;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {               // four 16-byte chunks of this group's half row
+              uint4 w;
+              w.x = pack2<kFmt>(__uint_as_float(v[b][8 * c + 0]), __uint_as_float(v[b][8 * c + 1]));
+              w.y = pack2<kFmt>(__uint_as_float(v[b][8 * c + 2]), __uint_as_float(v[b][8 * c + 3]));
+              w.z = pack2<kFmt>(__uint_as_float(v[b][8 * c + 4]), __uint_as_float(v[b][8 * c + 5]));
+              w.w = pack2<kFmt>(__uint_as_float(v[b][8 * c + 6]), __uint_as_float(v[b][8 * c + 7]));
+              sts128(dst + ((((lg & 1) * 4 + c) ^ (row & 7)) << 4), w);
+            }
           }
         }
         fence_proxy_async();                     // generic-proxy smem writes -> visible to the TMA engine
         named_bar_sync(1, kEpiThreads);
         if (leader) {
 #pragma unroll
-          for (int j = 0; j < PASS_N / 64; ++j) {
-            const int nc = n0 + ps * PASS_N + j * 64;
+          for (int j = 0; j < PASS_N / BOX_N; ++j) {
+            const int nc = n0 + ps * PASS_N + j * BOX_N;
             if (nc < p.N) {
               if (p.accumulate)
                 tma_reduce_add_2d(&tmD, out_stage + j * 16384, nc, m_blk * BLOCK_M);
@@ -402,7 +436,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           for (int rb = 0; rb < BLOCK_M / 8; ++rb) {     // 8 rows per step: rows rg + 8*rb + i*G
 #pragma unroll
             for (int i = 0; i < SWZ; ++i) {
-              const float2 f = unpack2<kBf16>(lds32(st_off[i] + rb * (8 * 128)));
+              const float2 f = kTf32 ? lds64f(st_off[i] + rb * (8 * 128)) : unpack2<kFmt>(lds32(st_off[i] + rb * (8 * 128)));
               st_sum[ps] = __fadd2_rn(st_sum[ps], f);
               st_sq[ps] = __ffma2_rn(f, f, st_sq[ps]);
             }
@@ -453,19 +487,26 @@ struct WgradParams {
   int ldw;
   int num_m_blocks;         // ceil(Cout / 128)
   int num_n_blocks;         // ceil(Ktot / BLOCK_N)
-  int num_kb;               // ceil(Mpix / 64)
+  int num_kb;               // ceil(Mpix / pixels per k-block)
   int kb_per_split, num_splits;
-  int cin_blocks, S;        // 64-wide column chunk j -> tap = j / cin_blocks, c0 = (j % cin_blocks)*64
+  int cin_blocks, S;        // column chunk j (one MN atom wide) -> tap = j / cin_blocks, c0 = (j % cin_blocks) * atom
   int P, Q, stride, pad;
   int b_im2col;
   FastDiv div_pq, div_q, div_cin;
   float* dw;
 };
 
-template <int BLOCK_N>
+// MN-major operands: a TMA box ("chunk") is KB_PIX pixel rows of 128 bytes, i.e. one MN atom of 64 16-bit or 32 fp32
+// columns.  A k-block is 64 pixels (16-bit) or 32 pixels (fp32): the same 48 KB per stage for a 128 x 256 tile and
+// four MMAs per stage in both formats.
+template <int BLOCK_N, int ES = 2>
 struct WgradSmem {
-  static constexpr uint32_t A_BYTES = 2 * CHUNK_BYTES;                    // 128 couts x 64 pixels
-  static constexpr uint32_t B_BYTES = (BLOCK_N / 64) * CHUNK_BYTES;       // BLOCK_N cols x 64 pixels
+  static constexpr int MN_ATOM = 128 / ES;                                 // columns per chunk: 64 / 32
+  static constexpr int KB_PIX = ES == 4 ? 32 : 64;                         // pixels per k-block
+  static constexpr uint32_t CHUNK_BYTES = KB_PIX * 128;                    // 8 KB / 4 KB
+  static constexpr int A_CHUNKS = BLOCK_M / MN_ATOM, B_CHUNKS = BLOCK_N / MN_ATOM;
+  static constexpr uint32_t A_BYTES = A_CHUNKS * CHUNK_BYTES;              // 128 couts x KB_PIX pixels
+  static constexpr uint32_t B_BYTES = B_CHUNKS * CHUNK_BYTES;              // BLOCK_N cols x KB_PIX pixels
   static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int kStages = BLOCK_N == 256 ? 4 : 6;
   static constexpr uint32_t BAR_OFFSET = kStages * STAGE_BYTES;
@@ -474,12 +515,18 @@ struct WgradSmem {
 
 // kStem: X is the space-to-depth stem input (16 channels per pixel): the 256 output columns are 16 taps x 16
 // channels, loaded as sixteen [64 pixels x 32 B] blocks per stage in 32-byte-swizzled MN-major layout.
-template <int BLOCK_N, bool kBf16, bool kStem = false>
+template <int BLOCK_N, int kFmt, bool kStem = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
                   const __grid_constant__ CUtensorMap tmB /* X: tiled [Mpix, C] or im2col (C,W,H,N) */,
                   const WgradParams p) {
-  using L = WgradSmem<BLOCK_N>;
+  using F = Fmt<kFmt>;
+  constexpr bool kTf32 = kFmt == kFmtTf32;
+  constexpr int UMMA_K = F::UMMA_K;
+  static_assert(!(kStem && kTf32), "the space-to-depth stem kernels are 16-bit only");
+  using L = WgradSmem<BLOCK_N, F::ES>;
+  constexpr int MN_ATOM = L::MN_ATOM, KB_PIX = L::KB_PIX, A_CHUNKS = L::A_CHUNKS, B_CHUNKS = L::B_CHUNKS;
+  constexpr uint32_t CHUNK_BYTES = L::CHUNK_BYTES;
   constexpr int kStages = L::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -524,20 +571,20 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.num_kb);
         // the (tap, channel-block) of each 64-column chunk of this output tile is fixed for the whole item
-        int ch_c[BLOCK_N / 64], ch_s[BLOCK_N / 64], ch_r[BLOCK_N / 64];
+        int ch_c[B_CHUNKS], ch_s[B_CHUNKS], ch_r[B_CHUNKS];
 #pragma unroll
-        for (int j = 0; j < BLOCK_N / 64; ++j) {
-          const int chunk = n_blk * (BLOCK_N / 64) + j;            // global 64-column chunk index
+        for (int j = 0; j < B_CHUNKS; ++j) {
+          const int chunk = n_blk * B_CHUNKS + j;                  // global column chunk index (MN_ATOM columns each)
           if (p.b_im2col) {
             const int tap = (int)p.div_cin.div((uint32_t)chunk);
             const int cb = chunk - tap * p.cin_blocks;
             const int r = tap / p.S;
             // chunks past Ktot: channel coordinate past C -> zero fill (tap clamped to stay in range)
-            ch_c[j] = chunk * 64 < p.Ktot ? cb * 64 : (1 << 20);
+            ch_c[j] = chunk * MN_ATOM < p.Ktot ? cb * MN_ATOM : (1 << 20);
             ch_s[j] = tap - r * p.S;
             ch_r[j] = min(r, 15);
           } else {
-            ch_c[j] = chunk * 64, ch_s[j] = 0, ch_r[j] = 0;
+            ch_c[j] = chunk * MN_ATOM, ch_s[j] = 0, ch_r[j] = 0;
           }
         }
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -545,10 +592,11 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
           uint8_t* sA = smem + stage * L::STAGE_BYTES;
           uint8_t* sB = sA + L::A_BYTES;
           mbar_arrive_expect_tx(full + stage, L::STAGE_BYTES);
-          const int pix0 = kb * 64;
-          // A: two boxes of [64 pixels][64 couts]; couts past Cout are zero-filled
-          tma_load_2d(sA, &tmA, full + stage, m_blk * BLOCK_M, pix0);
-          tma_load_2d(sA + CHUNK_BYTES, &tmA, full + stage, m_blk * BLOCK_M + 64, pix0);
+          const int pix0 = kb * KB_PIX;
+          // A: boxes of [KB_PIX pixels][MN_ATOM couts]; couts past Cout are zero-filled
+#pragma unroll
+          for (int j = 0; j < A_CHUNKS; ++j)
+            tma_load_2d(sA + j * CHUNK_BYTES, &tmA, full + stage, m_blk * BLOCK_M + j * MN_ATOM, pix0);
           if (kStem) {
             const int n_img = (int)p.div_pq.div((uint32_t)pix0);
             const int rem = pix0 - n_img * p.P * p.Q;
@@ -563,12 +611,12 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
             const int pp = (int)p.div_q.div((uint32_t)rem), qq = rem - pp * p.Q;
             const int base_w = qq * p.stride - p.pad, base_h = pp * p.stride - p.pad;
 #pragma unroll
-            for (int j = 0; j < BLOCK_N / 64; ++j)
+            for (int j = 0; j < B_CHUNKS; ++j)
               tma_load_im2col_4d(sB + j * CHUNK_BYTES, &tmB, full + stage, ch_c[j], base_w, base_h, n_img,
                                  (uint16_t)ch_s[j], (uint16_t)ch_r[j]);
           } else {
 #pragma unroll
-            for (int j = 0; j < BLOCK_N / 64; ++j)
+            for (int j = 0; j < B_CHUNKS; ++j)
               tma_load_2d(sB + j * CHUNK_BYTES, &tmB, full + stage, ch_c[j], pix0);
           }
           if (++stage == kStages) stage = 0, phase ^= 1;
@@ -576,9 +624,10 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
       }
     }
   } else if (warp == 1) {
-    constexpr uint32_t idesc = umma_idesc_f16(kBf16 ? 1 : 0, BLOCK_M, BLOCK_N, 1, 1);
-    // MN-major SW128: LBO = distance between 64-element MN atoms (one TMA box), SBO = 8 K-rows x 128 B
-    constexpr uint64_t desc_base = umma_desc_base(CHUNK_BYTES, 1024);
+    constexpr uint32_t idesc = kTf32 ? umma_idesc_tf32(BLOCK_M, BLOCK_N, 1, 1) : umma_idesc_f16(kFmt == 0 ? 1 : 0, BLOCK_M, BLOCK_N, 1, 1);
+    // MN-major SW128: LBO = distance between MN atoms (one TMA box), SBO = 8 K-rows x 128 B.  32-bit operands only
+    // exist in the layout swizzled in 32-byte units with a 4-row period: SBO = 4 K-rows x 128 B.
+    constexpr uint64_t desc_base = kTf32 ? umma_desc_base(CHUNK_BYTES, 512, kLayoutSw128Base32) : umma_desc_base(CHUNK_BYTES, 1024);
     // stem B operand, MN-major SW32: LBO = one [64 pixels x 32 B] tap block, SBO = 8 pixel rows x 32 B
     constexpr uint64_t desc_base_b = kStem ? umma_desc_base(2048, 256, kLayoutSw32) : desc_base;
     constexpr uint32_t kStepB = kStem ? UMMA_K * 32 : UMMA_K * 128;
@@ -598,9 +647,10 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA /* dY [Mpix, Cout] */,
           const uint32_t a_addr = smem_u32(smem + stage * L::STAGE_BYTES);
           const uint32_t b_addr = a_addr + L::A_BYTES;
 #pragma unroll
-          for (int k = 0; k < 64 / UMMA_K; ++k) {       // 16 pixel rows x 128 B per MMA
-            umma_f16(d_tmem, umma_desc(desc_base, a_addr + k * UMMA_K * 128), umma_desc(desc_base_b, b_addr + k * kStepB),
-                     idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < KB_PIX / UMMA_K; ++k) {   // UMMA_K (16 / 8) pixel rows x 128 B per MMA
+            const uint64_t da = umma_desc(desc_base, a_addr + k * UMMA_K * 128), db = umma_desc(desc_base_b, b_addr + k * kStepB);
+            if (kTf32) umma_tf32(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           umma_commit(empty + stage);
           if (kb == kb1 - 1) umma_commit(tfull + acc);
@@ -683,21 +733,28 @@ static int load_driver_fns() {
   return 0;
 }
 
-static CUtensorMapDataType tm_dtype(int dtype) {
+// `operand`: the map feeds an MMA operand.  fp32 operands are loaded as TFLOAT32: the copy engine rounds them to the
+// 10-bit mantissa (round to nearest) on their way into shared memory, where the tensor core would otherwise just
+// ignore the low 13 bits (truncation, a systematic bias) — the same conversion cuDNN's TF32 kernels apply.
+static CUtensorMapDataType tm_dtype(int dtype, bool operand) {
+  if (dtype == PDB_FP32) return operand ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   return dtype == PDB_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
 }
+static inline int elem_bytes(int dtype) { return dtype == PDB_FP32 ? 4 : 2; }
 
-// 2-D row-major [rows, cols] 16-bit matrix with row pitch ld (elements); box = [box_rows, box_cols]
+// 2-D row-major [rows, cols] matrix with row pitch ld (elements); box = [box_rows, box_cols]
 static int make_tiled_2d(CUtensorMap* m, const void* ptr, int dtype, uint64_t rows, uint64_t cols, uint64_t ld,
-                         uint32_t box_rows, uint32_t box_cols, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
+                         uint32_t box_rows, uint32_t box_cols, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B,
+                         bool operand = true) {
+  const uint64_t es = (uint64_t)elem_bytes(dtype);
   cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {ld * 2};
+  cuuint64_t strides[1] = {ld * es};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  PDB_CHECK_ARG((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld * 2) % 16 == 0,
+  PDB_CHECK_ARG((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld * es) % 16 == 0,
                 "tensor map: base must be 16-byte aligned and the row pitch a multiple of 16 bytes (ld=%llu)",
                 (unsigned long long)ld);
-  CUresult r = g_tiled(m, tm_dtype(dtype), 2, const_cast<void*>(ptr), dims, strides, box, estr,
+  CUresult r = g_tiled(m, tm_dtype(dtype, operand), 2, const_cast<void*>(ptr), dims, strides, box, estr,
                        CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   PDB_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d (rows=%llu cols=%llu ld=%llu box=%ux%u)",
@@ -709,17 +766,19 @@ static int make_tiled_2d(CUtensorMap* m, const void* ptr, int dtype, uint64_t ro
 // pad_hi < 0: symmetric padding.  cbox / swz: channels per load and the matching shared-memory swizzle (64 / 128B for
 // the regular layers, 16 / 32B for the space-to-depth stem).
 static int make_im2col_4d(CUtensorMap* m, const void* ptr, int dtype, int N, int H, int W, int C, int R, int S,
-                          int stride, int pad, uint32_t pixels, int pad_hi = -1, uint32_t cbox = 64,
+                          int stride, int pad, uint32_t pixels, int pad_hi = -1, uint32_t cbox = 0,
                           CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
+  const cuuint64_t es = (cuuint64_t)elem_bytes(dtype);
+  if (cbox == 0) cbox = (uint32_t)(128 / es);        // one 128-byte swizzle row of channels
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint64_t strides[3] = {(cuuint64_t)C * es, (cuuint64_t)W * C * es, (cuuint64_t)H * W * C * es};
   if (pad_hi < 0) pad_hi = pad;
   int lower[2] = {-pad, -pad};
   int upper[2] = {pad_hi - (S - 1), pad_hi - (R - 1)};
   cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
-  PDB_CHECK_ARG((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (C * 2) % 16 == 0,
-                "im2col tensor map: base must be 16-byte aligned and C a multiple of 8");
-  CUresult r = g_im2col(m, tm_dtype(dtype), 4, const_cast<void*>(ptr), dims, strides, lower, upper, cbox, pixels, estr,
+  PDB_CHECK_ARG((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (C * es) % 16 == 0,
+                "im2col tensor map: base must be 16-byte aligned and the pixel pitch a multiple of 16 bytes");
+  CUresult r = g_im2col(m, tm_dtype(dtype, true), 4, const_cast<void*>(ptr), dims, strides, lower, upper, cbox, pixels, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   PDB_CHECK_ARG(r == CUDA_SUCCESS, "cuTensorMapEncodeIm2col failed with %d (N=%d H=%d W=%d C=%d R=%d S=%d stride=%d pad=%d)",
@@ -742,15 +801,15 @@ static int walk_period(int units, int n_blocks) {
   return n_blocks / a;          // n_blocks / gcd(units, n_blocks)
 }
 
-template <bool kBf16>
+template <int kFmt>
 static int launch_fprop_pair(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, FpropParams p,
                              cudaStream_t st) {
   constexpr int BN = 256;
   static bool configured[64] = {};
-  auto kernel = conv_fprop_kernel<BN, kBf16, true>;
+  auto kernel = conv_fprop_kernel<BN, kFmt, true>;
   int dev = 0;
   PDB_CUDA(cudaGetDevice(&dev));
-  const uint32_t smem = FpropSmem<BN, true>::TOTAL;
+  const uint32_t smem = FpropSmem<BN, true, Fmt<kFmt>::ES>::TOTAL;
   if (!configured[dev & 63]) {
     if (int e = set_smem(kernel, smem)) return e;
     configured[dev & 63] = true;
@@ -772,40 +831,42 @@ static int launch_fprop_pair(const CUtensorMap& a, const CUtensorMap& b, const C
   return 0;
 }
 
-template <int BLOCK_N, bool kBf16, bool kStem = false>
+template <int BLOCK_N, int kFmt, bool kStem = false>
 static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, FpropParams p,
                         cudaStream_t st) {
   // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute (the single-process
   // DataParallel mode launches from one process on every GPU)
   static bool configured[64] = {};
-  auto kernel = conv_fprop_kernel<BLOCK_N, kBf16, false, kStem>;
+  auto kernel = conv_fprop_kernel<BLOCK_N, kFmt, false, kStem>;
+  constexpr uint32_t smem = FpropSmem<BLOCK_N, false, Fmt<kFmt>::ES>::TOTAL;
   int dev = 0;
   PDB_CUDA(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
-    if (int e = set_smem(kernel, FpropSmem<BLOCK_N>::TOTAL)) return e;
+    if (int e = set_smem(kernel, smem)) return e;
     configured[dev & 63] = true;
   }
   const int tiles = p.num_m_blocks * p.num_n_blocks;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   p.tile_period = walk_period(grid, p.num_n_blocks);
-  kernel<<<grid, kNumThreads, FpropSmem<BLOCK_N>::TOTAL, st>>>(a, b, d, p);
+  kernel<<<grid, kNumThreads, smem, st>>>(a, b, d, p);
   PDB_LAUNCH_CHECK();
   return 0;
 }
 
-template <int BLOCK_N, bool kBf16, bool kStem = false>
+template <int BLOCK_N, int kFmt, bool kStem = false>
 static int launch_wgrad(const CUtensorMap& a, const CUtensorMap& b, const WgradParams& p, cudaStream_t st) {
   static bool configured[64] = {};
-  auto kernel = conv_wgrad_kernel<BLOCK_N, kBf16, kStem>;
+  auto kernel = conv_wgrad_kernel<BLOCK_N, kFmt, kStem>;
+  constexpr uint32_t smem = WgradSmem<BLOCK_N, Fmt<kFmt>::ES>::TOTAL;
   int dev = 0;
   PDB_CUDA(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
-    if (int e = set_smem(kernel, WgradSmem<BLOCK_N>::TOTAL)) return e;
+    if (int e = set_smem(kernel, smem)) return e;
     configured[dev & 63] = true;
   }
   const int items = p.num_m_blocks * p.num_n_blocks * p.num_splits;
   const int grid = items < num_sms() ? items : num_sms();
-  kernel<<<grid, kNumThreads, WgradSmem<BLOCK_N>::TOTAL, st>>>(a, b, p);
+  kernel<<<grid, kNumThreads, smem, st>>>(a, b, p);
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -819,14 +880,16 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
                               int64_t ldd, float* stats, float* stats_scratch, const float* bias, int block_n,
                               int accumulate, void* stream) {
   PDB_CHECK_ARG(x && w && y && s, "pdb_conv_fprop: null pointer");
-  PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16, "pdb_conv_fprop: dtype must be PDB_BF16 or PDB_FP16");
+  PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16 || dtype == PDB_FP32,
+                "pdb_conv_fprop: dtype must be PDB_BF16, PDB_FP16 or PDB_FP32");
   if (int e = load_driver_fns()) return e;
+  const int es = elem_bytes(dtype), block_k = 128 / es;     // elements per k-block
   const int P = (s->H + 2 * s->pad - s->R) / s->stride + 1, Q = (s->W + 2 * s->pad - s->S) / s->stride + 1;
   const int64_t M = (int64_t)s->N * P * Q;
   const bool plain = s->R == 1 && s->S == 1 && s->stride == 1 && s->pad == 0;
   PDB_CHECK_ARG(M > 0 && M < (1ll << 31) && s->K > 0 && s->C > 0, "pdb_conv_fprop: bad shape");
-  PDB_CHECK_ARG(s->C % 8 == 0, "pdb_conv_fprop: C=%d must be a multiple of 8 (16-byte rows)", s->C);
-  PDB_CHECK_ARG(plain || s->C % 64 == 0, "pdb_conv_fprop: im2col path needs C %% 64 == 0 (C=%d)", s->C);
+  PDB_CHECK_ARG((s->C * es) % 16 == 0, "pdb_conv_fprop: rows of C=%d elements are not a multiple of 16 bytes", s->C);
+  PDB_CHECK_ARG(plain || s->C % block_k == 0, "pdb_conv_fprop: im2col path needs C %% %d == 0 (C=%d)", block_k, s->C);
   if (lda <= 0) lda = s->C;
   if (ldd <= 0) ldd = s->K;
   int bn = block_n;
@@ -846,7 +909,7 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
   p.M = (int)M, p.N = s->K;
   p.num_m_blocks = (int)((M + BLOCK_M - 1) / BLOCK_M);
   p.num_n_blocks = (s->K + bn - 1) / bn;
-  p.taps = s->R * s->S, p.cin_blocks = (s->C + BLOCK_K - 1) / BLOCK_K, p.S = s->S;
+  p.taps = s->R * s->S, p.cin_blocks = (s->C + block_k - 1) / block_k, p.S = s->S;
   p.P = P, p.Q = Q, p.stride = s->stride, p.pad = s->pad;
   p.a_im2col = plain ? 0 : 1;
   p.accumulate = accumulate ? 1 : 0;
@@ -855,18 +918,24 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
 
   CUtensorMap tmA, tmB, tmD;
   if (plain) {
-    if (int e = make_tiled_2d(&tmA, x, dtype, (uint64_t)M, (uint64_t)s->C, (uint64_t)lda, BLOCK_M, BLOCK_K)) return e;
+    if (int e = make_tiled_2d(&tmA, x, dtype, (uint64_t)M, (uint64_t)s->C, (uint64_t)lda, BLOCK_M, block_k)) return e;
   } else {
     if (int e = make_im2col_4d(&tmA, x, dtype, s->N, s->H, s->W, s->C, s->R, s->S, s->stride, s->pad, BLOCK_M)) return e;
   }
   const uint64_t ktot = (uint64_t)p.taps * s->C;
-  if (int e = make_tiled_2d(&tmB, w, dtype, (uint64_t)s->K, ktot, ktot, (uint32_t)(pair ? bn / 2 : bn), BLOCK_K)) return e;
-  if (int e = make_tiled_2d(&tmD, y, dtype, (uint64_t)M, (uint64_t)s->K, (uint64_t)ldd, BLOCK_M, 64)) return e;
+  if (int e = make_tiled_2d(&tmB, w, dtype, (uint64_t)s->K, ktot, ktot, (uint32_t)(pair ? bn / 2 : bn), block_k)) return e;
+  if (int e = make_tiled_2d(&tmD, y, dtype, (uint64_t)M, (uint64_t)s->K, (uint64_t)ldd, BLOCK_M, block_k,
+                            CU_TENSOR_MAP_SWIZZLE_128B, false)) return e;
 
   cudaStream_t st = (cudaStream_t)stream;
-  if (pair) return dtype == PDB_BF16 ? launch_fprop_pair<true>(tmA, tmB, tmD, p, st) : launch_fprop_pair<false>(tmA, tmB, tmD, p, st);
-#define GO(BN)                                                              \
-  (dtype == PDB_BF16 ? launch_fprop<BN, true>(tmA, tmB, tmD, p, st) : launch_fprop<BN, false>(tmA, tmB, tmD, p, st))
+  if (pair)
+    return dtype == PDB_BF16   ? launch_fprop_pair<0>(tmA, tmB, tmD, p, st)
+           : dtype == PDB_FP16 ? launch_fprop_pair<1>(tmA, tmB, tmD, p, st)
+                               : launch_fprop_pair<2>(tmA, tmB, tmD, p, st);
+#define GO(BN)                                                           \
+  (dtype == PDB_BF16   ? launch_fprop<BN, 0>(tmA, tmB, tmD, p, st)       \
+   : dtype == PDB_FP16 ? launch_fprop<BN, 1>(tmA, tmB, tmD, p, st)       \
+                       : launch_fprop<BN, 2>(tmA, tmB, tmD, p, st))
   if (bn == 64) return GO(64);
   if (bn == 128) return GO(128);
   return GO(256);
@@ -876,14 +945,19 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
 extern "C" int pdb_conv_wgrad(const void* x, const void* dy, float* dw, int dtype, const pdb_conv_shape* s, int64_t ldx,
                               int64_t lddy, int64_t ldw, int64_t kvalid, int splits, int block_n, void* stream) {
   PDB_CHECK_ARG(x && dy && dw && s, "pdb_conv_wgrad: null pointer");
-  PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16, "pdb_conv_wgrad: dtype must be PDB_BF16 or PDB_FP16");
+  PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16 || dtype == PDB_FP32,
+                "pdb_conv_wgrad: dtype must be PDB_BF16, PDB_FP16 or PDB_FP32");
   if (int e = load_driver_fns()) return e;
+  const int es = elem_bytes(dtype);
+  const int atom = 128 / es;                    // MN atom: columns per TMA box (64 / 32)
+  const int kb_pix = es == 4 ? 32 : 64;         // pixels per k-block
+  const CUtensorMapSwizzle mn_swz = es == 4 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
   const int P = (s->H + 2 * s->pad - s->R) / s->stride + 1, Q = (s->W + 2 * s->pad - s->S) / s->stride + 1;
   const int64_t M = (int64_t)s->N * P * Q;
   const bool plain = s->R == 1 && s->S == 1 && s->stride == 1 && s->pad == 0;
   PDB_CHECK_ARG(M > 0 && M < (1ll << 31) && s->K > 0 && s->C > 0, "pdb_conv_wgrad: bad shape");
-  PDB_CHECK_ARG(s->C % 8 == 0 && s->K % 8 == 0, "pdb_conv_wgrad: C and K must be multiples of 8");
-  PDB_CHECK_ARG(plain || s->C % 64 == 0, "pdb_conv_wgrad: im2col path needs C %% 64 == 0 (C=%d)", s->C);
+  PDB_CHECK_ARG((s->C * es) % 16 == 0 && (s->K * es) % 16 == 0, "pdb_conv_wgrad: rows of C / K elements must be multiples of 16 bytes");
+  PDB_CHECK_ARG(plain || s->C % atom == 0, "pdb_conv_wgrad: im2col path needs C %% %d == 0 (C=%d)", atom, s->C);
   if (ldx <= 0) ldx = s->C;
   if (lddy <= 0) lddy = s->K;
   const int ktot = s->R * s->S * s->C;
@@ -897,34 +971,38 @@ extern "C" int pdb_conv_wgrad(const void* x, const void* dy, float* dw, int dtyp
   p.Kvalid = kvalid > 0 && kvalid < ktot ? (int)kvalid : ktot;
   p.num_m_blocks = (s->K + BLOCK_M - 1) / BLOCK_M;
   p.num_n_blocks = (ktot + bn - 1) / bn;
-  p.num_kb = (int)((M + 63) / 64);
+  p.num_kb = (int)((M + kb_pix - 1) / kb_pix);
   const int tiles = p.num_m_blocks * p.num_n_blocks;
   if (splits <= 0) {
     // One wave of persistent CTAs: items = tiles * splits must not spill over the SM count (a second,
     // nearly empty wave doubles the time — measured with bench_tools/conv_tune.py), and every extra split
     // costs a full tile of fp32 reductions; keep at least 4 k-blocks of work per item.
     splits = num_sms() / tiles;
-    const int max_splits = (p.num_kb + 3) / 4;
+    const int max_splits = (p.num_kb * kb_pix / 64 + 3) / 4;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
   }
   p.kb_per_split = (p.num_kb + splits - 1) / splits;
   p.num_splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
-  p.cin_blocks = (s->C + 63) / 64, p.S = s->S;
+  p.cin_blocks = (s->C + atom - 1) / atom, p.S = s->S;
   p.P = P, p.Q = Q, p.stride = s->stride, p.pad = s->pad;
   p.b_im2col = plain ? 0 : 1;
   p.div_pq.init((uint32_t)(P * Q)), p.div_q.init((uint32_t)Q), p.div_cin.init((uint32_t)p.cin_blocks);
   p.dw = dw;
 
   CUtensorMap tmA, tmB;
-  if (int e = make_tiled_2d(&tmA, dy, dtype, (uint64_t)M, (uint64_t)s->K, (uint64_t)lddy, 64, 64)) return e;
+  if (int e = make_tiled_2d(&tmA, dy, dtype, (uint64_t)M, (uint64_t)s->K, (uint64_t)lddy, kb_pix, atom, mn_swz)) return e;
   if (plain) {
-    if (int e = make_tiled_2d(&tmB, x, dtype, (uint64_t)M, (uint64_t)s->C, (uint64_t)ldx, 64, 64)) return e;
+    if (int e = make_tiled_2d(&tmB, x, dtype, (uint64_t)M, (uint64_t)s->C, (uint64_t)ldx, kb_pix, atom, mn_swz)) return e;
   } else {
-    if (int e = make_im2col_4d(&tmB, x, dtype, s->N, s->H, s->W, s->C, s->R, s->S, s->stride, s->pad, 64)) return e;
+    if (int e = make_im2col_4d(&tmB, x, dtype, s->N, s->H, s->W, s->C, s->R, s->S, s->stride, s->pad, kb_pix, -1, atom, mn_swz))
+      return e;
   }
   cudaStream_t st = (cudaStream_t)stream;
-#define GO(BN) (dtype == PDB_BF16 ? launch_wgrad<BN, true>(tmA, tmB, p, st) : launch_wgrad<BN, false>(tmA, tmB, p, st))
+#define GO(BN)                                                     \
+  (dtype == PDB_BF16   ? launch_wgrad<BN, 0>(tmA, tmB, p, st)      \
+   : dtype == PDB_FP16 ? launch_wgrad<BN, 1>(tmA, tmB, p, st)      \
+                       : launch_wgrad<BN, 2>(tmA, tmB, p, st))
   if (bn == 64) return GO(64);
   if (bn == 128) return GO(128);
   return GO(256);
@@ -956,8 +1034,8 @@ extern "C" int pdb_stem_fprop(const void* xs, const void* ws, void* y, int dtype
   if (int e = make_tiled_2d(&tmB, ws, dtype, 64, 256, 256, 64, 16, CU_TENSOR_MAP_SWIZZLE_32B)) return e;
   if (int e = make_tiled_2d(&tmD, y, dtype, (uint64_t)M, 64, 64, BLOCK_M, 64)) return e;
   cudaStream_t st = (cudaStream_t)stream;
-  return dtype == PDB_BF16 ? launch_fprop<64, true, true>(tmA, tmB, tmD, p, st)
-                           : launch_fprop<64, false, true>(tmA, tmB, tmD, p, st);
+  return dtype == PDB_BF16 ? launch_fprop<64, 0, true>(tmA, tmB, tmD, p, st)
+                           : launch_fprop<64, 1, true>(tmA, tmB, tmD, p, st);
 }
 
 // dws[64, 256] (fp32, same column order as ws) += dY[M, 64]^T * im2col(xs); unpack with pdb_stem_dw_unpack.
@@ -985,5 +1063,5 @@ extern "C" int pdb_stem_wgrad(const void* xs, const void* dy, float* dws, int dt
   if (int e = make_tiled_2d(&tmA, dy, dtype, (uint64_t)M, 64, 64, 64, 64)) return e;
   if (int e = make_im2col_4d(&tmB, xs, dtype, N, Hs, Ws, 16, 4, 4, 1, 2, 64, 1, 16, CU_TENSOR_MAP_SWIZZLE_32B)) return e;
   cudaStream_t st = (cudaStream_t)stream;
-  return dtype == PDB_BF16 ? launch_wgrad<256, true, true>(tmA, tmB, p, st) : launch_wgrad<256, false, true>(tmA, tmB, p, st);
+  return dtype == PDB_BF16 ? launch_wgrad<256, 0, true>(tmA, tmB, p, st) : launch_wgrad<256, 1, true>(tmA, tmB, p, st);
 }

@@ -7,10 +7,13 @@ namespace pdb {
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
-template <typename T>
+// TD: storage type of the gradient.  fp32 (the default of the Python layer) keeps (softmax - onehot)/rows exact until
+// the amp loss scale has been applied: rounded to fp16 first, entries below 2^-24 * rows vanish and a scale of 65536
+// itself does not fit the format.
+template <typename T, typename TD>
 __global__ void __launch_bounds__(256) xent_kernel(const T* __restrict__ logits, const int64_t* __restrict__ labels,
                                                    int rows, int classes, float* __restrict__ loss,
-                                                   T* __restrict__ dlogits, const float* __restrict__ grad_scale) {
+                                                   TD* __restrict__ dlogits, const float* __restrict__ grad_scale) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= rows) return;
   const T* row = logits + (int64_t)warp * classes;
@@ -29,10 +32,10 @@ __global__ void __launch_bounds__(256) xent_kernel(const T* __restrict__ logits,
   if (dlogits != nullptr) {
     const float gs = (grad_scale ? *grad_scale : 1.0f) * inv_rows;
     const float inv_s = 1.0f / s;
-    T* drow = dlogits + (int64_t)warp * classes;
+    TD* drow = dlogits + (int64_t)warp * classes;
     for (int c = lane; c < classes; c += 32) {
       float p = exp2f((Elem<T>::to_f(row[c]) - m) * kLog2e) * inv_s;
-      drow[c] = Elem<T>::from_f((p - (c == y ? 1.f : 0.f)) * gs);
+      drow[c] = Elem<TD>::from_f((p - (c == y ? 1.f : 0.f)) * gs);
     }
   }
 }
@@ -63,11 +66,18 @@ __global__ void __launch_bounds__(256) topk_kernel(const T* __restrict__ logits,
 using namespace pdb;
 
 extern "C" int pdb_xent_fwd_bwd(const void* logits, int dtype, const int64_t* labels, int rows, int classes,
-                                float* loss, void* dlogits, const float* grad_scale, void* stream) {
+                                float* loss, void* dlogits, int dlogits_dtype, const float* grad_scale, void* stream) {
   PDB_CHECK_ARG(logits && labels && loss && rows > 0 && classes > 0, "pdb_xent_fwd_bwd: bad arguments");
+  PDB_CHECK_ARG(!dlogits || dlogits_dtype == dtype || dlogits_dtype == PDB_FP32,
+                "pdb_xent_fwd_bwd: dlogits must have the logits' dtype or be fp32");
   const int grid = (rows * 32 + 255) / 256;
-  PDB_DISPATCH_16(dtype, T, (xent_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(
-                                (const T*)logits, labels, rows, classes, loss, (T*)dlogits, grad_scale)));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dlogits && dlogits_dtype == PDB_FP32)
+    PDB_DISPATCH_ACT(dtype, T, (xent_kernel<T, float><<<grid, 256, 0, st>>>((const T*)logits, labels, rows, classes, loss,
+                                                                            (float*)dlogits, grad_scale)));
+  else
+    PDB_DISPATCH_ACT(dtype, T, (xent_kernel<T, T><<<grid, 256, 0, st>>>((const T*)logits, labels, rows, classes, loss,
+                                                                        (T*)dlogits, grad_scale)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -76,7 +86,7 @@ extern "C" int pdb_topk_correct(const void* logits, int dtype, const int64_t* la
                                 const int* ks, int nk, float* out, void* stream) {
   PDB_CHECK_ARG(logits && labels && ks && out && rows > 0 && classes > 0 && nk > 0, "pdb_topk_correct: bad arguments");
   const int grid = (rows * 32 + 255) / 256;
-  PDB_DISPATCH_16(dtype, T, (topk_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>((const T*)logits, labels, rows,
+  PDB_DISPATCH_ACT(dtype, T, (topk_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>((const T*)logits, labels, rows,
                                                                                      classes, ks, nk, out)));
   PDB_LAUNCH_CHECK();
   return 0;

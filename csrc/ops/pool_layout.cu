@@ -37,14 +37,14 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const T* __restrict__ 
         const int w = 2 * wo - 1 + kw;
         if (w < 0 || w >= W) continue;
         float f[8];
-        unpack8<T>(ldg128(xn + ((int64_t)h * W + w) * C + cg * 8), f);
+        unpack8<T>(ld8<T>(xn + ((int64_t)h * W + w) * C + cg * 8), f);
 #pragma unroll
         for (int k = 0; k < 8; ++k)
           if (f[k] > best[k]) best[k] = f[k], idx[k] = kh * 3 + kw;
       }
     }
     const int64_t o = orow + (int64_t)j * 8;
-    stg128(y + o, pack8<T>(best));
+    st8<T>(y + o, pack8v<T>(best));
     uint2 packed;
     packed.x = idx[0] | (idx[1] << 8) | (idx[2] << 16) | (idx[3] << 24);
     packed.y = idx[4] | (idx[5] << 8) | (idx[6] << 16) | (idx[7] << 24);
@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ 
     // the (up to) four windows are loaded up front — independent loads in flight instead of a dependent loop — and
     // the argmax bytes are compared four at a time
     uint2 a[4];
-    uint4 g[4];
+    V8<T> g[4];
     uint32_t pos4[4];
     bool live[4];
 #pragma unroll
@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ 
       if (live[t]) {
         const int64_t o = obase + ((int64_t)ho * Wo + wo) * C + cg * 8;
         a[t] = __ldg(reinterpret_cast<const uint2*>(argmax + o));
-        g[t] = ldg128(dy + o);
+        g[t] = ld8<T>(dy + o);
       }
     }
     float acc[8] = {0};
@@ -88,15 +88,12 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ 
     for (int t = 0; t < 4; ++t) {
       if (!live[t]) continue;
       const uint32_t m0 = __vcmpeq4(a[t].x, pos4[t]), m1 = __vcmpeq4(a[t].y, pos4[t]);   // 0xff per matching byte
-      uint4 v = g[t];
-      v.x &= __byte_perm(m0, 0, 0x1100), v.y &= __byte_perm(m0, 0, 0x3322);
-      v.z &= __byte_perm(m1, 0, 0x1100), v.w &= __byte_perm(m1, 0, 0x3322);
       float f[8];
-      unpack8<T>(v, f);
+      unpack8<T>(g[t], f);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      for (int k = 0; k < 8; ++k) acc[k] += ((k < 4 ? m0 >> (8 * k) : m1 >> (8 * (k - 4))) & 1u) ? f[k] : 0.f;
     }
-    stg128(dxrow + (int64_t)j * 8, pack8<T>(acc));
+    st8<T>(dxrow + (int64_t)j * 8, pack8v<T>(acc));
   }
 }
 
@@ -113,13 +110,13 @@ __global__ void __launch_bounds__(256) avgpool_fwd_kernel(const T* __restrict__ 
     float acc[8] = {0};
     for (int p = 0; p < HW; ++p) {
       float f[8];
-      unpack8<T>(ldg128(x + ((int64_t)n * HW + p) * C + cg * 8), f);
+      unpack8<T>(ld8<T>(x + ((int64_t)n * HW + p) * C + cg * 8), f);
 #pragma unroll
       for (int k = 0; k < 8; ++k) acc[k] += f[k];
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] *= inv;
-    stg128(y + i * 8, pack8<T>(acc));
+    st8<T>(y + i * 8, pack8v<T>(acc));
   }
 }
 
@@ -133,10 +130,10 @@ __global__ void __launch_bounds__(256) avgpool_bwd_kernel(const T* __restrict__ 
     const int cg = (int)(i % cvec);
     const int n = (int)(i / ((int64_t)HW * cvec));
     float f[8];
-    unpack8<T>(ldg128(dy + ((int64_t)n * C + cg * 8)), f);
+    unpack8<T>(ld8<T>(dy + ((int64_t)n * C + cg * 8)), f);
 #pragma unroll
     for (int k = 0; k < 8; ++k) f[k] *= inv;
-    stg128(dx + i * 8, pack8<T>(f));
+    st8<T>(dx + i * 8, pack8v<T>(f));
   }
 }
 
@@ -194,20 +191,20 @@ __global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restric
     float f[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) f[k] = off[k] >= 0 ? base[off[k]] : 0.f;
-    stg128(out + ((int64_t)wo * kvec + kv) * 8, pack8<T>(f));
+    st8<T>(out + ((int64_t)wo * kvec + kv) * 8, pack8v<T>(f));
   }
 }
 
 template <typename T>
 __global__ void __launch_bounds__(256) add16_kernel(const T* __restrict__ a, const T* __restrict__ b,
                                                     T* __restrict__ o, int64_t nvec) {
-  constexpr int U = 8;          // one tile per block (see bn_fast.cuh for the measurement behind this shape)
+  constexpr int U = sizeof(T) == 4 ? 4 : 8;          // one tile per block (see bn_fast.cuh for the measurement behind this shape)
   const int64_t base = (int64_t)blockIdx.x * (256 * U) + threadIdx.x;
-  uint4 va[U], vb[U];
+  V8<T> va[U], vb[U];
 #pragma unroll
   for (int u = 0; u < U; ++u) {
     const int64_t i = base + (int64_t)u * 256;
-    if (i < nvec) va[u] = ldg128_stream(a + i * 8), vb[u] = ldg128_stream(b + i * 8);
+    if (i < nvec) va[u] = ld8s<T>(a + i * 8), vb[u] = ld8s<T>(b + i * 8);
   }
 #pragma unroll
   for (int u = 0; u < U; ++u) {
@@ -218,7 +215,7 @@ __global__ void __launch_bounds__(256) add16_kernel(const T* __restrict__ a, con
     unpack8<T>(vb[u], fb);
 #pragma unroll
     for (int k = 0; k < 8; ++k) fa[k] += fb[k];
-    stg128(o + i * 8, pack8<T>(fa));
+    st8<T>(o + i * 8, pack8v<T>(fa));
   }
 }
 
@@ -233,9 +230,9 @@ __global__ void __launch_bounds__(256) upsample2_kernel(const T* __restrict__ sr
   const bool live = (h & 1) == 0;
   for (int j = threadIdx.x; j < W * cvec; j += blockDim.x) {
     const int w = j / cvec, cg = j - w * cvec;
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (live && (w & 1) == 0) v = ldg128_stream(srow + ((int64_t)(w / 2) * cvec + cg) * 8);
-    stg128(drow + (int64_t)j * 8, v);
+    V8<T> v = zero8<T>();
+    if (live && (w & 1) == 0) v = ld8s<T>(srow + ((int64_t)(w / 2) * cvec + cg) * 8);
+    st8<T>(drow + (int64_t)j * 8, v);
   }
 }
 
@@ -250,16 +247,16 @@ __global__ void __launch_bounds__(256) add_strided2_kernel(const T* __restrict__
   const bool live = (h & 1) == 0;
   for (int j = threadIdx.x; j < W * cvec; j += blockDim.x) {
     const int w = j / cvec, cg = j - w * cvec;
-    uint4 va = ldg128_stream(a + row + (int64_t)j * 8);
+    V8<T> va = ld8s<T>(a + row + (int64_t)j * 8);
     if (live && (w & 1) == 0) {
       float fa[8], fb[8];
       unpack8<T>(va, fa);
-      unpack8<T>(ldg128_stream(brow + ((int64_t)(w / 2) * cvec + cg) * 8), fb);
+      unpack8<T>(ld8s<T>(brow + ((int64_t)(w / 2) * cvec + cg) * 8), fb);
 #pragma unroll
       for (int k = 0; k < 8; ++k) fa[k] += fb[k];
-      va = pack8<T>(fa);
+      va = pack8v<T>(fa);
     }
-    stg128(o + row + (int64_t)j * 8, va);
+    st8<T>(o + row + (int64_t)j * 8, va);
   }
 }
 
@@ -285,8 +282,8 @@ __global__ void __launch_bounds__(128) stem_s2d_kernel(const float* __restrict__
     float lo[8], hi[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) lo[k] = f[k], hi[k] = f[8 + k];
-    stg128(out + q * 16, pack8<T>(lo));
-    stg128(out + q * 16 + 8, pack8<T>(hi));
+    st8<T>(out + q * 16, pack8v<T>(lo));
+    st8<T>(out + q * 16 + 8, pack8v<T>(hi));
   }
 }
 
@@ -323,7 +320,7 @@ extern "C" int pdb_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int
   PDB_CHECK_ARG(x && y && argmax && N > 0 && H > 0 && W > 0 && C % 8 == 0, "pdb_maxpool3x3s2_fwd: bad arguments");
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   PDB_CHECK_ARG((int64_t)N * Ho < (1ll << 31), "pdb_maxpool3x3s2_fwd: too many rows");
-  PDB_DISPATCH_16(dtype, T, (maxpool_fwd_kernel<T><<<N * Ho, 256, 0, ST>>>((const T*)x, (T*)y, argmax, H, W, C, Ho, Wo)));
+  PDB_DISPATCH_ACT(dtype, T, (maxpool_fwd_kernel<T><<<N * Ho, 256, 0, ST>>>((const T*)x, (T*)y, argmax, H, W, C, Ho, Wo)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -333,14 +330,14 @@ extern "C" int pdb_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void*
   PDB_CHECK_ARG(dy && dx && argmax && N > 0 && H > 0 && W > 0 && C % 8 == 0, "pdb_maxpool3x3s2_bwd: bad arguments");
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   PDB_CHECK_ARG((int64_t)N * H < (1ll << 31), "pdb_maxpool3x3s2_bwd: too many rows");
-  PDB_DISPATCH_16(dtype, T, (maxpool_bwd_kernel<T><<<N * H, 256, 0, ST>>>((const T*)dy, argmax, (T*)dx, H, W, C, Ho, Wo)));
+  PDB_DISPATCH_ACT(dtype, T, (maxpool_bwd_kernel<T><<<N * H, 256, 0, ST>>>((const T*)dy, argmax, (T*)dx, H, W, C, Ho, Wo)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int pdb_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW, int C, void* stream) {
   PDB_CHECK_ARG(x && y && N > 0 && HW > 0 && C % 8 == 0, "pdb_avgpool_fwd: bad arguments");
-  PDB_DISPATCH_16(dtype, T, (avgpool_fwd_kernel<T><<<ew_grid((int64_t)N * C / 8, 128), 128, 0, ST>>>((const T*)x, (T*)y,
+  PDB_DISPATCH_ACT(dtype, T, (avgpool_fwd_kernel<T><<<ew_grid((int64_t)N * C / 8, 128), 128, 0, ST>>>((const T*)x, (T*)y,
                                                                                                       N, HW, C)));
   PDB_LAUNCH_CHECK();
   return 0;
@@ -348,7 +345,7 @@ extern "C" int pdb_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW,
 
 extern "C" int pdb_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, void* stream) {
   PDB_CHECK_ARG(dy && dx && N > 0 && HW > 0 && C % 8 == 0, "pdb_avgpool_bwd: bad arguments");
-  PDB_DISPATCH_16(dtype, T, (avgpool_bwd_kernel<T><<<ew_grid((int64_t)N * HW * C / 8), 256, 0, ST>>>((const T*)dy,
+  PDB_DISPATCH_ACT(dtype, T, (avgpool_bwd_kernel<T><<<ew_grid((int64_t)N * HW * C / 8), 256, 0, ST>>>((const T*)dy,
                                                                                                       (T*)dx, N, HW, C)));
   PDB_LAUNCH_CHECK();
   return 0;
@@ -356,7 +353,7 @@ extern "C" int pdb_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int H
 
 extern "C" int pdb_nchw_f32_to_nhwc16(const float* x, void* y, int dtype, int N, int C, int H, int W, void* stream) {
   PDB_CHECK_ARG(x && y && N > 0 && C > 0 && H > 0 && W > 0, "pdb_nchw_f32_to_nhwc16: bad arguments");
-  PDB_DISPATCH_16(dtype, T, (nchw_to_nhwc_kernel<T><<<ew_grid((int64_t)N * H * W), 256, 0, ST>>>(x, (T*)y, N, C, H * W)));
+  PDB_DISPATCH_ACT(dtype, T, (nchw_to_nhwc_kernel<T><<<ew_grid((int64_t)N * H * W), 256, 0, ST>>>(x, (T*)y, N, C, H * W)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -367,14 +364,14 @@ extern "C" int pdb_stem_im2col(const float* x, void* col, int dtype, int N, int 
   const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
   const size_t smem = (size_t)7 * 3 * (W + 8) * sizeof(float);
   PDB_CHECK_ARG(smem <= 48 * 1024, "pdb_stem_im2col: image width %d too large for the row staging buffer", W);
-  PDB_DISPATCH_16(dtype, T, (stem_im2col_kernel<T><<<N * Ho, 256, smem, ST>>>(x, (T*)col, N, H, W, Ho, Wo, Kpad)));
+  PDB_DISPATCH_ACT(dtype, T, (stem_im2col_kernel<T><<<N * Ho, 256, smem, ST>>>(x, (T*)col, N, H, W, Ho, Wo, Kpad)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int pdb_add16(const void* a, const void* b, void* out, int dtype, int64_t n, void* stream) {
   PDB_CHECK_ARG(a && b && out && n > 0 && n % 8 == 0, "pdb_add16: bad arguments");
-  PDB_DISPATCH_16(dtype, T, (add16_kernel<T><<<(int)((n / 8 + 2047) / 2048), 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out, n / 8)));
+  PDB_DISPATCH_ACT(dtype, T, (add16_kernel<T><<<(int)((n / 8 + (dtype == PDB_FP32 ? 1023 : 2047)) / (dtype == PDB_FP32 ? 1024 : 2048)), 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out, n / 8)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -382,7 +379,7 @@ extern "C" int pdb_add16(const void* a, const void* b, void* out, int dtype, int
 extern "C" int pdb_upsample2_zero(const void* src, void* dst, int dtype, int N, int Ho, int Wo, int C, void* stream) {
   PDB_CHECK_ARG(src && dst && N > 0 && Ho > 0 && Wo > 0 && C % 8 == 0, "pdb_upsample2_zero: bad arguments");
   PDB_CHECK_ARG((int64_t)N * Ho * 2 < (1ll << 31), "pdb_upsample2_zero: too many rows");
-  PDB_DISPATCH_16(dtype, T, (upsample2_kernel<T><<<N * Ho * 2, 256, 0, ST>>>((const T*)src, (T*)dst, Ho, Wo, C)));
+  PDB_DISPATCH_ACT(dtype, T, (upsample2_kernel<T><<<N * Ho * 2, 256, 0, ST>>>((const T*)src, (T*)dst, Ho, Wo, C)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -391,7 +388,7 @@ extern "C" int pdb_add_strided2(const void* a, const void* b, void* out, int dty
                                 void* stream) {
   PDB_CHECK_ARG(a && b && out && N > 0 && H % 2 == 0 && W % 2 == 0 && C % 8 == 0, "pdb_add_strided2: bad arguments");
   PDB_CHECK_ARG((int64_t)N * H < (1ll << 31), "pdb_add_strided2: too many rows");
-  PDB_DISPATCH_16(dtype, T, (add_strided2_kernel<T><<<N * H, 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out, H, W, C)));
+  PDB_DISPATCH_ACT(dtype, T, (add_strided2_kernel<T><<<N * H, 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out, H, W, C)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -438,7 +435,7 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ a, fl
 
 extern "C" int pdb_weight_dgrad_layout(const void* w, void* wt, int dtype, int K, int R, int S, int C, void* stream) {
   PDB_CHECK_ARG(w && wt && K > 0 && R > 0 && S > 0 && C > 0, "pdb_weight_dgrad_layout: bad arguments");
-  PDB_DISPATCH_16(dtype, T, (weight_dgrad_kernel<T><<<ew_grid((int64_t)K * R * S * C), 256, 0, ST>>>((const T*)w, (T*)wt,
+  PDB_DISPATCH_ACT(dtype, T, (weight_dgrad_kernel<T><<<ew_grid((int64_t)K * R * S * C), 256, 0, ST>>>((const T*)w, (T*)wt,
                                                                                                       K, R, S, C)));
   PDB_LAUNCH_CHECK();
   return 0;
@@ -447,7 +444,7 @@ extern "C" int pdb_weight_dgrad_layout(const void* w, void* wt, int dtype, int K
 extern "C" int pdb_pad_rows16(const void* src, void* dst, int dtype, int rows, int cols_src, int cols_dst,
                               void* stream) {
   PDB_CHECK_ARG(src && dst && rows > 0 && cols_src > 0 && cols_dst >= cols_src, "pdb_pad_rows16: bad arguments");
-  PDB_DISPATCH_16(dtype, T, (pad_rows_kernel<T><<<ew_grid((int64_t)rows * cols_dst), 256, 0, ST>>>(
+  PDB_DISPATCH_ACT(dtype, T, (pad_rows_kernel<T><<<ew_grid((int64_t)rows * cols_dst), 256, 0, ST>>>(
                                 (const T*)src, (T*)dst, rows, cols_src, cols_dst)));
   PDB_LAUNCH_CHECK();
   return 0;
@@ -455,7 +452,7 @@ extern "C" int pdb_pad_rows16(const void* src, void* dst, int dtype, int rows, i
 
 extern "C" int pdb_colsum16(const void* a, float* out, int dtype, int rows, int cols, void* stream) {
   PDB_CHECK_ARG(a && out && rows > 0 && cols > 0, "pdb_colsum16: bad arguments");
-  PDB_DISPATCH_16(dtype, T, (colsum_kernel<T><<<(cols + 255) / 256, 256, 0, ST>>>((const T*)a, out, rows, cols)));
+  PDB_DISPATCH_ACT(dtype, T, (colsum_kernel<T><<<(cols + 255) / 256, 256, 0, ST>>>((const T*)a, out, rows, cols)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -502,7 +499,7 @@ extern "C" int pdb_weight_dgrad_layout_batched(const void* w_base, void* wt_base
                                                int dtype, void* stream) {
   PDB_CHECK_ARG(w_base && wt_base && table_dev && n > 0 && n <= 65535, "pdb_weight_dgrad_layout_batched: bad arguments");
   dim3 grid(512, n);          // the largest layers have ~2,300 tiles: enough blocks that none walks more than a few
-  PDB_DISPATCH_16(dtype, T, (weight_dgrad_batched_kernel<T><<<grid, 256, 0, ST>>>((const T*)w_base, (T*)wt_base, table_dev)));
+  PDB_DISPATCH_ACT(dtype, T, (weight_dgrad_batched_kernel<T><<<grid, 256, 0, ST>>>((const T*)w_base, (T*)wt_base, table_dev)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -510,14 +507,14 @@ extern "C" int pdb_weight_dgrad_layout_batched(const void* w_base, void* wt_base
 extern "C" int pdb_stem_s2d(const float* x, void* xs, int dtype, int N, int H, int W, void* stream) {
   PDB_CHECK_ARG(x && xs && N > 0 && H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0, "pdb_stem_s2d: H and W must be even");
   PDB_CHECK_ARG((reinterpret_cast<uintptr_t>(x) & 7) == 0, "pdb_stem_s2d: input must be 8-byte aligned");
-  PDB_DISPATCH_16(dtype, T, (stem_s2d_kernel<T><<<N * (H / 2), 128, 0, ST>>>(x, (T*)xs, H, W)));
+  PDB_DISPATCH_ACT(dtype, T, (stem_s2d_kernel<T><<<N * (H / 2), 128, 0, ST>>>(x, (T*)xs, H, W)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int pdb_stem_weight_s2d(const void* w, void* ws, int dtype, int K, void* stream) {
   PDB_CHECK_ARG(w && ws && K > 0, "pdb_stem_weight_s2d: bad arguments");
-  PDB_DISPATCH_16(dtype, T, (stem_weight_s2d_kernel<T><<<(K * 256 + 255) / 256, 256, 0, ST>>>((const T*)w, (T*)ws, K)));
+  PDB_DISPATCH_ACT(dtype, T, (stem_weight_s2d_kernel<T><<<(K * 256 + 255) / 256, 256, 0, ST>>>((const T*)w, (T*)ws, K)));
   PDB_LAUNCH_CHECK();
   return 0;
 }

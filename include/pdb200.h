@@ -4,8 +4,11 @@
  *   - every entry point returns 0 on success, non-zero on failure; pdb_last_error() then gives a
  *     human-readable message (thread-local);
  *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises;
- *   - activations are NHWC ("channels last") 16-bit, `dtype` selects the 16-bit format
- *     (PDB_BF16 / PDB_FP16); statistics, master weights, gradients and the loss are fp32;
+ *   - activations are NHWC ("channels last"); `dtype` selects their storage format: PDB_BF16 / PDB_FP16
+ *     (16-bit, the amp mode) or PDB_FP32 (fp32 storage; the GEMMs then run tcgen05 kind::tf32, which is what
+ *     the reference's three fp32 scripts get from cuDNN's TF32 default).  "16" in an entry point's name is
+ *     historical: unless a comment says otherwise every activation kernel takes all three tags.  Statistics,
+ *     master weights, gradients and the loss are always fp32;
  *   - "ref:" cites the reference script that causes the delegate kernel to run, "torch:" the
  *     delegate whose behaviour is reproduced (see SURVEY.md §2.4 for the K-numbers).
  */
@@ -21,6 +24,7 @@ extern "C" {
 
 #define PDB_BF16 0
 #define PDB_FP16 1
+#define PDB_FP32 2
 
 const char* pdb_last_error(void);
 int pdb_version(void);
@@ -52,11 +56,12 @@ int pdb_cast_f32_to_16(const float* src, void* dst, int dtype, int64_t n, void* 
 
 /* ---------------------------------------------------------------------------------------------
  * K10 — fused cross-entropy forward + backward (ref:restnet_ddp.py:28; torch:nn/functional.py:3421).
- * logits [rows, classes] 16-bit; labels int64.  loss_sum += sum_i -log softmax(x_i)[y_i] / rows
- * (caller zeroes *loss beforehand); dlogits = (softmax - onehot) * grad_scale / rows, same dtype.
- * grad_scale may be null (1.0) or a device float (amp loss scale). */
+ * logits [rows, classes] in any activation dtype; labels int64.  loss_sum += sum_i -log softmax(x_i)[y_i] / rows
+ * (caller zeroes *loss beforehand); dlogits (nullable) = (softmax - onehot) * grad_scale / rows, stored as
+ * dlogits_dtype: the logits' dtype or PDB_FP32 (what the Python layer uses, so that the amp loss scale is applied
+ * before the gradient is rounded to 16 bits).  grad_scale may be null (1.0) or a device float (amp loss scale). */
 int pdb_xent_fwd_bwd(const void* logits, int dtype, const int64_t* labels, int rows, int classes,
-                     float* loss, void* dlogits, const float* grad_scale, void* stream);
+                     float* loss, void* dlogits, int dlogits_dtype, const float* grad_scale, void* stream);
 
 /* K14 — top-k hit counters (ref:restnet_ddp.py:58-60).  out[j] += #rows whose label ranks < ks[j].
  * Ties are broken by index like torch.topk(sorted=True). */

@@ -85,7 +85,10 @@ class GradScaler:
         if self._scale is None:
             self._device = self._device or device
             self._scale = torch.full((), self._init_scale, dtype=torch.float32, device=self._device)
-            self._growth_tracker = torch.zeros((), dtype=torch.int32, device=self._device)
+            # a state_dict loaded before the first scale() (every resume) parked its counter here
+            self._growth_tracker = torch.full((), int(getattr(self, "_pending_tracker", 0)), dtype=torch.int32,
+                                              device=self._device)
+            self._pending_tracker = 0
             self._found_inf = torch.zeros((), dtype=torch.float32, device=self._device)
             self._inv_scale = torch.full((), 1.0 / self._init_scale, dtype=torch.float32,
                                          device=self._device)
@@ -214,5 +217,5 @@ class GradScaler:
             self._scale.fill_(self._init_scale)
             self._inv_scale.fill_(1.0 / self._init_scale)
             self._growth_tracker.fill_(int(sd["_growth_tracker"]))
-        elif sd.get("_growth_tracker"):
-            self._pending_tracker = int(sd["_growth_tracker"])
+        else:
+            self._pending_tracker = int(sd.get("_growth_tracker", 0))

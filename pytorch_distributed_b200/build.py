@@ -26,7 +26,9 @@ INCLUDE = ROOT / "include"
 CSRC = ROOT / "csrc"
 
 NVCC_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "--use_fast_math", "-Xcompiler", "-fPIC",
+# No --use_fast_math: the numerics oracles are fp32 PyTorch, and flushing denormals to zero would eat fp16
+# loss-scaled gradients.  The hot paths name their approximate instructions explicitly (rsqrtf, exp2f, fmaf).
+NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",
               "--expt-relaxed-constexpr", "-Xptxas", "-v"]
 
 

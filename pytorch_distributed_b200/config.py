@@ -46,7 +46,7 @@ class TrainConfig:
     val_samples: int = 50_000
     max_steps: Optional[int] = None      # stop an epoch early (bench/tests)
     max_val_steps: Optional[int] = None
-    dtype: str = "auto"            # auto -> fp32 for single/dp/ddp, bf16 for ddp_amp
+    dtype: str = "auto"            # auto -> the reference's precision: fp32 (TF32 GEMMs) for single/dp/ddp, fp16 for ddp_amp
     backend: str = "auto"          # auto -> nccl/native on CUDA, gloo on CPU
     engine: str = "auto"           # auto -> native sm_100a step graph on CUDA, stock torch ops on CPU
     sync_bn: bool = False
@@ -73,24 +73,14 @@ class TrainConfig:
         return Path(self.save_path)
 
     def resolved_dtype(self) -> str:
-        """`auto`: the amp mode computes in 16 bit like the reference's autocast script.  The three fp32 scripts
-        of the reference run cuDNN convolutions in TF32 (10-bit mantissa, torch's default); on a CUDA device
-        with the sm_100a library their `auto` here is bf16 activations + fp32 master weights, gradients,
-        statistics and loss on the native step graph — pass ``--dtype fp32`` for the stock TF32 cuDNN path."""
+        """`auto` is the reference's precision for the mode: fp16 autocast for the amp script
+        (ref:resnet_ddp_apex.py:27 ``torch.cuda.amp.autocast()``), fp32 storage with TF32 tensor-core math for the
+        other three (ref:resnet_single_gpu.py:26-30 et al.: no autocast, cuDNN's TF32 default).  On a CUDA device
+        all three run on the native sm_100a step graph (``kind::f16`` / ``kind::tf32`` tcgen05 GEMMs); ``--dtype
+        bf16`` selects bf16 activations with fp32 master weights for any mode."""
         if self.dtype != "auto":
             return self.dtype
-        if self.mode == "ddp_amp":
-            return "bf16"
-        if self.engine != "torch" and self.device != "cpu" and self.width % 64 == 0:
-            try:
-                import torch
-                if torch.cuda.is_available():
-                    from . import ops
-                    if ops.available():
-                        return "bf16"
-            except Exception:
-                pass
-        return "fp32"
+        return "fp16" if self.mode == "ddp_amp" else "fp32"
 
 
 def add_arguments(p: argparse.ArgumentParser, mode: str) -> argparse.ArgumentParser:

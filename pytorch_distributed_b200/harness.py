@@ -228,13 +228,21 @@ def build_model(cfg: TrainConfig, device: torch.device) -> ResNet:
     return model.to(device)
 
 
+_TORCH_DTYPES = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp32": torch.float32}
+
+
+def torch_dtype(cfg: TrainConfig) -> torch.dtype:
+    """Activation storage dtype of the native engine for this configuration."""
+    return _TORCH_DTYPES[cfg.resolved_dtype()]
+
+
 def _want_native(cfg: TrainConfig, device: torch.device) -> bool:
     if cfg.engine == "torch" or device.type != "cuda":
         return False
     from . import ops
     if cfg.engine == "native" and not ops.available():
         raise RuntimeError("engine=native requested but lib/libpdb200.so is not built/loadable")
-    return ops.available() and cfg.resolved_dtype() in ("bf16", "fp16")
+    return ops.available() and cfg.resolved_dtype() in _TORCH_DTYPES and cfg.width % 64 == 0
 
 
 def main(cfg: TrainConfig, local_rank: int = 0) -> float:
@@ -260,8 +268,7 @@ def main(cfg: TrainConfig, local_rank: int = 0) -> float:
         n_local = cfg.gpus or (torch.cuda.device_count() if device.type == "cuda" else 2)
     per_replica_batch = cfg.batch_size
     if _want_native(cfg, device):
-        dt = torch.bfloat16 if cfg.resolved_dtype() == "bf16" else torch.float16
-        model.enable_native(batch_size=per_replica_batch, dtype=dt, sync_bn=cfg.sync_bn)
+        model.enable_native(batch_size=per_replica_batch, dtype=torch_dtype(cfg), sync_bn=cfg.sync_bn)
 
     if cfg.mode == "dp":
         ids = list(range(n_local)) if device.type == "cuda" else ["cpu"] * n_local

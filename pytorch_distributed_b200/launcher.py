@@ -55,8 +55,10 @@ def _bind_numa(local_rank: int) -> None:
                 pci = None
             if pci:
                 runtime.bind_numa_for_pci(pci)
-    except Exception:
-        pass  # affinity is an optimisation; never fail a launch over it
+    except Exception as e:
+        # affinity is an optimisation and must not fail a launch, but it must not fail silently either
+        import warnings
+        warnings.warn(f"pdb200: NUMA binding of local rank {local_rank} skipped: {type(e).__name__}: {e}")
 
 
 def _child(fn: Callable, i: int, args: Sequence, error_file: str, bind_numa: bool) -> None:

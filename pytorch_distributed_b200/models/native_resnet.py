@@ -45,7 +45,7 @@ class _ConvPlan:
         self.R, self.S = conv.kernel_size
         self.stride, self.pad = conv.stride[0], conv.padding[0]
         self.pindex = eng.pindex[name + ".weight"]
-        self.w16 = eng.arena.shadow_view(name + ".weight")                  # [K, R, S, C] 16-bit
+        self.w16 = eng._weights_view(name + ".weight")          # [K, R, S, C] in the compute dtype (fp32: the master)
         self.dw = eng.arena.grads[eng.arena.by_name[name + ".weight"].offset:][: self.K * self.R * self.S * self.C]
         self.w_off = eng.arena.by_name[name + ".weight"].offset
         self.wt16 = None                      # slice of the engine's flat dgrad-weight buffer (set later)
@@ -134,13 +134,19 @@ class NativeResNetEngine:
             raise RuntimeError("the native engine needs the model on a CUDA device")
         if model.width % 64 != 0:
             raise RuntimeError(f"the tcgen05 conv path needs channel counts that are multiples of 64 (width={model.width})")
-        if dtype not in (torch.bfloat16, torch.float16):
-            raise RuntimeError("native engine compute dtype must be bf16 or fp16")
+        if dtype not in (torch.bfloat16, torch.float16, torch.float32):
+            raise RuntimeError("native engine compute dtype must be bf16, fp16 or fp32 (TF32 tensor-core math)")
         self.model, self.batch_size, self.dtype, self.sync_bn = model, batch_size, dtype, sync_bn
         self.device = p0.device
         self.arena: ParamArena = getattr(model, "_pdb200_arena", None) or ParamArena(model, self.device)
         self.buffers: BufferArena = getattr(model, "_pdb200_buffer_arena", None) or BufferArena(model, self.device)
-        self.arena.ensure_shadow(dtype)
+        # GEMM operand source: the 16-bit shadow of the weights, or — fp32 storage / TF32 math — the master weights
+        # themselves (already [Cout, kh, kw, Cin] in the arena; no copy, nothing to refresh after an optimizer step)
+        if dtype == torch.float32:
+            self.arena.shadow = None
+            self._wsrc = self.arena.params
+        else:
+            self._wsrc = self.arena.ensure_shadow(dtype)
         self.pindex: Dict[str, int] = {e.name: i for i, e in enumerate(self.arena.entries)}
         self._stat_floats = 0
         self._scratch_floats = 0
@@ -150,6 +156,9 @@ class NativeResNetEngine:
         # it is captured and replayed like every other launch; with a torch.distributed fallback exchange the capture
         # aborts (see _sync_stats) and the step stays eager.
         self.graphs = os.environ.get("PDB200_GRAPHS", "1") != "0"
+        # A failed capture is an error unless PDB200_GRAPHS_FALLBACK=1 asks for "warn and stay eager": a silent
+        # fallback would quietly turn a 20-launch step into a 350-launch one.
+        self.graphs_fallback = os.environ.get("PDB200_GRAPHS_FALLBACK", "0") == "1"
         self.graph_warmup = 2                     # eager steps per shape before capture
         self._plans: Dict[tuple, _StepPlan] = {}
         self._plan: Optional[_StepPlan] = None
@@ -162,7 +171,8 @@ class NativeResNetEngine:
         # The standard 7x7/2 stem runs as a 4x4/1 convolution over the space-to-depth input, fed by TMA im2col loads
         # (no patch matrix); any other stem geometry goes through the explicit im2col matrix.
         c1 = self.stem_conv
-        self.stem_s2d = (c1.R, c1.S, c1.stride, c1.pad, c1.C, c1.K) == (7, 7, 2, 3, 3, 64)
+        # (16-bit only: the tf32 instantiation of the stem goes through the explicit patch matrix)
+        self.stem_s2d = (c1.R, c1.S, c1.stride, c1.pad, c1.C, c1.K) == (7, 7, 2, 3, 3, 64) and dtype != torch.float32
         self.stem_ws = torch.zeros(64, 256, dtype=dtype, device=self.device)
         self.stem_dws = torch.zeros(64, 256, dtype=torch.float32, device=self.device)
         self.blocks: List[_BlockPlan] = []
@@ -172,7 +182,7 @@ class NativeResNetEngine:
                 self.blocks.append(_BlockPlan(f"layer{li}.{bi}", block, self))
         fc = model.fc
         self.fc_K, self.fc_C = fc.out_features, fc.in_features
-        self.fc_w16 = self.arena.shadow_view("fc.weight")
+        self.fc_w16 = self._weights_view("fc.weight")
         self.fc_bias = self.arena.param_view("fc.bias")
         e = self.arena.by_name["fc.weight"]
         self.fc_dw = self.arena.grads[e.offset: e.offset + e.numel]
@@ -202,6 +212,10 @@ class NativeResNetEngine:
         self._wt_table = torch.tensor(table, dtype=torch.int64, device=self.device)
 
     # -- plan construction -------------------------------------------------------------------------
+    def _weights_view(self, name: str) -> torch.Tensor:
+        e = self.arena.by_name[name]
+        return self._wsrc[e.offset: e.offset + e.numel]
+
     def _conv(self, name: str, conv: nn.Conv2d) -> _ConvPlan:
         return _ConvPlan(name, conv, self)
 
@@ -212,6 +226,10 @@ class NativeResNetEngine:
 
     def attach_ddp(self, ddp) -> None:
         self.ddp = ddp
+        if self.sync_bn and getattr(ddp, "world_size", 1) > 1 and not hasattr(getattr(ddp, "comm", None), "allreduce_small_"):
+            # SyncBN statistics would go through torch.distributed calls (explicit --backend nccl): those are not
+            # capturable, so this configuration runs the step eagerly — decided here, not discovered by a failed capture
+            self.graphs = False
 
     def _ready(self, *indices: int) -> None:
         if self._ready_log is not None:           # capturing: remember, tell DDP when the segment is replayed
@@ -269,7 +287,7 @@ class NativeResNetEngine:
             ops.stem_weight_s2d(c.w16, self.stem_ws)
         ops.pad_rows16(c.w16, self.stem_w16, c.K, c.R * c.S * c.C, STEM_KPAD)
         if need_dgrad:
-            ops.weight_dgrad_layout_batched(self.arena.shadow, self.wt_all, self._wt_table, self._wt_table.shape[0])
+            ops.weight_dgrad_layout_batched(self._wsrc, self.wt_all, self._wt_table, self._wt_table.shape[0])
 
     def _fwd_scratch(self, bn: _BNPlan) -> torch.Tensor:
         r0 = self._stat_floats + bn.rslot
@@ -397,7 +415,10 @@ class NativeResNetEngine:
                         plan.logits, plan.saved = self._forward_impl(plan.x_static)
                         plan.fwd_end = plan.cursor
                     plan.fwd_graph = self._capture(fwd)
-                except Exception as e:            # capture is an optimisation: fall back to eager launches
+                except Exception as e:
+                    if not self.graphs_fallback:
+                        raise RuntimeError("pdb200: CUDA-graph capture of the forward pass failed (set PDB200_GRAPHS=0 "
+                                           f"to run eagerly, PDB200_GRAPHS_FALLBACK=1 to fall back): {e}") from e
                     import warnings
                     warnings.warn(f"pdb200: CUDA-graph capture of the forward pass failed, staying eager: {e}")
                     plan.fwd_graph, plan.graphs_failed = None, True
@@ -556,6 +577,9 @@ class NativeResNetEngine:
                         graphs.append((g, tuple(self._ready_log)))
                     plan.bwd_graphs = graphs
                 except Exception as e:
+                    if not self.graphs_fallback:
+                        raise RuntimeError("pdb200: CUDA-graph capture of the backward pass failed (set PDB200_GRAPHS=0 "
+                                           f"to run eagerly, PDB200_GRAPHS_FALLBACK=1 to fall back): {e}") from e
                     import warnings
                     warnings.warn(f"pdb200: CUDA-graph capture of the backward pass failed, staying eager: {e}")
                     plan.bwd_graphs, plan.graphs_failed = None, True

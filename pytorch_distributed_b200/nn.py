@@ -17,20 +17,21 @@ class _FusedXent(torch.autograd.Function):
     @staticmethod
     def forward(ctx, logits, labels):
         from . import ops
-        loss, dlogits = ops.xent_fwd_bwd(logits, labels)
+        loss, dlogits = ops.xent_fwd_bwd(logits, labels)          # dlogits: fp32 (softmax - onehot)/B
         ctx.save_for_backward(dlogits)
+        ctx.logits_dtype = logits.dtype
         return loss
 
     @staticmethod
     def backward(ctx, g):
         (dlogits,) = ctx.saved_tensors
-        # dlogits already holds (softmax - onehot)/B in the logits dtype; g carries the loss scale
-        return dlogits * g.to(dlogits.dtype), None
+        # g carries the amp loss scale (65536 does not even fit fp16): multiply in fp32, round once afterwards
+        return (dlogits * g.float()).to(ctx.logits_dtype), None
 
 
 class CrossEntropyLoss(nn.Module):
     def forward(self, logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
-        if logits.is_cuda and logits.dim() == 2:
+        if logits.is_cuda and logits.dim() == 2 and logits.dtype in (torch.bfloat16, torch.float16, torch.float32):
             from . import ops
             if ops.available():
                 return _FusedXent.apply(logits, labels)

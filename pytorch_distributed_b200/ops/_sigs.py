@@ -22,7 +22,7 @@ def declare(L):
     sig("pdb_check_finite", [P, c_int64, P, P])
     sig("pdb_scaler_update", [P, P, P, P, c_float, c_float, c_int, P])
     sig("pdb_cast_f32_to_16", [P, P, c_int, c_int64, P])
-    sig("pdb_xent_fwd_bwd", [P, c_int, P, c_int, c_int, P, P, P, P])
+    sig("pdb_xent_fwd_bwd", [P, c_int, P, c_int, c_int, P, P, c_int, P, P])
     sig("pdb_topk_correct", [P, c_int, P, c_int, c_int, P, c_int, P, P])
     sig("pdb_bn_stats_scratch_bytes", [c_int], c_size_t)
     sig("pdb_bn_stats", [P, c_int, c_int64, c_int, P, P, c_size_t, P])

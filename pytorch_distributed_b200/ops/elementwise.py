@@ -17,14 +17,14 @@ __all__ = ["dtype_tag", "sgd_step", "check_finite", "scaler_update", "cast_to_16
            "add_strided2", "conv_fprop", "conv_wgrad", "weight_dgrad_layout", "weight_dgrad_layout_batched", "pad_rows16", "colsum16",
            "peer_copy", "peer_copy_", "reduce_to_root", "ConvShape"]
 
-_TAG = {torch.bfloat16: 0, torch.float16: 1}
+_TAG = {torch.bfloat16: 0, torch.float16: 1, torch.float32: 2}
 
 
 def dtype_tag(dt: torch.dtype) -> int:
     try:
         return _TAG[dt]
     except KeyError:
-        raise TypeError(f"native kernels take bf16/fp16 activations, got {dt}") from None
+        raise TypeError(f"native kernels take bf16/fp16/fp32 activations, got {dt}") from None
 
 
 def _st(t: torch.Tensor):
@@ -61,13 +61,17 @@ def cast_to_16(src: torch.Tensor, dst: torch.Tensor) -> None:
 
 
 def xent_fwd_bwd(logits: torch.Tensor, labels: torch.Tensor, grad_scale: Optional[torch.Tensor] = None,
-                 need_grad: bool = True) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+                 need_grad: bool = True, grad_dtype: Optional[torch.dtype] = torch.float32
+                 ) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """Mean cross-entropy and its gradient.  The gradient comes back in fp32 unless ``grad_dtype`` asks for the
+    logits' own dtype: the amp loss scale must be applied before the rounding to 16 bits, not after."""
     logits = logits.contiguous()
     rows, classes = logits.shape
     loss = torch.zeros((), dtype=torch.float32, device=logits.device)
-    dl = torch.empty_like(logits) if need_grad else None
+    dl = torch.empty(logits.shape, dtype=grad_dtype or logits.dtype, device=logits.device) if need_grad else None
     check(require().pdb_xent_fwd_bwd(ptr(logits), dtype_tag(logits.dtype), ptr(labels), rows, classes, ptr(loss),
-                                     ptr(dl), ptr(grad_scale), _st(logits)), "pdb_xent_fwd_bwd")
+                                     ptr(dl), dtype_tag(dl.dtype) if dl is not None else 0, ptr(grad_scale),
+                                     _st(logits)), "pdb_xent_fwd_bwd")
     count_launch()
     return loss, dl
 
@@ -78,7 +82,7 @@ _ks_cache = {}
 def topk_correct(logits: torch.Tensor, labels: torch.Tensor, ks: Sequence[int] = (1, 5)) -> torch.Tensor:
     logits = logits.contiguous()
     if logits.dtype not in _TAG:
-        logits = logits.to(torch.bfloat16)
+        logits = logits.float()
     key = (tuple(ks), logits.device)
     if key not in _ks_cache:
         _ks_cache[key] = torch.tensor(list(ks), dtype=torch.int32, device=logits.device)

@@ -47,10 +47,16 @@ class SGD(Optimizer):
         ps = [p for g in self.param_groups for p in g["params"]]
         if not ps or len(self.param_groups) != 1:
             return None
-        base = ps[0].untyped_storage().data_ptr()
-        if any(p.untyped_storage().data_ptr() != base for p in ps):
+        arena = getattr(ps[0], "_pdb200_arena", None)
+        if arena is None:
             return None
-        return getattr(ps[0], "_pdb200_arena", None)
+        # The fused step walks the WHOLE flat arena, so it is only valid when this optimizer was given exactly the
+        # arena's parameters and all of them train; SGD(model.fc.parameters()) or a frozen layer takes the
+        # per-tensor path and touches nothing else (torch.optim.SGD semantics).
+        own = arena.parameters()
+        if len(ps) != len(own) or {id(p) for p in ps} != {id(p) for p in own} or not all(p.requires_grad for p in own):
+            return None
+        return arena
 
     # -- grads ---------------------------------------------------------------------
     def zero_grad(self, set_to_none: bool = True) -> None:

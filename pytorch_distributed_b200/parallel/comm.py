@@ -128,7 +128,11 @@ _active_native = None        # the NativeComm of the default group, once one exi
 
 
 def make_comm(backend: str = "auto", group=None):
-    """auto: native on multi-GPU CUDA with symmetric memory available, else torch."""
+    """auto: the native peer-memory backend on multi-GPU CUDA, torch.distributed on CPU / single rank.
+
+    On a multi-GPU CUDA job a failure to bring up the native backend is an ERROR, not a quiet switch to NCCL:
+    ask for the library path explicitly (``backend='nccl'``) or set ``PDB200_ALLOW_NCCL_FALLBACK=1``."""
+    import os
     if backend in ("nccl", "gloo", "torch"):
         return TorchComm(group)
     want_native = backend == "native"
@@ -143,9 +147,14 @@ def make_comm(backend: str = "auto", group=None):
             if group is None:
                 _active_native = c
             return c
-        except Exception:
-            if want_native:
-                raise
+        except Exception as e:
+            if want_native or os.environ.get("PDB200_ALLOW_NCCL_FALLBACK", "0") != "1":
+                raise RuntimeError(
+                    f"the native peer-memory communication backend could not be initialised ({type(e).__name__}: {e}); "
+                    "pass backend='nccl' (--backend nccl) or set PDB200_ALLOW_NCCL_FALLBACK=1 to run on "
+                    "torch.distributed instead") from e
+            import warnings
+            warnings.warn(f"pdb200: native comm backend unavailable ({type(e).__name__}: {e}); using torch.distributed")
     elif want_native and is_initialized() and dist.get_world_size(group) > 1:
         raise RuntimeError("backend='native' needs CUDA + an NCCL process group for the bootstrap")
     return TorchComm(group)

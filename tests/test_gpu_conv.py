@@ -27,6 +27,59 @@ def test_fprop(case):
     assert e_y < TOL and e_s < 1e-3, (e_y, e_s)
 
 
+# fp32 storage, kind::tf32 MMAs (10-bit mantissa operands, rounded to nearest by the TMA load), fp32 accumulate and output
+TOL_TF32 = 2e-3
+
+
+@pytest.mark.parametrize("case", [
+    (2, 16, 16, 64, 64, 1, 1, 1, 0, 64), (2, 16, 16, 128, 256, 1, 1, 1, 0, 256), (2, 16, 16, 64, 128, 1, 1, 1, 0, 128),
+    (3, 14, 14, 256, 1024, 1, 1, 1, 0, 256), (2, 56, 56, 64, 64, 3, 3, 1, 1, 64),
+    (2, 28, 28, 128, 128, 3, 3, 1, 1, 128), (2, 56, 56, 128, 128, 3, 3, 2, 1, 128),
+    (2, 56, 56, 256, 512, 1, 1, 2, 0, 256), (5, 7, 7, 512, 512, 3, 3, 1, 1, 256),
+    (400, 1, 1, 2048, 1000, 1, 1, 1, 0, 128), (2, 112, 112, 152, 64, 1, 1, 1, 0, 64),
+    (3, 14, 14, 256, 1024, 1, 1, 1, 0, 512), (3, 14, 14, 256, 256, 3, 3, 1, 1, 512),
+    (80, 14, 14, 512, 2048, 1, 1, 1, 0, 0),
+])
+def test_fprop_tf32(case):
+    N, H, W, C, K, R, S, stride, pad, bn = case
+    e_y, e_s = conv_case(N, H, W, C, K, R, S, stride, pad, block_n=bn, dtype=torch.float32)
+    assert e_y < TOL_TF32 and e_s < 1e-4, (e_y, e_s)
+
+
+@pytest.mark.parametrize("case", [(2, 28, 28, 128, 128, 3, 3, 1), (2, 14, 14, 256, 1024, 1, 1, 0), (400, 1, 1, 2048, 1000, 1, 1, 0)])
+def test_dgrad_tf32(case):
+    assert dgrad_case(*case, dtype=torch.float32) < TOL_TF32
+
+
+@pytest.mark.parametrize("case", [
+    (2, 16, 16, 64, 64, 1, 1, 1, 0, 64), (2, 28, 28, 64, 64, 3, 3, 1, 1, 256), (2, 16, 16, 64, 128, 1, 1, 1, 0, 128),
+    (2, 28, 28, 128, 256, 3, 3, 1, 1, 256), (2, 56, 56, 128, 128, 3, 3, 2, 1, 256),
+    (2, 56, 56, 256, 512, 1, 1, 2, 0, 256), (400, 1, 1, 2048, 1000, 1, 1, 1, 0, 256),
+    (2, 112, 112, 152, 64, 1, 1, 1, 0, 256),          # the explicit stem patch matrix (K = 147 padded to 152)
+])
+def test_wgrad_tf32(case):
+    """MN-major fp32 operands: TMA 128B swizzle with 32-byte atoms, descriptor layout SWIZZLE_128B_BASE32B."""
+    N, H, W, C, K, R, S, stride, pad, bn = case
+    assert wgrad_case(N, H, W, C, K, R, S, stride, pad, block_n=bn, dtype=torch.float32) < TOL_TF32
+
+
+def test_fprop_accumulate_epilogue_tf32():
+    import torch.nn.functional as F  # noqa: F401
+    from pytorch_distributed_b200 import ops
+    from pytorch_distributed_b200.ops import ConvShape
+    from ._gpu_helpers import rel_err
+    g = torch.Generator(device="cuda").manual_seed(7)
+    N, H, C, K = 3, 14, 256, 1024
+    x = torch.randn(N, H, H, C, device="cuda", generator=g)
+    w = torch.randn(K, 1, 1, C, device="cuda", generator=g) / C ** 0.5
+    y0 = torch.randn(N, H, H, K, device="cuda", generator=g)
+    y = y0.clone()
+    ops.conv_fprop(x, w, y, ConvShape(N, H, H, C, K, 1, 1, 1, 0), accumulate=True)
+    torch.cuda.synchronize()
+    ref = y0 + (x.reshape(-1, C).double() @ w.reshape(K, C).double().t()).float().reshape(N, H, H, K)
+    assert rel_err(y, ref) < TOL_TF32
+
+
 def test_fprop_fp16():
     e_y, e_s = conv_case(2, 28, 28, 128, 128, 3, 3, 1, 1, dtype=torch.float16)
     assert e_y < 3e-3 and e_s < 1e-3

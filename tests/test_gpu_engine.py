@@ -123,3 +123,71 @@ def test_training_steps_match_torch_engine():
     assert abs(losses[0][1] - losses[1][1]) < 0.08 * losses[1][1]
     # both engines fit the fixed batch at a similar pace
     assert losses[0][-1] < losses[0][0] and abs(losses[0][-1] - losses[1][-1]) < 0.25 * losses[1][0], losses
+
+
+def test_tf32_engine_matches_fp32_model():
+    """fp32 storage + kind::tf32 GEMMs (what `single` / `dp` / `ddp` run by default) against the stock model in true
+    fp32; yardstick = the stock model with cuDNN/cuBLAS TF32 enabled, i.e. what the reference's fp32 scripts execute."""
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref = resnet50().to(dev)
+    ours = copy.deepcopy(ref)
+    ours.enable_native(batch_size=16, dtype=torch.float32)
+    assert ours._pdb200_arena.shadow is None          # the master weights ARE the GEMM operands
+    x = torch.randn(16, 3, 96, 96, device=dev)
+    y = torch.randint(0, 1000, (16,), device=dev)
+    ref.train()
+    out_ref = ref(x)
+    loss_ref = F.cross_entropy(out_ref, y)
+    loss_ref.backward()
+    ours.train()
+    out = ours(x)
+    assert out.dtype == torch.float32
+    loss = CrossEntropyLoss()(out, y)
+    loss.backward()
+    yard = copy.deepcopy(ref)
+    for p in yard.parameters():
+        p.grad = None
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        out_y = yard(x)
+        F.cross_entropy(out_y, y).backward()
+    finally:
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+    torch.cuda.synchronize()
+    cos_out, cos_yard = _cos(out, out_ref), _cos(out_y, out_ref)
+    print(f"[tf32] logits cos: ours {cos_out:.6f}  stock-tf32 {cos_yard:.6f}; loss ours {float(loss):.5f} fp32 {float(loss_ref):.5f}")
+    assert cos_out > min(0.9995, cos_yard - 1e-3), (cos_out, cos_yard)
+    assert abs(float(loss) - float(loss_ref)) < 5e-3 * abs(float(loss_ref))
+    ga, gr, gy = [], [], []
+    for (n, p), q, r in zip(ours.named_parameters(), ref.parameters(), yard.parameters()):
+        c, cy = _cos(p.grad, q.grad), _cos(r.grad, q.grad)
+        if cy > 0.9:
+            assert c > cy - 0.03, (n, c, cy)
+            rel = float(p.grad.norm() / (q.grad.norm() + 1e-20))
+            assert 0.9 < rel < 1.1, (n, rel)
+        ga.append(p.grad.flatten()), gr.append(q.grad.flatten()), gy.append(r.grad.flatten())
+    ga, gr, gy = torch.cat(ga), torch.cat(gr), torch.cat(gy)
+    print(f"[tf32] whole-gradient cos: ours {_cos(ga, gr):.5f}  stock-tf32 {_cos(gy, gr):.5f}")
+    assert _cos(ga, gr) > min(0.995, _cos(gy, gr) - 0.01)
+    for (n, b), c in zip(ours.named_buffers(), ref.buffers()):
+        if b.is_floating_point():
+            assert _cos(b, c) > 0.9999 and 0.99 < float(b.norm() / c.norm()) < 1.01, n
+    ours.eval(), ref.eval()
+    with torch.no_grad():
+        assert _cos(ours(x), ref(x)) > 0.9995
+
+
+@pytest.mark.parametrize("engine", ["native", "torch"])
+def test_fp32_single_mode_trains_through_the_harness(engine, tmp_path):
+    """`resnet_single_gpu.py` with no flags = fp32: on the native engine (TF32 GEMMs) and on the stock-op engine
+    (fp32 logits into the fused loss — used to raise a TypeError)."""
+    cfg = TrainConfig(mode="single", batch_size=8, epochs=1, max_steps=3, max_val_steps=1, image_size=64,
+                      train_samples=64, val_samples=16, engine=engine, device="cuda", save_path=str(tmp_path))
+    assert cfg.resolved_dtype() == "fp32"
+    acc = harness.main(cfg)
+    assert 0.0 <= acc <= 1.0

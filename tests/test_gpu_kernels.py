@@ -10,7 +10,7 @@ from pytorch_distributed_b200.optim.sgd import _flat_sgd  # noqa: E402
 
 from ._gpu_helpers import rel_err  # noqa: E402
 
-DT = [torch.bfloat16, torch.float16]
+DT = [torch.bfloat16, torch.float16, torch.float32]      # fp32 storage = the TF32 path of the three fp32 modes
 
 
 def test_library_loaded():
@@ -72,6 +72,38 @@ def test_xent_and_topk(dt):
     _, pred = logits.float().topk(5, -1, True, True)
     eq = pred.eq(labels[:, None])
     assert hits.tolist() == [float(eq[:, :1].sum()), float(eq.sum())]
+
+
+def test_fused_xent_survives_the_initial_amp_scale():
+    """fp16 logits, GradScaler's initial scale 65536 (does not fit fp16) and batch 400: the gradient must come out
+    finite and un-flushed — the loss scale is applied in fp32, before the rounding to 16 bits."""
+    from pytorch_distributed_b200.nn import CrossEntropyLoss
+    g = torch.Generator(device="cuda").manual_seed(11)
+    logits = (torch.randn(400, 1000, device="cuda", generator=g) * 4).half().requires_grad_(True)
+    labels = torch.randint(0, 1000, (400,), device="cuda", generator=g)
+    scale = torch.tensor(65536.0, device="cuda")
+    (CrossEntropyLoss()(logits, labels) * scale).backward()
+    ref_in = logits.detach().float().requires_grad_(True)
+    (F.cross_entropy(ref_in, labels) * 65536.0).backward()
+    assert logits.grad.dtype == torch.float16 and bool(torch.isfinite(logits.grad).all())
+    assert rel_err(logits.grad, ref_in.grad) < 2e-3
+    # entries that (softmax - onehot)/400 alone would flush to zero in fp16 (< 6e-8) survive with the scale applied first
+    tiny = (ref_in.grad.abs() / 65536.0 < 5.9e-8) & (ref_in.grad.abs() > 6.2e-5)
+    assert int(tiny.sum()) > 0 and bool((logits.grad[tiny] != 0).all())
+
+
+def test_fused_xent_takes_fp32_logits():
+    from pytorch_distributed_b200.nn import CrossEntropyLoss
+    g = torch.Generator(device="cuda").manual_seed(12)
+    logits = (torch.randn(64, 1000, device="cuda", generator=g) * 3).requires_grad_(True)
+    labels = torch.randint(0, 1000, (64,), device="cuda", generator=g)
+    loss = CrossEntropyLoss()(logits, labels)
+    loss.backward()
+    ref_in = logits.detach().clone().requires_grad_(True)
+    ref = F.cross_entropy(ref_in, labels)
+    ref.backward()
+    assert abs(float(loss) - float(ref)) < 1e-5 * abs(float(ref)) + 1e-6
+    assert rel_err(logits.grad, ref_in.grad) < 1e-5
 
 
 @pytest.mark.parametrize("dt", DT)

@@ -104,3 +104,43 @@ def test_grad_scaler_unscale_value():
     opt_ref.step()
     for p, q in zip(m.parameters(), ref.parameters()):
         assert torch.allclose(p, q, rtol=1e-4, atol=1e-6)
+
+
+def test_sgd_on_a_subset_of_an_arena_touches_nothing_else():
+    """SGD(model.fc.parameters()) on an arena-backed model must behave like torch.optim.SGD: the fused whole-arena
+    step is only taken when the optimizer owns every parameter of the arena."""
+    import torch
+    from pytorch_distributed_b200.optim import SGD
+    from pytorch_distributed_b200.utils.arena import ParamArena
+    torch.manual_seed(0)
+    m = torch.nn.Sequential(torch.nn.Linear(8, 8), torch.nn.Linear(8, 4))
+    ParamArena(m, torch.device("cpu"))
+    opt = SGD(m[1].parameters(), lr=0.1, momentum=0.9, weight_decay=0.1)
+    assert opt.arena is None
+    before0 = m[0].weight.detach().clone()
+    before1 = m[1].weight.detach().clone()
+    m(torch.randn(2, 8)).sum().backward()
+    opt.step()
+    assert torch.equal(m[0].weight, before0) and not torch.equal(m[1].weight, before1)
+    full = SGD(m.parameters(), lr=0.1)
+    assert full.arena is m._pdb200_arena
+    m[0].bias.requires_grad_(False)
+    assert SGD(m.parameters(), lr=0.1).arena is None          # a frozen parameter: no whole-arena step either
+
+
+def test_grad_scaler_resume_keeps_the_growth_counter():
+    """save -> new scaler -> load (before the first scale(), as harness.main does) -> the tracker survives."""
+    import torch
+    from pytorch_distributed_b200 import amp
+    a = amp.GradScaler(init_scale=256.0, growth_interval=5)
+    a.scale(torch.ones(()))
+    for _ in range(3):
+        a.update()
+    sd = a.state_dict()
+    assert sd["_growth_tracker"] == 3
+    b = amp.GradScaler()
+    b.load_state_dict(sd)
+    b.scale(torch.ones(()))                                    # lazy init happens here
+    assert b.state_dict()["_growth_tracker"] == 3 and b.get_scale() == 256.0
+    b.update(), b.update()
+    assert b.get_scale() == 512.0                              # grows on schedule, as the uninterrupted run would
