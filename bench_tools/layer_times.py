@@ -26,11 +26,12 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=400)
     ap.add_argument("--out", default="gpurun_out/layer_times.json")
+    ap.add_argument("--dtype", choices=("bf16", "fp16", "fp32"), default="bf16")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
-    cfg = TrainConfig(mode="ddp_amp", batch_size=args.batch, dtype="bf16", device="cuda")
+    cfg = TrainConfig(mode="ddp_amp" if args.dtype != "fp32" else "single", batch_size=args.batch, dtype=args.dtype, device="cuda")
     model = harness.build_model(cfg, dev)
-    model.enable_native(batch_size=args.batch, dtype=torch.bfloat16)
+    model.enable_native(batch_size=args.batch, dtype=harness.torch_dtype(cfg))
     opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
     sc = amp.GradScaler(device=dev)
     crit = CrossEntropyLoss()
@@ -62,8 +63,8 @@ def main():
                     t = a[2] if name in ("bn_bwd_reduce", "bn_bwd_apply") else a[0]
                     tag = f"{name} {tuple(t.shape)}" + (" +res" if name == "bn_apply" and a[1] is not None else "") \
                         + (" +dres" if name == "bn_bwd_apply" and a[4] is not None else "")
-                    # bytes moved (16-bit streams): for a GB/s column
-                    n = t.numel()
+                    # bytes moved per activation stream: for a GB/s column
+                    n = t.numel() * t.element_size() // 2
                     streams = {"bn_apply": 2 + (a[1] is not None), "bn_bwd_reduce": 2.06,
                                "bn_bwd_apply": 3.06 + (a[4] is not None if name == "bn_bwd_apply" else 0)}.get(name, 0)
                     flops = -2.0 * n * streams          # negative => bytes, reported as GB/s
