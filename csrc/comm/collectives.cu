@@ -13,9 +13,13 @@
 // in place on the gradients, so DDP needs no bucket copies at all.  With a multicast mapping the
 // reduce-scatter is a single `multimem.ld_reduce` per 16 bytes: the NVSwitch adds the eight copies.
 //
-// Cross-GPU synchronisation: one 32-bit slot per (block, peer) in the symmetric signal pad; release/acquire
-// CAS at system scope (the protocol of torch's CUDASymmetricMemory sync_remote_blocks, re-implemented).
+// Cross-GPU synchronisation: one 32-bit slot per (block, peer) in the symmetric signal pad, used as a monotonic
+// meeting counter (comm/peer_sync.cuh): a meeting costs one one-way release store per peer plus a local spin.
 // Every spin is bounded by the global timer and traps instead of hanging the box.
+//
+// Algorithm per payload size (chosen by the caller, parallel/symm.py): up to 256 KB the ONE-SHOT kernel (every rank
+// reads every copy and keeps the sum: one NVLink latency, no all-gather), above it the two-shot kernel (reduce-scatter
+// + all-gather, through the NVLS multicast address when there is one).
 #include "common.cuh"
 #include "comm/peer_sync.cuh"
 
@@ -266,23 +270,57 @@ __global__ void __launch_bounds__(kCommThreads) broadcast_kernel(PeerPtrs pp, in
   cross_rank_barrier(pp.pad, rank, world);            // root may overwrite its copy only after everyone has read it
 }
 
-// One-shot all-reduce for tiny payloads (SyncBN statistics, metric vectors): every rank pushes its n floats
-// into slot [rank] of every peer's staging buffer, then sums the `world` slots locally.  Single block.
-// staging layout per rank: float[world][n_max].
-__global__ void __launch_bounds__(1024) small_allreduce_kernel(PeerPtrs pp, int rank, int world, float* __restrict__ data,
-                                                               int n, int slot_stride) {
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    const float v = data[i];
-    for (int p = 0; p < world; ++p) pp.buf[p][(int64_t)rank * slot_stride + i] = v;
-  }
-  __threadfence_system();
+// One-shot IN-PLACE all-reduce of a small range (gradient buckets up to 256 KB: shrunken models, generic modules):
+// meet, every rank reads all `world` copies and adds them in rank order (so every rank holds bit-identical sums and
+// the non-finite verdict is the same everywhere without a flag exchange), meet again (nobody may overwrite a copy
+// that a peer is still reading), write the local copy.  The whole range lives in registers between the two
+// meetings: gridDim.x * blockDim.x * kOneShotUnroll float4 must cover it (the launcher sizes the grid).
+constexpr int kOneShotUnroll = 4;
+__global__ void __launch_bounds__(kCommThreads) allreduce_oneshot_kernel(PeerPtrs pp, int rank, int world, int64_t start,
+                                                                         int64_t n, float scale,
+                                                                         const float* __restrict__ inv_scale) {
   cross_rank_barrier(pp.pad, rank, world);
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    float acc = 0.f;
-    for (int p = 0; p < world; ++p) acc += __ldcg(pp.buf[rank] + (int64_t)p * slot_stride + i);
-    data[i] = acc;
+  const float s = scale * (inv_scale ? *inv_scale : 1.0f);
+  const int64_t n4 = n / 4;
+  float4 acc[kOneShotUnroll];
+  int64_t idx[kOneShotUnroll];
+  bool bad = false;
+#pragma unroll
+  for (int u = 0; u < kOneShotUnroll; ++u) {
+    idx[u] = ((int64_t)blockIdx.x * kOneShotUnroll + u) * blockDim.x + threadIdx.x;
+    acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  cross_rank_barrier(pp.pad, rank, world);            // slots may be reused by the next call
+#pragma unroll 1
+  for (int p = 0; p < world; ++p) {
+    const float* src = pp.buf[p] + start;
+    float4 v[kOneShotUnroll];
+#pragma unroll
+    for (int u = 0; u < kOneShotUnroll; ++u)
+      if (idx[u] < n4) v[u] = ld_peer(src + idx[u] * 4);
+#pragma unroll
+    for (int u = 0; u < kOneShotUnroll; ++u)
+      if (idx[u] < n4) acc[u].x += v[u].x, acc[u].y += v[u].y, acc[u].z += v[u].z, acc[u].w += v[u].w;
+  }
+#pragma unroll
+  for (int u = 0; u < kOneShotUnroll; ++u) {
+    if (idx[u] >= n4) continue;
+    acc[u].x *= s, acc[u].y *= s, acc[u].z *= s, acc[u].w *= s;
+    bad |= !(isfinite(acc[u].x) && isfinite(acc[u].y) && isfinite(acc[u].z) && isfinite(acc[u].w));
+  }
+  cross_rank_barrier(pp.pad, rank, world);            // every rank has read every copy
+  float* dst = pp.buf[rank] + start;
+#pragma unroll
+  for (int u = 0; u < kOneShotUnroll; ++u)
+    if (idx[u] < n4) reinterpret_cast<float4*>(dst)[idx[u]] = acc[u];
+  if (pp.flag[0] != nullptr && __syncthreads_or(bad) && threadIdx.x == 0)
+    *reinterpret_cast<volatile float*>(pp.flag[rank]) = 1.0f;      // same sums on every rank: a local flag suffices
+}
+
+// All-reduce of a tiny fp32 vector that is NOT in symmetric memory (SyncBN statistics outside the fused kernels,
+// metric vectors): one block per rank, one meeting (exchange_sum, comm/peer_sync.cuh).
+// staging layout per rank: float[2][world][slot_stride].
+__global__ void __launch_bounds__(1024) small_allreduce_kernel(SyncPeers sp, float* __restrict__ data, int n) {
+  exchange_sum(sp, data, data, n, threadIdx.x, blockDim.x, [] { __syncthreads(); });
 }
 
 // ---- single-process DataParallel helpers (all GPUs in one address space, peer access enabled) ----------
@@ -396,12 +434,43 @@ extern "C" int pdb_broadcast_inplace(void* const* bufs, void* const* pads, int r
   return 0;
 }
 
+extern "C" int pdb_allreduce_oneshot(void* const* bufs, void* const* pads, void* const* flags, int rank, int world,
+                                     int64_t start, int64_t n, float scale, const float* inv_scale, void* stream) {
+  PDB_CHECK_ARG(bufs && pads && n >= 0 && start >= 0, "pdb_allreduce_oneshot: bad arguments");
+  PDB_CHECK_ARG(n % 4 == 0 && start % 4 == 0, "pdb_allreduce_oneshot: range must be 16-byte aligned (start=%lld n=%lld)",
+                (long long)start, (long long)n);
+  PDB_CHECK_ARG(rank >= 0 && rank < world, "pdb_allreduce_oneshot: rank %d out of range", rank);
+  if (n == 0) return 0;
+  const int64_t per_block = (int64_t)kCommThreads * kOneShotUnroll;            // float4 per block
+  const int64_t blocks = (n / 4 + per_block - 1) / per_block;
+  PDB_CHECK_ARG(blocks <= 64, "pdb_allreduce_oneshot: range of %lld floats is too large for the one-shot kernel (max %lld)",
+                (long long)n, (long long)(64 * per_block * 4));
+  PeerPtrs pp;
+  if (int e = fill_peers(&pp, bufs, pads, flags, world)) return e;
+  allreduce_oneshot_kernel<<<(int)blocks, kCommThreads, 0, (cudaStream_t)stream>>>(pp, rank, world, start, n, scale, inv_scale);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+namespace pdb {
+int fill_sync(SyncPeers* sp, void* const* staging, void* const* pads, int rank, int world, int slot_stride, int row) {
+  PDB_CHECK_ARG(staging && pads, "sync peers: null staging / pads");
+  PDB_CHECK_ARG(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "sync peers: bad rank %d / world %d", rank, world);
+  for (int i = 0; i < kMaxWorld; ++i) {
+    sp->staging[i] = i < world ? static_cast<float*>(staging[i]) : nullptr;
+    sp->pad[i] = i < world ? static_cast<uint32_t*>(pads[i]) : nullptr;
+  }
+  sp->rank = rank, sp->world = world, sp->slot_stride = slot_stride, sp->row = row;
+  return 0;
+}
+}  // namespace pdb
+
 extern "C" int pdb_small_allreduce(void* const* staging, void* const* pads, int rank, int world, float* data, int n,
                                    int slot_stride, void* stream) {
   PDB_CHECK_ARG(staging && pads && data && n > 0 && n <= slot_stride, "pdb_small_allreduce: bad arguments");
-  PeerPtrs pp;
-  if (int e = fill_peers(&pp, staging, pads, nullptr, world)) return e;
-  small_allreduce_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(pp, rank, world, data, n, slot_stride);
+  SyncPeers sp;
+  if (int e = fill_sync(&sp, staging, pads, rank, world, slot_stride, 0)) return e;
+  small_allreduce_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(sp, data, n);
   PDB_LAUNCH_CHECK();
   return 0;
 }

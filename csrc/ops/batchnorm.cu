@@ -15,6 +15,8 @@
 
 namespace pdb {
 
+int fill_sync(SyncPeers* sp, void* const* staging, void* const* pads, int rank, int world, int slot_stride, int row);   // collectives.cu
+
 constexpr int kThreads = 256;
 constexpr int kMaxC = 4096;
 
@@ -162,16 +164,10 @@ __global__ void __launch_bounds__(kThreads) bn_stats_kernel(const T* __restrict_
 // the per-block partials also pushes the [2C] sums into slot `rank` of every peer's symmetric staging
 // buffer (P2P stores over NVLink), meets the peers on the signal pad, and adds up the `world` slots — the
 // kernel returns global sums, no collective call.
-struct SyncPeers {
-  float* staging[kMaxWorld];      // float[world][slot_stride] per rank
-  uint32_t* pad[kMaxWorld];
-};
-
 template <typename T>
 __global__ void __launch_bounds__(kThreads) bn_stats_sync_kernel(const T* __restrict__ x, int64_t rows, int C, int cx,
                                                                  int ry, float* __restrict__ sums,
-                                                                 StatsScratch* __restrict__ scratch, SyncPeers sp,
-                                                                 int rank, int world, int slot_stride) {
+                                                                 StatsScratch* __restrict__ scratch, SyncPeers sp) {
   extern __shared__ float smem[];
   __shared__ bool is_last;
   const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
@@ -200,40 +196,11 @@ __global__ void __launch_bounds__(kThreads) bn_stats_sync_kernel(const T* __rest
   for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
     float acc = 0.f;
     for (unsigned b = 0; b < gridDim.x; ++b) acc += __ldcg(all + (size_t)b * 2 * C + c);
-    for (int p = 0; p < world; ++p) sp.staging[p][(int64_t)rank * slot_stride + c] = acc;      // push to every rank
+    sums[c] = acc;                                       // local sums; replaced by the global ones below
   }
   if (threadIdx.x == 0) scratch->ticket = 0;
-  __threadfence_system();
-  // one block per rank takes part: it uses signal-pad row 0 of the (dedicated) staging allocation
   __syncthreads();
-  if (threadIdx.x < world && (int)threadIdx.x != rank) {
-    const int peer = threadIdx.x;
-    uint32_t* remote = sp.pad[peer] + rank;
-    uint32_t* local = sp.pad[rank] + peer;
-    const unsigned long long t0 = globaltimer_ns();
-    while (cas_release_sys(remote, 0u, 1u) != 0u)
-      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
-    while (cas_acquire_sys(local, 1u, 0u) != 1u)
-      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
-  }
-  __syncthreads();
-  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
-    float acc = 0.f;
-    for (int p = 0; p < world; ++p) acc += __ldcg(sp.staging[rank] + (int64_t)p * slot_stride + c);
-    sums[c] = acc;
-  }
-  // second meeting: nobody may overwrite a slot (next layer) before every rank has read it
-  __syncthreads();
-  if (threadIdx.x < world && (int)threadIdx.x != rank) {
-    const int peer = threadIdx.x;
-    uint32_t* remote = sp.pad[peer] + rank;
-    uint32_t* local = sp.pad[rank] + peer;
-    const unsigned long long t0 = globaltimer_ns();
-    while (cas_release_sys(remote, 0u, 1u) != 0u)
-      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
-    while (cas_acquire_sys(local, 1u, 0u) != 1u)
-      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
-  }
+  exchange_sum(sp, sums, sums, 2 * C, threadIdx.x, blockDim.x, [] { __syncthreads(); });
 }
 
 // Every block ends by adding its per-channel partials to global memory.  Hundreds of blocks hitting the same 2C
@@ -249,7 +216,7 @@ __global__ void __launch_bounds__(kThreads, 3) bn_bwd_reduce_kernel(const T* __r
                                                                     int ry, const float* __restrict__ mean,
                                                                     const float* __restrict__ rstd,
                                                                     float* __restrict__ dsums, float* __restrict__ rep,
-                                                                    unsigned int* __restrict__ ticket) {
+                                                                    unsigned int* __restrict__ ticket, const SyncPeers sp) {
   extern __shared__ float smem[];
   __shared__ bool is_last;
   const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
@@ -281,6 +248,12 @@ __global__ void __launch_bounds__(kThreads, 3) bn_bwd_reduce_kernel(const T* __r
 #pragma unroll
     for (int r = 0; r < kReduceReplicas; ++r) acc += __ldcg(rep + (size_t)r * 2 * C + c);
     dsums[c] = acc;
+  }
+  // SyncBatchNorm backward (torch:nn/modules/_functions.py:126-209 all-reduces [sum_dy, sum_dy_xmu]): the block that
+  // folded the replicas exchanges the [2C] sums with its peers right here — no extra launch, one cross-GPU meeting
+  if (sp.world > 1) {
+    __syncthreads();
+    exchange_sum(sp, dsums, dsums, 2 * C, threadIdx.x, blockDim.x, [] { __syncthreads(); });
   }
 }
 
@@ -533,13 +506,10 @@ extern "C" int pdb_bn_stats_sync(const void* x, int dtype, int64_t rows, int C, 
   const size_t need = sizeof(StatsScratch) + (size_t)grid * 2 * C * sizeof(float);
   PDB_CHECK_ARG(scratch_bytes >= need && ((uintptr_t)scratch) % 256 == 0, "pdb_bn_stats_sync: scratch too small or misaligned");
   SyncPeers sp;
-  for (int i = 0; i < kMaxWorld; ++i) {
-    sp.staging[i] = i < world ? static_cast<float*>(staging[i]) : nullptr;
-    sp.pad[i] = i < world ? static_cast<uint32_t*>(pads[i]) : nullptr;
-  }
+  if (int e = fill_sync(&sp, staging, pads, rank, world, slot_stride, 0)) return e;
   const size_t smem = (size_t)kThreads * 16 * sizeof(float);
   PDB_DISPATCH_ACT(dtype, T, (bn_stats_sync_kernel<T><<<grid, kThreads, smem, (cudaStream_t)stream>>>(
-                                (const T*)x, rows, C, cx, ry, sums, (StatsScratch*)scratch, sp, rank, world, slot_stride)));
+                                (const T*)x, rows, C, cx, ry, sums, (StatsScratch*)scratch, sp)));
   PDB_LAUNCH_CHECK();
   return 0;
 }
@@ -548,8 +518,14 @@ extern "C" size_t pdb_bn_bwd_reduce_scratch_floats(int C) { return (size_t)kRedu
 
 extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, int dtype,
                                  int64_t rows, int C, const float* mean, const float* rstd, float* dsums,
-                                 float* scratch, void* stream) {
+                                 float* scratch, const pdb_sync_peers* sync, void* stream) {
   PDB_CHECK_ARG(dz && x && mean && rstd && dsums, "pdb_bn_bwd_reduce: null pointer");
+  SyncPeers sp{};
+  if (sync && sync->world > 1) {
+    PDB_CHECK_ARG(scratch, "pdb_bn_bwd_reduce: the cross-GPU exchange needs the replica scratch (last-block fold)");
+    PDB_CHECK_ARG(2 * C <= sync->slot_stride, "pdb_bn_bwd_reduce: 2C=%d exceeds the staging slot (%d floats)", 2 * C, sync->slot_stride);
+    if (int e = fill_sync(&sp, sync->staging, sync->pads, sync->rank, sync->world, sync->slot_stride, sync->row)) return e;
+  }
   float* rep = scratch;
   unsigned int* ticket = scratch ? reinterpret_cast<unsigned int*>(scratch + (size_t)kReduceReplicas * 2 * C) : nullptr;
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_bwd_reduce: bad shape rows=%lld C=%d",
@@ -564,13 +540,13 @@ extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* r
   PDB_DISPATCH_ACT(dtype, T, {
     if (relu_mask)
       bn_bwd_reduce_kernel<T, 2><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, relu_mask, (const T*)x, rows, C,
-                                                               cx, ry, mean, rstd, dsums, rep, ticket);
+                                                               cx, ry, mean, rstd, dsums, rep, ticket, sp);
     else if (z)
       bn_bwd_reduce_kernel<T, 1><<<grid, kThreads, smem, st>>>((const T*)dz, (const T*)z, nullptr, (const T*)x, rows, C,
-                                                               cx, ry, mean, rstd, dsums, rep, ticket);
+                                                               cx, ry, mean, rstd, dsums, rep, ticket, sp);
     else
       bn_bwd_reduce_kernel<T, 0><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, nullptr, (const T*)x, rows, C, cx,
-                                                               ry, mean, rstd, dsums, rep, ticket);
+                                                               ry, mean, rstd, dsums, rep, ticket, sp);
   });
   PDB_LAUNCH_CHECK();
   return 0;

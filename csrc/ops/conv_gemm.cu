@@ -22,6 +22,7 @@
 // Delegates being replaced: cuDNN 9.22 convolutions and cuBLAS(Lt) linear.
 #include "common.cuh"
 #include "tc05.cuh"
+#include "comm/peer_sync.cuh"
 
 namespace pdb {
 using namespace tc05;
@@ -101,6 +102,8 @@ struct FpropParams {
                        // to copy b % R and the last CTA folds the copies into `stats` — hundreds of CTAs adding to
                        // the same 2N addresses serialise in L2 (~100 ns each, 20-30 us per launch otherwise)
   const float* bias;   // [N]; may be null
+  SyncPeers sync;      // world > 1: SyncBatchNorm — the CTA that folds the replicas also exchanges the [2N] sums with
+                       // the peer GPUs (one meeting over the signal pad), so `stats` comes back global
 };
 
 // kPair: the CTA is one half of a cta_group::2 pair working on a 256-row tile; it stages only HALF of the B tile.
@@ -463,6 +466,12 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll
           for (int r = 0; r < kStatReplicas; ++r) a += __ldcg(p.stats_rep + (size_t)r * 2 * p.N + c);
           p.stats[c] = a;
+        }
+        if (p.sync.world > 1) {
+          // K6: the statistics all-reduce of SyncBatchNorm (torch:nn/modules/_functions.py:7-124 runs stats ->
+          // all_gather -> combine as separate launches + a library collective) happens in the producing GEMM
+          named_bar_sync(1, kEpiThreads);
+          exchange_sum(p.sync, p.stats, p.stats, 2 * p.N, tid_e, kEpiThreads, [] { named_bar_sync(1, kEpiThreads); });
         }
       }
     }
@@ -876,9 +885,20 @@ using namespace pdb;
 
 extern "C" size_t pdb_conv_stats_scratch_floats(int K) { return (size_t)kStatReplicas * 2 * K + 32; }
 
+namespace pdb {
+int fill_sync(SyncPeers* sp, void* const* staging, void* const* pads, int rank, int world, int slot_stride, int row);   // collectives.cu
+static int set_sync(FpropParams* p, const pdb_sync_peers* sync, const char* who) {
+  p->sync = SyncPeers{};
+  if (!sync || sync->world <= 1) return 0;
+  PDB_CHECK_ARG(p->stats && p->stats_rep, "%s: the cross-GPU statistics exchange needs stats and stats_scratch", who);
+  PDB_CHECK_ARG(2 * p->N <= sync->slot_stride, "%s: 2K=%d exceeds the staging slot (%d floats)", who, 2 * p->N, sync->slot_stride);
+  return fill_sync(&p->sync, sync->staging, sync->pads, sync->rank, sync->world, sync->slot_stride, sync->row);
+}
+}  // namespace pdb
+
 extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, const pdb_conv_shape* s, int64_t lda,
                               int64_t ldd, float* stats, float* stats_scratch, const float* bias, int block_n,
-                              int accumulate, void* stream) {
+                              int accumulate, const pdb_sync_peers* sync, void* stream) {
   PDB_CHECK_ARG(x && w && y && s, "pdb_conv_fprop: null pointer");
   PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16 || dtype == PDB_FP32,
                 "pdb_conv_fprop: dtype must be PDB_BF16, PDB_FP16 or PDB_FP32");
@@ -915,6 +935,7 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
   p.accumulate = accumulate ? 1 : 0;
   p.div_pq.init((uint32_t)(P * Q)), p.div_q.init((uint32_t)Q), p.div_nb.init((uint32_t)p.num_n_blocks);
   p.stats = stats, p.stats_rep = stats ? stats_scratch : nullptr, p.bias = bias;
+  if (int e = set_sync(&p, sync, "pdb_conv_fprop")) return e;
 
   CUtensorMap tmA, tmB, tmD;
   if (plain) {
@@ -1015,7 +1036,7 @@ extern "C" int pdb_conv_wgrad(const void* x, const void* dy, float* dw, int dtyp
 // p-2 .. p+1.  ws: [64, 256] 16-bit, column (r*4 + s)*16 + ch (pdb_stem_weight_s2d).  No im2col matrix exists: TMA
 // im2col mode gathers the taps straight from xs (ref delegate: cuDNN's 7x7 stem on NCHW input).
 extern "C" int pdb_stem_fprop(const void* xs, const void* ws, void* y, int dtype, int N, int Hs, int Ws, float* stats,
-                              float* stats_scratch, void* stream) {
+                              float* stats_scratch, const pdb_sync_peers* sync, void* stream) {
   PDB_CHECK_ARG(xs && ws && y && N > 0 && Hs > 0 && Ws > 0, "pdb_stem_fprop: bad arguments");
   PDB_CHECK_ARG(dtype == PDB_BF16 || dtype == PDB_FP16, "pdb_stem_fprop: dtype must be PDB_BF16 or PDB_FP16");
   if (int e = load_driver_fns()) return e;
@@ -1029,6 +1050,7 @@ extern "C" int pdb_stem_fprop(const void* xs, const void* ws, void* y, int dtype
   p.a_im2col = 1, p.accumulate = 0;
   p.div_pq.init((uint32_t)(Hs * Ws)), p.div_q.init((uint32_t)Ws), p.div_nb.init(1u);
   p.stats = stats, p.stats_rep = stats ? stats_scratch : nullptr, p.bias = nullptr;
+  if (int e = set_sync(&p, sync, "pdb_stem_fprop")) return e;
   CUtensorMap tmA, tmB, tmD;
   if (int e = make_im2col_4d(&tmA, xs, dtype, N, Hs, Ws, 16, 4, 4, 1, 2, BLOCK_M, 1, 16, CU_TENSOR_MAP_SWIZZLE_32B)) return e;
   if (int e = make_tiled_2d(&tmB, ws, dtype, 64, 256, 256, 64, 16, CU_TENSOR_MAP_SWIZZLE_32B)) return e;

@@ -26,6 +26,20 @@ extern "C" {
 #define PDB_FP16 1
 #define PDB_FP32 2
 
+/* Peers of a small cross-GPU sum that a kernel performs itself (SyncBatchNorm statistics in the convolution epilogue and
+ * in the BatchNorm backward reduction; pdb_small_allreduce uses the same protocol).  staging[r]: rank r's symmetric
+ * staging area float[2][world][slot_stride] as mapped in THIS process; pads[r]: rank r's signal pad, of which row `row`
+ * (world 32-bit slots) is used.  Exchanges alternate between the two halves of the staging area, so one meeting per
+ * exchange suffices; all ranks must issue the same sequence of exchanges on a row.  world <= 1 or a null pointer: no
+ * exchange.  (K6; torch:nn/modules/_functions.py:7-209 does this with all_gather / all_reduce calls per BN layer.) */
+typedef struct {
+  void* staging[16];
+  void* pads[16];
+  int rank, world;
+  int slot_stride;
+  int row;
+} pdb_sync_peers;
+
 const char* pdb_last_error(void);
 int pdb_version(void);
 
@@ -83,7 +97,7 @@ int pdb_bn_stats(const void* x, int dtype, int64_t rows, int C, float* sums, voi
 
 /* K6 — SyncBatchNorm statistics (torch:nn/modules/_functions.py:7-124): pdb_bn_stats with the cross-GPU
  * reduction inside the kernel.  The block that folds the partials pushes the [2C] sums into slot `rank` of
- * every peer's symmetric staging buffer (float[world][slot_stride], P2P stores), meets the peers on the
+ * every peer's symmetric staging buffer (float[2][world][slot_stride], P2P stores), meets the peers on the
  * staging allocation's signal pad and adds the `world` slots: `sums` comes back global.  One rank per GPU. */
 int pdb_bn_stats_sync(const void* x, int dtype, int64_t rows, int C, float* sums, void* scratch,
                       size_t scratch_bytes, void* const* staging, void* const* pads, int rank, int world,
@@ -119,11 +133,12 @@ int pdb_bn_apply_eval(const void* x, const void* residual, void* y, int dtype, i
  * zeroed by the caller.
  * scratch (nullable): pdb_bn_bwd_reduce_scratch_floats(C) ZEROED floats; when given, the per-block partials are
  * spread over 16 replicas and folded by the last block (dsums is then overwritten, not accumulated) — this
- * removes the atomic contention that otherwise costs ~45 us per launch. */
+ * removes the atomic contention that otherwise costs ~45 us per launch.
+ * sync (nullable; needs scratch): SyncBatchNorm — the block that folds the replicas also sums dsums over the peer GPUs. */
 size_t pdb_bn_bwd_reduce_scratch_floats(int C);
 int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, int dtype,
                       int64_t rows, int C, const float* mean, const float* rstd, float* dsums, float* scratch,
-                      void* stream);
+                      const pdb_sync_peers* sync, void* stream);
 
 /* dx = gamma*rstd * (g - dsums[c]/count - xhat * dsums[C+c]/count);  optionally also writes
  * dres = g (gradient of the residual branch).  Block 0 accumulates dgamma += dsums[C:], dbeta +=
@@ -156,7 +171,7 @@ int pdb_stem_im2col(const float* x, void* col, int dtype, int N, int H, int W, i
 int pdb_stem_s2d(const float* x, void* xs, int dtype, int N, int H, int W, void* stream);
 int pdb_stem_weight_s2d(const void* w, void* ws, int dtype, int K, void* stream);
 int pdb_stem_fprop(const void* xs, const void* ws, void* y, int dtype, int N, int Hs, int Ws, float* stats,
-                   float* stats_scratch, void* stream);
+                   float* stats_scratch, const pdb_sync_peers* sync, void* stream);
 int pdb_stem_wgrad(const void* xs, const void* dy, float* dws, int dtype, int N, int Hs, int Ws, int splits,
                    void* stream);
 int pdb_stem_dw_unpack(const float* dws, float* dw, int K, int accumulate, void* stream);
@@ -190,9 +205,11 @@ typedef struct {
  * per-channel partial sums over 16 replicas and the last CTA folds them (stats is then overwritten): without it
  * every CTA adds to the same 2K addresses and the L2 atomic units serialise (20-30 us on wide layers). */
 size_t pdb_conv_stats_scratch_floats(int K);
+/* sync (nullable; needs stats + stats_scratch): SyncBatchNorm — the CTA that folds the replicas also sums the [2K]
+ * statistics over the peer GPUs before the kernel ends (no separate collective launch). */
 int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, const pdb_conv_shape* s, int64_t lda,
                    int64_t ldd, float* stats, float* stats_scratch, const float* bias, int block_n, int accumulate,
-                   void* stream);
+                   const pdb_sync_peers* sync, void* stream);
 
 /* dw[K, R*S*C] (fp32, row pitch ldw) += dy[N*P*Q, K]^T * im2col(x).  The pixel range is split over
  * CTAs (`splits`, 0 = heuristic) and partial tiles are added with fp32 vector reductions, so dw
@@ -241,8 +258,13 @@ int pdb_allreduce_inplace_wire16(void* const* bufs, void* const* pads, void* con
  * [start, start+n) from root's buffer. */
 int pdb_broadcast_inplace(void* const* bufs, void* const* pads, int rank, int world, int root, int64_t start,
                           int64_t n, int blocks, void* stream);
+/* K1 for small buckets (up to 64 * 8192 floats; the Python layer switches at 256 KB): one-shot variant of
+ * pdb_allreduce_inplace — meet, every rank reads all copies and adds them in rank order (bit-identical sums on every
+ * rank), meet, write the local copy.  Same fused scale / un-scale / non-finite check; flags[rank][0] is raised locally. */
+int pdb_allreduce_oneshot(void* const* bufs, void* const* pads, void* const* flags, int rank, int world, int64_t start,
+                          int64_t n, float scale, const float* inv_scale, void* stream);
 /* K5/K6 (ref:restnet_ddp.py:63-64 metric reduce; SyncBatchNorm statistics): one-shot in-place sum over
- * ranks of data[0:n] through a symmetric staging area float[world][slot_stride]. */
+ * ranks of data[0:n] through a symmetric staging area float[2][world][slot_stride] (see pdb_sync_peers). */
 int pdb_small_allreduce(void* const* staging, void* const* pads, int rank, int world, float* data, int n,
                         int slot_stride, void* stream);
 /* K4a-K4c (ref:resnet_dp.py:21 DataParallel scatter / replicate / gather): the current GPU pulls

@@ -293,32 +293,50 @@ class NativeResNetEngine:
         r0 = self._stat_floats + bn.rslot
         return self.stats[r0: r0 + bn.rsize]
 
-    def _sync_stats(self, buf: torch.Tensor) -> float:
-        """SyncBatchNorm: sums are additive, so one all-reduce of [2C] per layer and direction."""
+    def _sync_world(self) -> int:
         if not self.sync_bn:
-            return 1.0
+            return 1
         import torch.distributed as dist
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+    def _sync_handle(self, n_floats: int):
+        """SyncBatchNorm on the native comm backend: the handle that lets the kernel which already holds the [2C]
+        sums (conv epilogue forward, BN reduction backward) add them up over the GPUs itself — K6, zero extra
+        launches.  None: no SyncBN, one rank, or a backend without peer memory (then `_sync_stats` does it)."""
+        if self._sync_world() <= 1:
+            return None
+        comm = getattr(self.ddp, "comm", None)
+        return comm.sync_peers(n_floats) if hasattr(comm, "sync_peers") else None
+
+    def _sync_stats(self, buf: torch.Tensor, fused: bool) -> float:
+        """SyncBatchNorm: sums are additive, so one all-reduce of [2C] per layer and direction.  `fused`: the producing
+        kernel has already exchanged them.  Returns the factor on the per-channel element count."""
+        world = self._sync_world()
+        if world <= 1:
+            return 1.0
+        if not fused:
+            import torch.distributed as dist
             comm = getattr(self.ddp, "comm", None)
             if comm is not None and hasattr(comm, "allreduce_small_"):
-                comm.allreduce_small_(buf)        # K6: peer-memory exchange, no NCCL call per BN layer
+                comm.allreduce_small_(buf)        # peer-memory exchange as a launch of its own (payload > one slot)
             else:
                 if buf.is_cuda and torch.cuda.is_current_stream_capturing():
                     raise RuntimeError("SyncBN statistics go through torch.distributed here: not captured")
                 dist.all_reduce(buf)
-            return float(dist.get_world_size())
-        return 1.0
+        return float(world)
 
     def _conv_bn(self, cv: _ConvPlan, bn: _BNPlan, x: torch.Tensor, *, residual=None, relu=True, train=True):
         N, H, W, _ = x.shape
         P, Q = cv.out_hw(H, W)
         y = self._new(N, P, Q, cv.K)
         sums = self.stats[bn.slot: bn.slot + 2 * bn.C] if train else None
-        ops.conv_fprop(x, cv.w16, y, cv.shape(N, H, W), stats=sums, stats_scratch=self._fwd_scratch(bn) if train else None)
+        sync = self._sync_handle(2 * bn.C) if train else None
+        ops.conv_fprop(x, cv.w16, y, cv.shape(N, H, W), stats=sums, stats_scratch=self._fwd_scratch(bn) if train else None,
+                       sync=sync)
         z = self._new(N, P, Q, cv.K)
         rows = N * P * Q
         if train:
-            world = self._sync_stats(sums)
+            world = self._sync_stats(sums, fused=sync is not None)
             # one bit per element records the ReLU decision; BN backward reads it instead of z (1/16 the bytes)
             mask = self._new(rows * cv.K // 8, dtype=torch.uint8) if relu else None
             ops.bn_apply(y.view(rows, cv.K), None if residual is None else residual.view(rows, cv.K),
@@ -338,19 +356,21 @@ class NativeResNetEngine:
         rows = N * P * Q
         y = self._new(N, P, Q, cv.K)
         sums = self.stats[bn.slot: bn.slot + 2 * bn.C] if train else None
+        sync = self._sync_handle(2 * bn.C) if train else None
         if self.stem_s2d and H % 2 == 0 and W % 2 == 0:
             col = self._new(N, H // 2, W // 2, 16)          # space-to-depth input; also the wgrad operand
             ops.stem_s2d(x.contiguous().float(), col)
-            ops.stem_fprop(col, self.stem_ws, y, stats=sums, stats_scratch=self._fwd_scratch(bn) if train else None)
+            ops.stem_fprop(col, self.stem_ws, y, stats=sums, stats_scratch=self._fwd_scratch(bn) if train else None,
+                           sync=sync)
         else:
             col = self._new(rows, STEM_KPAD)
             ops.stem_im2col(x.contiguous().float(), col)
             ops.conv_fprop(col, self.stem_w16, y, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0), stats=sums,
-                           stats_scratch=self._fwd_scratch(bn) if train else None)
+                           stats_scratch=self._fwd_scratch(bn) if train else None, sync=sync)
         z = self._new(N, P, Q, cv.K)
         mask = None
         if train:
-            world = self._sync_stats(sums)
+            world = self._sync_stats(sums, fused=sync is not None)
             mask = self._new(rows * cv.K // 8, dtype=torch.uint8)
             ops.bn_apply(y.view(rows, cv.K), None, z.view(rows, cv.K), sums, rows * world, bn.gamma, bn.beta, bn.eps,
                          bn.momentum, bn.running_mean, bn.running_var, bn.nbt, bn.mean, bn.rstd, True, mask)
@@ -459,8 +479,9 @@ class NativeResNetEngine:
         v = lambda t: None if t is None else t.view(rows, bn.C)    # noqa: E731
         r0 = self._stat_floats + bn.rslot
         scratch = self.dstats[r0: r0 + bn.rsize]
-        ops.bn_bwd_reduce(v(dz), None, v(y), bn.mean, bn.rstd, ds, relu_mask=mask, scratch=scratch)
-        world = self._sync_stats(ds)
+        sync = self._sync_handle(2 * bn.C)
+        ops.bn_bwd_reduce(v(dz), None, v(y), bn.mean, bn.rstd, ds, relu_mask=mask, scratch=scratch, sync=sync)
+        world = self._sync_stats(ds, fused=sync is not None)
         dy = self._new(*y.shape)
         dres = self._new(*y.shape) if want_dres else None
         ops.bn_bwd_apply(v(dz), None, v(y), v(dy), v(dres), bn.mean, bn.rstd, bn.gamma, ds, rows * world, bn.dgamma,

@@ -5,6 +5,12 @@ from ctypes import POINTER, Structure, c_char_p, c_double, c_float, c_int, c_int
 P = c_void_p
 
 
+class SyncPeersC(Structure):
+    """pdb_sync_peers of include/pdb200.h."""
+    _fields_ = [("staging", c_void_p * 16), ("pads", c_void_p * 16), ("rank", c_int), ("world", c_int),
+                ("slot_stride", c_int), ("row", c_int)]
+
+
 class ConvShape(Structure):
     _fields_ = [("N", c_int), ("H", c_int), ("W", c_int), ("C", c_int), ("K", c_int), ("R", c_int), ("S", c_int),
                 ("stride", c_int), ("pad", c_int)]
@@ -28,7 +34,7 @@ def declare(L):
     sig("pdb_bn_stats", [P, c_int, c_int64, c_int, P, P, c_size_t, P])
     sig("pdb_bn_apply", [P, P, P, c_int, c_int64, c_int, P, c_double, P, P, c_float, c_float, P, P, P, P, P, c_int, P, P])
     sig("pdb_bn_apply_eval", [P, P, P, c_int, c_int64, c_int, P, P, P, P, c_float, c_int, P])
-    sig("pdb_bn_bwd_reduce", [P, P, P, P, c_int, c_int64, c_int, P, P, P, P, P])
+    sig("pdb_bn_bwd_reduce", [P, P, P, P, c_int, c_int64, c_int, P, P, P, P, POINTER(SyncPeersC), P])
     sig("pdb_bn_bwd_reduce_scratch_floats", [c_int], c_size_t)
     sig("pdb_bn_bwd_apply", [P, P, P, P, P, P, c_int, c_int64, c_int, P, P, P, P, c_double, P, P, P])
     sig("pdb_maxpool3x3s2_fwd", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])
@@ -39,13 +45,13 @@ def declare(L):
     sig("pdb_stem_im2col", [P, P, c_int, c_int, c_int, c_int, c_int, P])
     sig("pdb_stem_s2d", [P, P, c_int, c_int, c_int, c_int, P])
     sig("pdb_stem_weight_s2d", [P, P, c_int, c_int, P])
-    sig("pdb_stem_fprop", [P, P, P, c_int, c_int, c_int, c_int, P, P, P])
+    sig("pdb_stem_fprop", [P, P, P, c_int, c_int, c_int, c_int, P, P, POINTER(SyncPeersC), P])
     sig("pdb_stem_wgrad", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])
     sig("pdb_stem_dw_unpack", [P, P, c_int, c_int, P])
     sig("pdb_add16", [P, P, P, c_int, c_int64, P])
     sig("pdb_upsample2_zero", [P, P, c_int, c_int, c_int, c_int, c_int, P])
     sig("pdb_add_strided2", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])
-    sig("pdb_conv_fprop", [P, P, P, c_int, POINTER(ConvShape), c_int64, c_int64, P, P, P, c_int, c_int, P])
+    sig("pdb_conv_fprop", [P, P, P, c_int, POINTER(ConvShape), c_int64, c_int64, P, P, P, c_int, c_int, POINTER(SyncPeersC), P])
     sig("pdb_conv_stats_scratch_floats", [c_int], c_size_t)
     sig("pdb_conv_wgrad", [P, P, P, c_int, POINTER(ConvShape), c_int64, c_int64, c_int64, c_int64, c_int, c_int, P])
     sig("pdb_weight_dgrad_layout", [P, P, c_int, c_int, c_int, c_int, c_int, P])
@@ -63,6 +69,7 @@ OPTIONAL = {
     "pdb_bn_stats_sync": [P, c_int, c_int64, c_int, P, P, c_size_t, P, P, c_int, c_int, c_int, P],
     "pdb_broadcast_inplace": [P, P, c_int, c_int, c_int, c_int64, c_int64, c_int, P],
     "pdb_small_allreduce": [P, P, c_int, c_int, P, c_int, c_int, P],
+    "pdb_allreduce_oneshot": [P, P, P, c_int, c_int, c_int64, c_int64, c_float, P, P],
     "pdb_peer_pull": [P, P, c_int64, P],
     "pdb_reduce_to_root": [P, P, c_int, c_int64, P],
     "pdb_comm_max_blocks": [c_int, c_size_t],

@@ -8,14 +8,14 @@ import torch
 
 from . import _lib
 from ._lib import check, count_launch, ptr, require, stream_ptr
-from ._sigs import ConvShape
+from ._sigs import ConvShape, SyncPeersC
 
 __all__ = ["dtype_tag", "sgd_step", "check_finite", "scaler_update", "cast_to_16", "xent_fwd_bwd", "topk_correct", "bn_stats",
            "bn_apply", "bn_apply_eval", "bn_bwd_reduce", "bn_bwd_reduce_scratch_floats", "bn_bwd_apply", "maxpool_fwd", "maxpool_bwd",
            "avgpool_fwd", "avgpool_bwd", "nchw_to_nhwc16", "stem_im2col", "stem_s2d", "stem_weight_s2d", "stem_fprop",
            "stem_wgrad", "stem_dw_unpack", "add16", "upsample2_zero",
            "add_strided2", "conv_fprop", "conv_wgrad", "weight_dgrad_layout", "weight_dgrad_layout_batched", "pad_rows16", "colsum16",
-           "peer_copy", "peer_copy_", "reduce_to_root", "ConvShape"]
+           "peer_copy", "peer_copy_", "reduce_to_root", "ConvShape", "SyncPeersC"]
 
 _TAG = {torch.bfloat16: 0, torch.float16: 1, torch.float32: 2}
 
@@ -136,10 +136,15 @@ def bn_bwd_reduce_scratch_floats(C: int) -> int:
     return int(require().pdb_bn_bwd_reduce_scratch_floats(C))
 
 
-def bn_bwd_reduce(dz, z, x, mean, rstd, dsums, relu_mask=None, scratch=None) -> None:
+def _sync_ref(sync):
+    """ctypes reference to a SyncPeersC (or NULL): the in-kernel cross-GPU sum of SyncBatchNorm."""
+    return ctypes.byref(sync) if sync is not None else None
+
+
+def bn_bwd_reduce(dz, z, x, mean, rstd, dsums, relu_mask=None, scratch=None, sync=None) -> None:
     rows, C = x.shape
     check(require().pdb_bn_bwd_reduce(ptr(dz), ptr(z), ptr(relu_mask), ptr(x), dtype_tag(x.dtype), rows, C, ptr(mean),
-                                      ptr(rstd), ptr(dsums), ptr(scratch), _st(x)), "pdb_bn_bwd_reduce")
+                                      ptr(rstd), ptr(dsums), ptr(scratch), _sync_ref(sync), _st(x)), "pdb_bn_bwd_reduce")
     count_launch()
 
 
@@ -208,11 +213,11 @@ def stem_weight_s2d(w16: torch.Tensor, ws: torch.Tensor) -> None:
     count_launch()
 
 
-def stem_fprop(xs: torch.Tensor, ws: torch.Tensor, y: torch.Tensor, stats=None, stats_scratch=None) -> None:
+def stem_fprop(xs: torch.Tensor, ws: torch.Tensor, y: torch.Tensor, stats=None, stats_scratch=None, sync=None) -> None:
     N, Hs, Ws, C = xs.shape
     assert C == 16 and ws.shape == (64, 256) and y.numel() == N * Hs * Ws * 64
     check(require().pdb_stem_fprop(ptr(xs), ptr(ws), ptr(y), dtype_tag(xs.dtype), N, Hs, Ws, ptr(stats),
-                                   ptr(stats_scratch), _st(xs)), "pdb_stem_fprop")
+                                   ptr(stats_scratch), _sync_ref(sync), _st(xs)), "pdb_stem_fprop")
     count_launch()
 
 
@@ -252,10 +257,10 @@ def add_strided2(a, b, out) -> None:
 
 
 def conv_fprop(x, w, y, shape: ConvShape, *, lda: int = 0, ldd: int = 0, stats=None, stats_scratch=None, bias=None,
-               block_n: int = 0, accumulate: bool = False) -> None:
+               block_n: int = 0, accumulate: bool = False, sync=None) -> None:
     check(require().pdb_conv_fprop(ptr(x), ptr(w), ptr(y), dtype_tag(x.dtype), ctypes.byref(shape), lda, ldd,
-                                   ptr(stats), ptr(stats_scratch), ptr(bias), block_n, int(accumulate), _st(x)),
-          "pdb_conv_fprop")
+                                   ptr(stats), ptr(stats_scratch), ptr(bias), block_n, int(accumulate), _sync_ref(sync),
+                                   _st(x)), "pdb_conv_fprop")
     count_launch()
 
 

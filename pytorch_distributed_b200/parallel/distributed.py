@@ -144,6 +144,13 @@ class DistributedDataParallel(nn.Module):
         self.arena.refresh_shadow()
         self._sync_buffers()
 
+    def _buffers_replicated(self) -> bool:
+        """Native engine + SyncBatchNorm: every rank derives its running statistics from the same global sums, added
+        in the same (rank) order, so the BN buffers are bit-identical everywhere after the construction-time broadcast
+        and the per-iteration one (K3, torch:nn/parallel/distributed.py:2214-2257) would copy equal bytes."""
+        eng = getattr(self.module, "_engine", None)
+        return bool(eng is not None and getattr(eng, "sync_bn", False) and hasattr(self.comm, "sync_peers"))
+
     def _sync_buffers(self) -> None:                         # K3
         self.comm.broadcast_(self.buffer_arena.storage, 0)     # fp32 stats + int64 counters, one transfer
 
@@ -251,7 +258,8 @@ class DistributedDataParallel(nn.Module):
         with torch.autograd.profiler.record_function("pdb200.DistributedDataParallel.forward"):
             if torch.is_grad_enabled() and self.require_backward_grad_sync:
                 self.require_forward_param_sync = True
-            if self.require_forward_param_sync and self.broadcast_buffers and self.world_size > 1:
+            if self.require_forward_param_sync and self.broadcast_buffers and self.world_size > 1 \
+                    and not self._buffers_replicated():
                 self._sync_buffers()
             if not torch.is_grad_enabled():
                 # delegate clears the flag after a no_grad forward (distributed.py:1649-1650), so an

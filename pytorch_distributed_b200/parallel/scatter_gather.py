@@ -3,7 +3,7 @@
 Spec: torch:nn/parallel/_functions.py:82-155 (``Gather``/``Scatter``: each is the other's
 backward) and torch:nn/parallel/scatter_gather.py:49-150 (recursion over tuples / lists / dicts,
 non-tensors replicated by reference).  On CUDA the copies are peer-memory *pull* kernels
-(K4a/K4c, csrc/comm/p2p_copy.cu): the destination GPU reads its chunk straight from the source
+(K4a/K4c, `peer_pull_kernel` in csrc/comm/collectives.cu): the destination GPU reads its chunk straight from the source
 GPU's memory over NVLink, instead of the source pushing seven cudaMemcpyPeerAsync in a row.
 """
 from __future__ import annotations

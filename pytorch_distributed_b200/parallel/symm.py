@@ -56,15 +56,24 @@ class NativeComm:
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.stream = torch.cuda.Stream(self.device, priority=-1)
         self._mapped: Dict[int, _Mapped] = {}
-        # symmetric scratch: [0:64) non-finite flags, then the staging area of the small all-reduce
+        # symmetric scratch: [0:64) non-finite flags, then the staging area float[2][world][slot] of the small sums
+        # (SyncBN statistics inside the conv / BN kernels, metric vectors): two halves used alternately, see
+        # csrc/comm/peer_sync.cuh
         self.slot = 8192
-        self._aux_t = symm_mem.empty(64 + self.world * self.slot, dtype=torch.float32, device=self.device)
+        self._aux_t = symm_mem.empty(64 + 2 * self.world * self.slot, dtype=torch.float32, device=self.device)
         self._aux_t.zero_()
         self._aux = _Mapped(self._aux_t, group)
         self.flag = self._aux_t[:1]
         fl = [int(p) for p in self._aux.handle.buffer_ptrs]
         self._flag_ptrs = (ctypes.c_void_p * self.world)(*fl)
         self._staging_ptrs = (ctypes.c_void_p * self.world)(*[p + 64 * 4 for p in fl])
+        from ..ops import SyncPeersC
+        self._sync = SyncPeersC()
+        for r in range(self.world):
+            self._sync.staging[r] = fl[r] + 64 * 4
+            self._sync.pads[r] = int(self._aux.handle.signal_pad_ptrs[r])
+        self._sync.rank, self._sync.world, self._sync.slot_stride, self._sync.row = self.rank, self.world, self.slot, 0
+        self.oneshot_bytes = int(os.environ.get("PDB200_ONESHOT_BYTES", str(256 << 10)))
         self.use_multicast = os.environ.get("PDB200_NVLS", "1") != "0"
         self.blocks = int(os.environ.get("PDB200_COMM_BLOCKS", "32"))
         self._wire: Dict[torch.dtype, tuple] = {}       # wire dtype -> (mapped staging, half_elems)
@@ -105,6 +114,11 @@ class NativeComm:
             cur = (m, half)
             self._wire[dtype] = cur
         return cur
+
+    def sync_peers(self, n_floats: int):
+        """The handle a kernel needs to sum ``n_floats`` values over the ranks by itself (SyncBN statistics inside
+        the convolution epilogue / the BN backward reduction), or None when the payload does not fit a staging slot."""
+        return self._sync if self.world > 1 and n_floats <= self.slot else None
 
     def _blocks(self, m: _Mapped, n: int) -> int:
         cap = require().pdb_comm_max_blocks(self.world, m.pad_bytes)
@@ -165,6 +179,19 @@ class NativeComm:
                 self._events.append(done)
                 if t0 is not None:
                     self._bucket_marks.append((4 * n, t0, done))
+                return
+            if 4 * n <= self.oneshot_bytes and n % 4 == 0:
+                # small bucket: latency-bound, one NVLink round instead of reduce-scatter + all-gather
+                check(require().pdb_allreduce_oneshot(
+                    m.bufs, m.pads, self._flag_ptrs if found_inf is not None else None, self.rank, self.world, start, n,
+                    (1.0 / self.world) if average else 1.0, ptr(inv_scale),
+                    ctypes.c_void_p(self.stream.cuda_stream)), "pdb_allreduce_oneshot")
+                count_launch()
+                done = torch.cuda.Event(enable_timing=t0 is not None)
+                done.record(self.stream)
+                if t0 is not None:
+                    self._bucket_marks.append((4 * n, t0, done))
+                self._events.append(done)
                 return
             check(require().pdb_allreduce_inplace(
                 m.bufs, m.pads, self._flag_ptrs if found_inf is not None else None,

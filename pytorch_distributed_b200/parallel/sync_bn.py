@@ -4,8 +4,10 @@ Not used by the reference scripts but named by BASELINE.json.  D
 algorithm (torch:nn/modules/_functions.py:7-209): local per-channel statistics → all-gather of
 ``[mean, invstd, count]`` → combine → normalise; backward: local ``[sum_dy, sum_dy_xmu]`` →
 all-reduce → dx.  Here the exchanged quantities are the additive ``[sum, sum_sq, count]`` so a
-single all-reduce suffices in each direction; on the native path that exchange happens *inside*
-the BN statistics kernel over peer memory (K6) — zero NCCL calls for the 53 BN layers.
+single all-reduce suffices in each direction.  This module is the stock-op implementation (CPU / ``--engine torch``);
+on the native engine the exchange happens inside the kernels that already hold the sums — the last CTA of the
+producing convolution (forward) and the folding block of the BN backward reduction — over peer memory (K6,
+``csrc/comm/peer_sync.cuh::exchange_sum``): zero extra launches and zero NCCL calls for the 53 BN layers.
 """
 from __future__ import annotations
 
