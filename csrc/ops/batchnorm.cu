@@ -257,6 +257,51 @@ __global__ void __launch_bounds__(kThreads, 3) bn_bwd_reduce_kernel(const T* __r
   }
 }
 
+// Deterministic variant (PDB200_DETERMINISTIC=1): no atomics — every block writes its partials to a slot of its own
+// and the last block adds the slots in block order, like bn_stats_kernel.  Two runs on the same input give the same
+// bits, which turns "run it twice and compare" into a race detector for the whole step.
+template <typename T, int kMask>
+__global__ void __launch_bounds__(kThreads, 3) bn_bwd_reduce_det_kernel(const T* __restrict__ dz, const T* __restrict__ z,
+                                                                        const uint8_t* __restrict__ bits,
+                                                                        const T* __restrict__ x, int64_t rows, int C,
+                                                                        int cx, int ry, const float* __restrict__ mean,
+                                                                        const float* __restrict__ rstd,
+                                                                        float* __restrict__ dsums,
+                                                                        StatsScratch* __restrict__ scratch) {
+  extern __shared__ float smem[];
+  __shared__ bool is_last;
+  const int tx = threadIdx.x % cx, ty = threadIdx.x / cx;
+  float* partial = reinterpret_cast<float*>(scratch + 1) + (size_t)blockIdx.x * 2 * C;
+  const int ncg = C / 8;
+  for (int cg0 = 0; cg0 < ncg; cg0 += cx) {
+    const int cg = cg0 + tx;
+    float s0[8] = {0}, s1[8] = {0};
+    if (ty < ry && cg < ncg) reduce_rows<T, 1, kMask>(dz, z, bits, x, rows, C, cg, cx, ry, ty, mean, rstd, s0, s1);
+    block_fold(s0, s1, tx, ty, cx, ry, smem);
+    if (ty == 0 && cg < ncg) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int c = cg * 8 + k;
+        partial[c] = s0[k];
+        partial[C + c] = rstd[c] * (s1[k] - mean[c] * s0[k]);
+      }
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(&scratch->ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  const float* all = reinterpret_cast<const float*>(scratch + 1);
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
+    float acc = 0.f;
+    for (unsigned b = 0; b < gridDim.x; ++b) acc += __ldcg(all + (size_t)b * 2 * C + c);
+    dsums[c] = acc;
+  }
+  if (threadIdx.x == 0) scratch->ticket = 0;
+}
+
 // ------------------------------------------------------------------------------------------------
 // Forward apply.
 template <typename T, bool kRes, bool kRelu>
@@ -547,6 +592,35 @@ extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* r
     else
       bn_bwd_reduce_kernel<T, 0><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, nullptr, (const T*)x, rows, C, cx,
                                                                ry, mean, rstd, dsums, rep, ticket, sp);
+  });
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_bn_bwd_reduce_det(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, int dtype,
+                                     int64_t rows, int C, const float* mean, const float* rstd, float* dsums,
+                                     void* scratch, size_t scratch_bytes, void* stream) {
+  PDB_CHECK_ARG(dz && x && mean && rstd && dsums && scratch, "pdb_bn_bwd_reduce_det: null pointer");
+  PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_bwd_reduce_det: bad shape rows=%lld C=%d",
+                (long long)rows, C);
+  int cx, ry;
+  reduce_geometry(C, &cx, &ry);
+  const size_t smem = (size_t)kThreads * 16 * sizeof(float);
+  static int cap = 0;
+  if (cap == 0) cap = resident_blocks(bn_bwd_reduce_det_kernel<__nv_bfloat16, 2>, smem);
+  const int grid = reduce_grid(rows, ry, cap);
+  const size_t need = sizeof(StatsScratch) + (size_t)grid * 2 * C * sizeof(float);
+  PDB_CHECK_ARG(scratch_bytes >= need && ((uintptr_t)scratch) % 256 == 0,
+                "pdb_bn_bwd_reduce_det: scratch too small (%zu < %zu bytes) or misaligned", scratch_bytes, need);
+  cudaStream_t st = (cudaStream_t)stream;
+  StatsScratch* sc = (StatsScratch*)scratch;
+  PDB_DISPATCH_ACT(dtype, T, {
+    if (relu_mask)
+      bn_bwd_reduce_det_kernel<T, 2><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, relu_mask, (const T*)x, rows, C, cx, ry, mean, rstd, dsums, sc);
+    else if (z)
+      bn_bwd_reduce_det_kernel<T, 1><<<grid, kThreads, smem, st>>>((const T*)dz, (const T*)z, nullptr, (const T*)x, rows, C, cx, ry, mean, rstd, dsums, sc);
+    else
+      bn_bwd_reduce_det_kernel<T, 0><<<grid, kThreads, smem, st>>>((const T*)dz, nullptr, nullptr, (const T*)x, rows, C, cx, ry, mean, rstd, dsums, sc);
   });
   PDB_LAUNCH_CHECK();
   return 0;

@@ -140,6 +140,13 @@ int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* relu_mask, c
                       int64_t rows, int C, const float* mean, const float* rstd, float* dsums, float* scratch,
                       const pdb_sync_peers* sync, void* stream);
 
+/* The same reduction without atomics: per-block partials in `scratch` (>= pdb_bn_stats_scratch_bytes(C) bytes, ticket
+ * word zero) folded in block order by the last block — bit-reproducible from run to run.  Used by the engine's
+ * deterministic mode (PDB200_DETERMINISTIC=1), whose "same input, same bits" property is the step's race detector. */
+int pdb_bn_bwd_reduce_det(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, int dtype,
+                          int64_t rows, int C, const float* mean, const float* rstd, float* dsums, void* scratch,
+                          size_t scratch_bytes, void* stream);
+
 /* dx = gamma*rstd * (g - dsums[c]/count - xhat * dsums[C+c]/count);  optionally also writes
  * dres = g (gradient of the residual branch).  Block 0 accumulates dgamma += dsums[C:], dbeta +=
  * dsums[:C] (fp32 gradient arena views; may be null). */

@@ -127,7 +127,8 @@ class _StepPlan:
 
 
 class NativeResNetEngine:
-    def __init__(self, model, batch_size: int, dtype: torch.dtype = torch.bfloat16, sync_bn: bool = False):
+    def __init__(self, model, batch_size: int, dtype: torch.dtype = torch.bfloat16, sync_bn: bool = False,
+                 deterministic: Optional[bool] = None):
         ops.require()
         p0 = next(model.parameters())
         if not p0.is_cuda:
@@ -160,6 +161,14 @@ class NativeResNetEngine:
         # fallback would quietly turn a 20-launch step into a 350-launch one.
         self.graphs_fallback = os.environ.get("PDB200_GRAPHS_FALLBACK", "0") == "1"
         self.graph_warmup = 2                     # eager steps per shape before capture
+        # Deterministic mode (PDB200_DETERMINISTIC=1): every floating-point sum of the step is added in a fixed order —
+        # BN statistics through the two-stage kernels instead of epilogue atomics, the BN backward reduction without
+        # atomics, wgrad without split-K.  Slower (wgrad loses its parallelism over pixels), but two runs on the same
+        # input give the same bits: "run twice, compare with torch.equal" is the race detector for the whole step,
+        # and comparing against the default mode measures how much of a gradient is summation-order noise.
+        self.deterministic = (os.environ.get("PDB200_DETERMINISTIC", "0") == "1") if deterministic is None else bool(deterministic)
+        self._det_scratch = None
+        self._splits = 1 if self.deterministic else 0          # wgrad split-K: 0 = heuristic, 1 = one CTA per tile
         self._plans: Dict[tuple, _StepPlan] = {}
         self._plan: Optional[_StepPlan] = None
         self._ready_log: Optional[List[int]] = None
@@ -193,6 +202,9 @@ class NativeResNetEngine:
         # backward: [dsums of every BN | replica scratch + tickets of every BN], zeroed once per backward pass
         self.dstats = torch.zeros(self._stat_floats + self._scratch_floats, dtype=torch.float32, device=self.device)
         self._anchor = model.fc.bias
+        if self.deterministic:
+            maxc = max(b.C for b in [self.stem_bn] + [x for blk in self.blocks for x in (blk.bn1, blk.bn2, blk.bn3, blk.bnd) if x is not None])
+            self._det_scratch = torch.zeros(ops.require().pdb_bn_stats_scratch_bytes(maxc), dtype=torch.uint8, device=self.device)
         self._convs: List[_ConvPlan] = [self.stem_conv] + [c for b in self.blocks for c in
                                                            (b.conv1, b.conv2, b.conv3, b.convd) if c is not None]
         # dgrad operand layouts [Cin, kh, kw(flipped), Cout] of every conv but the stem, plus fc, in ONE flat
@@ -330,12 +342,15 @@ class NativeResNetEngine:
         P, Q = cv.out_hw(H, W)
         y = self._new(N, P, Q, cv.K)
         sums = self.stats[bn.slot: bn.slot + 2 * bn.C] if train else None
-        sync = self._sync_handle(2 * bn.C) if train else None
-        ops.conv_fprop(x, cv.w16, y, cv.shape(N, H, W), stats=sums, stats_scratch=self._fwd_scratch(bn) if train else None,
-                       sync=sync)
+        sync = self._sync_handle(2 * bn.C) if train and not self.deterministic else None
+        fused_stats = train and not self.deterministic
+        ops.conv_fprop(x, cv.w16, y, cv.shape(N, H, W), stats=sums if fused_stats else None,
+                       stats_scratch=self._fwd_scratch(bn) if fused_stats else None, sync=sync)
         z = self._new(N, P, Q, cv.K)
         rows = N * P * Q
         if train:
+            if not fused_stats:
+                ops.bn_stats(y.view(rows, cv.K), sums, self._det_scratch)       # fixed summation order
             world = self._sync_stats(sums, fused=sync is not None)
             # one bit per element records the ReLU decision; BN backward reads it instead of z (1/16 the bytes)
             mask = self._new(rows * cv.K // 8, dtype=torch.uint8) if relu else None
@@ -356,20 +371,26 @@ class NativeResNetEngine:
         rows = N * P * Q
         y = self._new(N, P, Q, cv.K)
         sums = self.stats[bn.slot: bn.slot + 2 * bn.C] if train else None
-        sync = self._sync_handle(2 * bn.C) if train else None
+        sync = self._sync_handle(2 * bn.C) if train and not self.deterministic else None
+        fused_stats = train and not self.deterministic
+        if not fused_stats:
+            sums_arg, scr_arg = None, None
+        else:
+            sums_arg, scr_arg = sums, self._fwd_scratch(bn)
         if self.stem_s2d and H % 2 == 0 and W % 2 == 0:
             col = self._new(N, H // 2, W // 2, 16)          # space-to-depth input; also the wgrad operand
             ops.stem_s2d(x.contiguous().float(), col)
-            ops.stem_fprop(col, self.stem_ws, y, stats=sums, stats_scratch=self._fwd_scratch(bn) if train else None,
-                           sync=sync)
+            ops.stem_fprop(col, self.stem_ws, y, stats=sums_arg, stats_scratch=scr_arg, sync=sync)
         else:
             col = self._new(rows, STEM_KPAD)
             ops.stem_im2col(x.contiguous().float(), col)
-            ops.conv_fprop(col, self.stem_w16, y, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0), stats=sums,
-                           stats_scratch=self._fwd_scratch(bn) if train else None, sync=sync)
+            ops.conv_fprop(col, self.stem_w16, y, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0), stats=sums_arg,
+                           stats_scratch=scr_arg, sync=sync)
         z = self._new(N, P, Q, cv.K)
         mask = None
         if train:
+            if not fused_stats:
+                ops.bn_stats(y.view(rows, cv.K), sums, self._det_scratch)
             world = self._sync_stats(sums, fused=sync is not None)
             mask = self._new(rows * cv.K // 8, dtype=torch.uint8)
             ops.bn_apply(y.view(rows, cv.K), None, z.view(rows, cv.K), sums, rows * world, bn.gamma, bn.beta, bn.eps,
@@ -479,8 +500,12 @@ class NativeResNetEngine:
         v = lambda t: None if t is None else t.view(rows, bn.C)    # noqa: E731
         r0 = self._stat_floats + bn.rslot
         scratch = self.dstats[r0: r0 + bn.rsize]
-        sync = self._sync_handle(2 * bn.C)
-        ops.bn_bwd_reduce(v(dz), None, v(y), bn.mean, bn.rstd, ds, relu_mask=mask, scratch=scratch, sync=sync)
+        if self.deterministic:
+            sync = None
+            ops.bn_bwd_reduce_det(v(dz), None, v(y), bn.mean, bn.rstd, ds, relu_mask=mask, scratch=self._det_scratch)
+        else:
+            sync = self._sync_handle(2 * bn.C)
+            ops.bn_bwd_reduce(v(dz), None, v(y), bn.mean, bn.rstd, ds, relu_mask=mask, scratch=scratch, sync=sync)
         world = self._sync_stats(ds, fused=sync is not None)
         dy = self._new(*y.shape)
         dres = self._new(*y.shape) if want_dres else None
@@ -493,7 +518,7 @@ class NativeResNetEngine:
         gradient buffer of dx's shape that the dgrad result is ADDED to in the GEMM epilogue (TMA reduction
         store) — how the two branches of a residual block are summed without a separate elementwise pass."""
         N, H, W, _ = x.shape
-        ops.conv_wgrad(x, dy, cv.dw, cv.shape(N, H, W))
+        ops.conv_wgrad(x, dy, cv.dw, cv.shape(N, H, W), splits=self._splits)
         if not need_dx:
             return None
         _, P, Q, _ = dy.shape
@@ -549,7 +574,7 @@ class NativeResNetEngine:
         dl = plan.dlogits
         N = dl.shape[0]
         self.dstats.zero_()
-        ops.conv_wgrad(pooled, dl, self.fc_dw, ConvShape(N, 1, 1, self.fc_C, self.fc_K, 1, 1, 1, 0))
+        ops.conv_wgrad(pooled, dl, self.fc_dw, ConvShape(N, 1, 1, self.fc_C, self.fc_K, 1, 1, 1, 0), splits=self._splits)
         ops.colsum16(dl, self.fc_db)
         self._ready(*self.fc_pindex[::-1])
         dpooled = self._new(N, self.fc_C)
@@ -572,12 +597,12 @@ class NativeResNetEngine:
         cv = self.stem_conv
         if col.dim() == 4:                                  # space-to-depth path
             self.stem_dws.zero_()
-            ops.stem_wgrad(col, dy0, self.stem_dws)
+            ops.stem_wgrad(col, dy0, self.stem_dws, splits=self._splits)
             ops.stem_dw_unpack(self.stem_dws, cv.dw, accumulate=True)
         else:
             rows = col.shape[0]
             ops.conv_wgrad(col, dy0.view(rows, cv.K), cv.dw, ConvShape(rows, 1, 1, STEM_KPAD, cv.K, 1, 1, 1, 0),
-                           ldw=cv.R * cv.S * cv.C, kvalid=cv.R * cv.S * cv.C)
+                           ldw=cv.R * cv.S * cv.C, kvalid=cv.R * cv.S * cv.C, splits=self._splits)
         self._ready(cv.pindex)
 
     def _segments(self):

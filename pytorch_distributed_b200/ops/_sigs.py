@@ -36,6 +36,7 @@ def declare(L):
     sig("pdb_bn_apply_eval", [P, P, P, c_int, c_int64, c_int, P, P, P, P, c_float, c_int, P])
     sig("pdb_bn_bwd_reduce", [P, P, P, P, c_int, c_int64, c_int, P, P, P, P, POINTER(SyncPeersC), P])
     sig("pdb_bn_bwd_reduce_scratch_floats", [c_int], c_size_t)
+    sig("pdb_bn_bwd_reduce_det", [P, P, P, P, c_int, c_int64, c_int, P, P, P, P, c_size_t, P])
     sig("pdb_bn_bwd_apply", [P, P, P, P, P, P, c_int, c_int64, c_int, P, P, P, P, c_double, P, P, P])
     sig("pdb_maxpool3x3s2_fwd", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])
     sig("pdb_maxpool3x3s2_bwd", [P, P, P, c_int, c_int, c_int, c_int, c_int, P])

@@ -11,7 +11,7 @@ from ._lib import check, count_launch, ptr, require, stream_ptr
 from ._sigs import ConvShape, SyncPeersC
 
 __all__ = ["dtype_tag", "sgd_step", "check_finite", "scaler_update", "cast_to_16", "xent_fwd_bwd", "topk_correct", "bn_stats",
-           "bn_apply", "bn_apply_eval", "bn_bwd_reduce", "bn_bwd_reduce_scratch_floats", "bn_bwd_apply", "maxpool_fwd", "maxpool_bwd",
+           "bn_apply", "bn_apply_eval", "bn_bwd_reduce", "bn_bwd_reduce_det", "bn_bwd_reduce_scratch_floats", "bn_bwd_apply", "maxpool_fwd", "maxpool_bwd",
            "avgpool_fwd", "avgpool_bwd", "nchw_to_nhwc16", "stem_im2col", "stem_s2d", "stem_weight_s2d", "stem_fprop",
            "stem_wgrad", "stem_dw_unpack", "add16", "upsample2_zero",
            "add_strided2", "conv_fprop", "conv_wgrad", "weight_dgrad_layout", "weight_dgrad_layout_batched", "pad_rows16", "colsum16",
@@ -145,6 +145,16 @@ def bn_bwd_reduce(dz, z, x, mean, rstd, dsums, relu_mask=None, scratch=None, syn
     rows, C = x.shape
     check(require().pdb_bn_bwd_reduce(ptr(dz), ptr(z), ptr(relu_mask), ptr(x), dtype_tag(x.dtype), rows, C, ptr(mean),
                                       ptr(rstd), ptr(dsums), ptr(scratch), _sync_ref(sync), _st(x)), "pdb_bn_bwd_reduce")
+    count_launch()
+
+
+def bn_bwd_reduce_det(dz, z, x, mean, rstd, dsums, relu_mask=None, scratch=None) -> None:
+    """Atomic-free, bit-reproducible variant (deterministic mode)."""
+    rows, C = x.shape
+    scratch = scratch if scratch is not None else bn_stats_scratch(C, x.device)
+    check(require().pdb_bn_bwd_reduce_det(ptr(dz), ptr(z), ptr(relu_mask), ptr(x), dtype_tag(x.dtype), rows, C, ptr(mean),
+                                          ptr(rstd), ptr(dsums), ptr(scratch), scratch.numel(), _st(x)),
+          "pdb_bn_bwd_reduce_det")
     count_launch()
 
 

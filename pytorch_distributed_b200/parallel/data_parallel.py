@@ -159,7 +159,7 @@ class DataParallel(nn.Module):
         self._replica_arenas.append(ParamArena(rep, device))
         self._replica_buffers.append(BufferArena(rep, device))
         if eng is not None:
-            rep.enable_native(batch_size=eng.batch_size, dtype=eng.dtype)
+            rep.enable_native(batch_size=eng.batch_size, dtype=eng.dtype, deterministic=eng.deterministic)
         self._replicas.append(rep)
 
     # -- K4b: parameter + buffer broadcast --------------------------------------------------

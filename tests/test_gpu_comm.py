@@ -72,8 +72,13 @@ def test_dp_peer_kernels():
 
 
 @pytest.mark.timeout(600)
-def test_data_parallel_native_two_gpus():
-    """DP mode with the native engine per replica: gradients are the SUM over replicas on GPU 0."""
+@pytest.mark.parametrize("dt,det", [(torch.float32, True), (torch.float16, False)])
+def test_data_parallel_native_two_gpus(dt, det):
+    """DP mode with the native engine per replica: gradients are the SUM over replicas on GPU 0
+    (ref:resnet_dp.py:24,82).  In deterministic fp32 mode every sum has a fixed order, so the two-replica result must
+    equal the sequential oracle (same two chunks through one engine) to rounding of a single addition; the fp16
+    default-mode case is held against the oracle's own run-to-run agreement (16-bit rounding makes a random-init
+    ResNet at batch 8 chaotic: see test_gpu_engine.py::test_default_mode_differs_from_deterministic_only_by_rounding_noise)."""
     import copy
     from pytorch_distributed_b200.models import resnet50
     from pytorch_distributed_b200.nn import CrossEntropyLoss
@@ -81,8 +86,8 @@ def test_data_parallel_native_two_gpus():
     torch.manual_seed(0)
     base = resnet50().cuda(0)
     ref = copy.deepcopy(base)
-    base.enable_native(batch_size=8, dtype=torch.float16)
-    ref.enable_native(batch_size=8, dtype=torch.float16)
+    base.enable_native(batch_size=8, dtype=dt, deterministic=det)
+    ref.enable_native(batch_size=8, dtype=dt, deterministic=det)
     dp = DataParallel(base, device_ids=[0, 1], output_device=0)
     x = torch.randn(16, 3, 128, 128, device="cuda:0")
     y = torch.randint(0, 1000, (16,), device="cuda:0")
@@ -100,14 +105,17 @@ def test_data_parallel_native_two_gpus():
 
     cos = torch.nn.functional.cosine_similarity
     r1, r2 = sequential(), sequential()
-    # the engine's fp32 atomics make two identical runs differ in the last bits, and 16-bit rounding amplifies
-    # that through 53 layers: the run-to-run agreement of the oracle itself is the yardstick
     noise = float(cos(r1, r2, dim=0))
     a = base._pdb200_arena.grads
     got = float(cos(a, r1, dim=0))
-    print(f"DP vs sequential cos {got:.4f}; sequential run-to-run cos {noise:.4f}")
-    assert got > noise - 0.05, (got, noise)
-    assert 0.9 < float(a.norm() / r1.norm()) < 1.1
+    print(f"[{dt}, deterministic={det}] DP vs sequential cos {got:.6f}; sequential run-to-run cos {noise:.6f}")
+    if det:
+        assert torch.equal(r1, r2)                              # the oracle is bit-reproducible
+        assert got > 0.99999, got
+        assert float((a - r1).abs().max() / r1.abs().max()) < 1e-5
+    else:
+        assert got > noise - 0.05, (got, noise)
+        assert 0.9 < float(a.norm() / r1.norm()) < 1.1
     # replica parameters follow the root on the next forward (K4b)
     with torch.no_grad():
         base.fc.bias.add_(1.0)
