@@ -347,6 +347,34 @@ struct PeerList {
   const float* p[kMaxWorld];
 };
 
+// Shard-wise gather (single process, all GPUs in one address space): shard q of the destination array is copied from
+// the same byte range of source q.  Second half of the sharded parameter replicate / gradient reduce of the
+// DataParallel mode: instead of GPU 0 sending (or receiving) n-1 full arenas, every GPU first moves / reduces ONE shard
+// and then all shards are exchanged peer to peer, so GPU 0's NVLink carries ~2/n of the bytes it carried before.
+__global__ void __launch_bounds__(256) peer_gather_kernel(uint4* __restrict__ dst, PeerList srcs, int64_t shard16,
+                                                          int64_t total16, int skip) {
+  const int q = blockIdx.y;
+  if (q == skip || srcs.p[q] == nullptr) return;
+  const int64_t lo = (int64_t)q * shard16, hi = min(lo + shard16, total16);
+  const uint4* src = reinterpret_cast<const uint4*>(srcs.p[q]);
+  constexpr int kUnroll = 8;
+  const int64_t tile = (int64_t)blockDim.x * kUnroll;
+  for (int64_t base = lo + (int64_t)blockIdx.x * tile; base < hi; base += (int64_t)gridDim.x * tile) {
+    uint4 v[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+      if (i < hi)
+        asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + i));
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t i = base + (int64_t)u * blockDim.x + threadIdx.x;
+      if (i < hi) dst[i] = v[u];
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) reduce_to_root_kernel(float* __restrict__ root, PeerList peers, int n_peers,
                                                              int64_t n4) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -528,6 +556,33 @@ extern "C" int pdb_reduce_to_root(float* root, void* const* peers, int n_peers, 
   int64_t want = (n4 + 255) / 256;
   const int grid = (int)(want < 128 ? want : 128);
   reduce_to_root_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(root, pl, n_peers, n4);
+  PDB_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int pdb_peer_gather(void* dst, void* const* srcs, int n, int64_t shard_bytes, int64_t total_bytes, int skip,
+                               void* stream) {
+  PDB_CHECK_ARG(dst && srcs && n >= 1 && n <= kMaxWorld, "pdb_peer_gather: bad arguments");
+  PDB_CHECK_ARG(shard_bytes > 0 && shard_bytes % 16 == 0 && total_bytes > 0 && total_bytes % 16 == 0,
+                "pdb_peer_gather: shard (%lld) and total (%lld) bytes must be positive multiples of 16",
+                (long long)shard_bytes, (long long)total_bytes);
+  PDB_CHECK_ARG(((uintptr_t)dst & 15) == 0, "pdb_peer_gather: dst must be 16-byte aligned");
+  int cur = 0;
+  PDB_CUDA(cudaGetDevice(&cur));
+  PeerList pl;
+  for (int i = 0; i < kMaxWorld; ++i) pl.p[i] = nullptr;
+  for (int i = 0; i < n; ++i) {
+    if (i == skip || srcs[i] == nullptr) continue;
+    PDB_CHECK_ARG(((uintptr_t)srcs[i] & 15) == 0, "pdb_peer_gather: sources must be 16-byte aligned");
+    int d = 0;
+    if (int e = device_of(srcs[i], &d)) return e;
+    if (int e = enable_peer(cur, d)) return e;
+    pl.p[i] = static_cast<const float*>(srcs[i]);
+  }
+  const int64_t shard16 = shard_bytes / 16;
+  int64_t want = (shard16 + 2047) / 2048;
+  dim3 grid((unsigned)(want < 32 ? (want > 0 ? want : 1) : 32), (unsigned)n);     // n x 32 blocks x 32 KB in flight
+  peer_gather_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((uint4*)dst, pl, shard16, total_bytes / 16, skip);
   PDB_LAUNCH_CHECK();
   return 0;
 }

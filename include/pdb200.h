@@ -281,6 +281,15 @@ int pdb_peer_pull(void* dst, const void* src, int64_t bytes, void* stream);
  * peers' arrays, read over NVLink by the root GPU. */
 int pdb_reduce_to_root(float* root, void* const* peers, int n_peers, int64_t n, void* stream);
 
+/* K4b/K4d, second half of the SHARDED replicate / reduce of the DataParallel mode: for every q < n except `skip`, bytes
+ * [q*shard_bytes, min((q+1)*shard_bytes, total_bytes)) of dst are copied from the same range of srcs[q] (the GPU of dst
+ * reads its peers).  With it, parameter replicate = "replica r pulls shard r from GPU 0, then everybody gathers the
+ * other shards from each other" and gradient reduce = "GPU r sums shard r of all replicas, then GPU 0 gathers the
+ * shards": GPU 0's links carry ~2/n of an arena per direction instead of n-1 arenas (ref:resnet_dp.py:21-25,82;
+ * delegates torch:nn/parallel/comm.py:50-168 broadcast_coalesced / reduce_add_coalesced). */
+int pdb_peer_gather(void* dst, void* const* srcs, int n, int64_t shard_bytes, int64_t total_bytes, int skip,
+                    void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,7 +35,7 @@ def pick_device(cfg: TrainConfig, local_rank: int = 0) -> torch.device:
 
 
 def to_device(batch, device: torch.device):
-    if device.type == "cuda":
+    if device.type == "cuda":      # (a PreScattered batch of the DataParallel mode already sits on its GPUs)
         return [x if x.is_cuda else x.cuda(device, non_blocking=True) for x in batch]
     return list(batch)
 
@@ -51,9 +51,14 @@ class DevicePrefetcher:
     The reference issues ``x.cuda(non_blocking=True)`` on the compute stream (ref:restnet_ddp.py:25),
     which serialises a 240 MB copy with every step."""
 
-    def __init__(self, loader, device: torch.device):
+    def __init__(self, loader, device: torch.device, dp=None):
         self.loader, self.device = loader, device
         self.stream = torch.cuda.Stream(device) if device.type == "cuda" else None
+        # DataParallel mode: the samples go from pinned host memory straight to the GPU of their replica (one PCIe link
+        # each, on a side stream per device) instead of to GPU 0 first; labels and anything else still go to GPU 0
+        self.dp = dp if (dp is not None and self.stream is not None and len(getattr(dp, "devices", [])) > 1
+                         and all(d.type == "cuda" for d in dp.devices)) else None
+        self.dp_streams = [torch.cuda.Stream(d) for d in self.dp.devices] if self.dp is not None else None
 
     def __len__(self):
         return len(self.loader)
@@ -61,10 +66,16 @@ class DevicePrefetcher:
     def _stage(self, batch):
         if self.stream is None:
             return list(batch), None
+        batch = list(batch)
+        pre = None
+        if self.dp is not None and torch.is_tensor(batch[0]) and not batch[0].is_cuda:
+            pre = self.dp.prescatter(batch[0], self.dp_streams)
         with torch.cuda.stream(self.stream):
-            out = [x.cuda(self.device, non_blocking=True) for x in batch]
+            out = [x.cuda(self.device, non_blocking=True) for x in (batch[1:] if pre is not None else batch)]
             ev = torch.cuda.Event()
             ev.record(self.stream)
+        if pre is not None:
+            out = [pre] + out
         return out, ev
 
     def __iter__(self):
@@ -82,7 +93,8 @@ class DevicePrefetcher:
             if ev is not None:
                 torch.cuda.current_stream(self.device).wait_event(ev)
                 for t in cur:
-                    t.record_stream(torch.cuda.current_stream(self.device))
+                    if torch.is_tensor(t):
+                        t.record_stream(torch.cuda.current_stream(self.device))
             yield cur
 
 
@@ -138,7 +150,7 @@ def train(dataloader, model, criterion, optimizer, scheduler, epoch: int, start_
     model.train()
     stock_autocast = getattr(checkpoint.unwrap(model), "_engine", None) is None
     last_loss = None
-    batches = DevicePrefetcher(dataloader, device) if device.type == "cuda" else dataloader
+    batches = DevicePrefetcher(dataloader, device, dp=model if cfg.mode == "dp" else None) if device.type == "cuda" else dataloader
     for step, batch in enumerate(batches):
         if step < start_step:                       # resume skip (ref:restnet_ddp.py:22-23)
             continue

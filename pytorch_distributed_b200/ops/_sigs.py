@@ -73,5 +73,6 @@ OPTIONAL = {
     "pdb_allreduce_oneshot": [P, P, P, c_int, c_int, c_int64, c_int64, c_float, P, P],
     "pdb_peer_pull": [P, P, c_int64, P],
     "pdb_reduce_to_root": [P, P, c_int, c_int64, P],
+    "pdb_peer_gather": [P, P, c_int, c_int64, c_int64, c_int, P],
     "pdb_comm_max_blocks": [c_int, c_size_t],
 }

@@ -15,7 +15,7 @@ __all__ = ["dtype_tag", "sgd_step", "check_finite", "scaler_update", "cast_to_16
            "avgpool_fwd", "avgpool_bwd", "nchw_to_nhwc16", "stem_im2col", "stem_s2d", "stem_weight_s2d", "stem_fprop",
            "stem_wgrad", "stem_dw_unpack", "add16", "upsample2_zero",
            "add_strided2", "conv_fprop", "conv_wgrad", "weight_dgrad_layout", "weight_dgrad_layout_batched", "pad_rows16", "colsum16",
-           "peer_copy", "peer_copy_", "reduce_to_root", "ConvShape", "SyncPeersC"]
+           "peer_copy", "peer_copy_", "peer_gather_", "reduce_to_root", "ConvShape", "SyncPeersC"]
 
 _TAG = {torch.bfloat16: 0, torch.float16: 1, torch.float32: 2}
 
@@ -348,4 +348,26 @@ def reduce_to_root(root: torch.Tensor, peers) -> None:
             torch.cuda.current_stream(root.device).wait_event(e)
         arr = (ctypes.c_void_p * len(peers))(*[g.data_ptr() for g in peers])
         check(require().pdb_reduce_to_root(ptr(root), arr, len(peers), root.numel(), _st(root)), "pdb_reduce_to_root")
+    count_launch()
+
+
+def peer_gather_(dst: torch.Tensor, srcs, shard_elems: int, skip: int = -1) -> None:
+    """Shard q of flat `dst` <- the same range of srcs[q] (q != skip; None entries are skipped): the GPU of dst reads
+    its peers over NVLink in ONE launch (second half of the sharded DataParallel replicate / reduce)."""
+    es = dst.element_size()
+    evs = []
+    for i, t in enumerate(srcs):
+        if t is None or i == skip:
+            continue
+        assert t.is_contiguous() and t.numel() == dst.numel() and t.dtype == dst.dtype
+        e = torch.cuda.Event()
+        e.record(torch.cuda.current_stream(t.device))
+        evs.append(e)
+    with torch.cuda.device(dst.device):
+        cur = torch.cuda.current_stream(dst.device)
+        for e in evs:
+            cur.wait_event(e)
+        arr = (ctypes.c_void_p * len(srcs))(*[0 if (t is None or i == skip) else t.data_ptr() for i, t in enumerate(srcs)])
+        check(require().pdb_peer_gather(ptr(dst), arr, len(srcs), shard_elems * es, dst.numel() * es, skip, _st(dst)),
+              "pdb_peer_gather")
     count_launch()

@@ -17,7 +17,12 @@ is computed on device 0 over the whole batch — with a different execution stra
     buffer arena — no module-tree rebuild, no per-tensor broadcast through autograd;
   * the gradient reduce-to-root is one pass over the peers' gradient arenas at the end of
     backward (K4d) — no flatten / unflatten, no 10 MiB chunking;
-  * scatter / gather are pull kernels (parallel/scatter_gather.py).
+  * with three or more GPUs both of them are SHARDED so that GPU 0 is not the bottleneck: replica r pulls shard r of
+    the parameters from GPU 0 and the replicas then gather the other shards from each other; GPU r sums shard r of
+    every replica's gradients and GPU 0 gathers the reduced shards.  GPU 0's NVLink ports carry ~2/n of an arena per
+    direction instead of n-1 arenas (8 GPUs: 0.18 GB instead of 0.71 GB each way per step);
+  * scatter / gather are pull kernels (parallel/scatter_gather.py); a batch that is still in (pinned) host memory is
+    scattered straight to the replicas' GPUs, each over its own PCIe link (`prescatter`), instead of going through GPU 0.
 """
 from __future__ import annotations
 
@@ -33,6 +38,21 @@ from torch.autograd import Variable
 from .. import amp
 from ..utils.arena import BufferArena, ParamArena
 from .scatter_gather import gather, scatter_kwargs
+
+
+class PreScattered:
+    """A batch that already lies split over the replicas' GPUs (made by ``DataParallel.prescatter``): ``forward`` uses
+    the chunks as they are.  Quacks like a tensor where the training loop needs it (``size`` / ``shape``)."""
+
+    def __init__(self, chunks, events, shape):
+        self.chunks, self.events, self.shape = chunks, events, torch.Size(shape)
+
+    def size(self, dim=None):
+        return self.shape if dim is None else self.shape[dim]
+
+    @property
+    def is_cuda(self):
+        return True
 
 
 def _dev(d) -> torch.device:
@@ -162,11 +182,51 @@ class DataParallel(nn.Module):
             rep.enable_native(batch_size=eng.batch_size, dtype=eng.dtype, deterministic=eng.deterministic)
         self._replicas.append(rep)
 
+    # -- host -> replicas without the detour through GPU 0 ----------------------------------
+    def prescatter(self, x: torch.Tensor, streams=None) -> "PreScattered":
+        """Splits a HOST batch along ``dim`` like ``scatter`` would and copies chunk i straight to GPU i (pinned memory:
+        asynchronous, one PCIe link per GPU).  The reference moves the whole global batch to GPU 0 and scatters from
+        there (ref:resnet_dp.py:24-25,69): 1.9 GB per step through one PCIe link and then out of GPU 0's NVLink ports.
+        ``streams``: optional per-device side streams (the harness prefetches the next batch during the current step)."""
+        from .scatter_gather import _chunk_sizes
+        sizes = _chunk_sizes(x.size(self.dim), len(self.devices))
+        chunks, events = [], []
+        for i, (c, d) in enumerate(zip(x.split(sizes, self.dim), self.devices)):
+            if d.type != "cuda":
+                chunks.append(c), events.append(None)
+                continue
+            st = streams[i] if streams is not None else torch.cuda.current_stream(d)
+            with torch.cuda.device(d), torch.cuda.stream(st):
+                t = c.to(d, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(st)
+            chunks.append(t), events.append(ev)
+        return PreScattered(chunks, events, x.shape)
+
     # -- K4b: parameter + buffer broadcast --------------------------------------------------
+    def _sharded(self, n: int) -> bool:
+        return n >= 3 and self.arena.params.is_cuda and _native_ok()
+
     def _replicate(self, n: int) -> None:
         src_p, src_b = self.arena.params, self.buffer_arena.storage
-        for a, b in zip(self._replica_arenas[1:n], self._replica_buffers[1:n]):
-            _flat_copy(a.params, src_p)
+        arenas = self._replica_arenas[:n]
+        if self._sharded(n):
+            from .. import ops
+            total = src_p.numel()
+            shard = ((total + n - 1) // n + 63) // 64 * 64      # elements; 256-byte aligned
+            # phase 1: replica r takes shard r from GPU 0 (GPU 0 sends each byte once) ...
+            for r in range(1, n):
+                lo, hi = r * shard, min((r + 1) * shard, total)
+                if lo < hi:
+                    ops.peer_copy_(arenas[r].params[lo:hi], src_p[lo:hi])
+            # ... phase 2: and collects the other shards from the GPUs that now hold them (shard 0 from GPU 0)
+            srcs = [a.params for a in arenas]
+            for r in range(1, n):
+                ops.peer_gather_(arenas[r].params, srcs, shard, skip=r)
+        else:
+            for a in arenas[1:]:
+                _flat_copy(a.params, src_p)
+        for a, b in zip(arenas[1:], self._replica_buffers[1:n]):
             _flat_copy(b.storage, src_b)          # fp32 statistics + int64 counters, one transfer
             a.grads.zero_()
             a.refresh_shadow()
@@ -178,6 +238,20 @@ class DataParallel(nn.Module):
         if not peers:
             return
         root = self.arena.grads
+        n = self._active
+        if self._sharded(n):
+            from .. import ops
+            grads = [a.grads for a in self._replica_arenas[:n]]
+            total = root.numel()
+            shard = ((total + n - 1) // n + 63) // 64 * 64
+            # phase 1: GPU r sums shard r of every replica into its own copy (7 remote reads of 1/n each, on n GPUs at once)
+            for r in range(n):
+                lo, hi = r * shard, min((r + 1) * shard, total)
+                if lo < hi:
+                    ops.reduce_to_root(grads[r][lo:hi], [g[lo:hi] for q, g in enumerate(grads) if q != r])
+            # phase 2: GPU 0 gathers the reduced shards 1..n-1
+            ops.peer_gather_(root, grads, shard, skip=0)
+            return
         if root.is_cuda:
             from .. import ops
             if ops.available():
@@ -194,9 +268,21 @@ class DataParallel(nn.Module):
 
     def forward(self, *inputs, **kwargs):
         with torch.autograd.profiler.record_function("pdb200.DataParallel.forward"):
+            pre = inputs[0] if inputs and isinstance(inputs[0], PreScattered) else None
             if len(self.devices) == 1:
+                if pre is not None:
+                    inputs = (pre.chunks[0],) + tuple(inputs[1:])
                 return self.module(*inputs, **kwargs)
-            s_in, s_kw = scatter_kwargs(inputs, kwargs, self.devices, self.dim)
+            if pre is not None:
+                if len(inputs) > 1 or kwargs:
+                    raise ValueError("a PreScattered batch must be the only argument")
+                for c, ev, d in zip(pre.chunks, pre.events, self.devices):
+                    if ev is not None:
+                        torch.cuda.current_stream(d).wait_event(ev)
+                        c.record_stream(torch.cuda.current_stream(d))
+                s_in, s_kw = [(c,) for c in pre.chunks], [{} for _ in pre.chunks]
+            else:
+                s_in, s_kw = scatter_kwargs(inputs, kwargs, self.devices, self.dim)
             n = len(s_in)
             self._active = n
             self.training_replicas(n)
@@ -211,6 +297,11 @@ class DataParallel(nn.Module):
         for r in self._replicas[1:n]:
             if r.training != self.module.training:
                 r.train(self.module.training)
+
+
+def _native_ok() -> bool:
+    from .. import ops
+    return ops.available() and hasattr(ops.require(), "pdb_peer_gather")
 
 
 def _flat_copy(dst: torch.Tensor, src: torch.Tensor) -> None:

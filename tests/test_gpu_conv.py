@@ -126,3 +126,25 @@ def test_stem_space_to_depth_path(shape):
     from ._gpu_helpers import stem_case
     e_y, e_s, e_w = stem_case(*shape)
     assert e_y < TOL and e_s < 1e-3 and e_w < 5e-3, (e_y, e_s, e_w)
+
+
+# The shapes bench.py actually runs (batch 400): the tile / split heuristics pick the CTA-pair kernel, the one-wave
+# split-K and the replica fold here, which the small cases above only reach through explicit block_n values.
+BENCHED = [
+    (400, 56, 56, 64, 256, 1, 1, 1, 0), (400, 56, 56, 256, 64, 1, 1, 1, 0), (400, 56, 56, 64, 64, 3, 3, 1, 1),
+    (400, 56, 56, 128, 128, 3, 3, 2, 1), (400, 28, 28, 128, 512, 1, 1, 1, 0), (400, 56, 56, 256, 512, 1, 1, 2, 0),
+    (400, 14, 14, 256, 256, 3, 3, 1, 1), (400, 14, 14, 1024, 256, 1, 1, 1, 0), (400, 7, 7, 512, 2048, 1, 1, 1, 0),
+    (400, 7, 7, 512, 512, 3, 3, 1, 1),
+]
+
+
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("case", BENCHED)
+def test_benched_shapes(case, dt):
+    N, H, W, C, K, R, S, stride, pad = case
+    tol = TOL if dt == torch.bfloat16 else TOL_TF32
+    e_y, e_s = conv_case(N, H, W, C, K, R, S, stride, pad, dtype=dt)
+    assert e_y < tol and e_s < 1e-3, ("fprop", e_y, e_s)
+    e_w = wgrad_case(N, H, W, C, K, R, S, stride, pad, dtype=dt)
+    assert e_w < (5e-3 if dt == torch.bfloat16 else TOL_TF32), ("wgrad", e_w)
+    torch.cuda.empty_cache()

@@ -225,25 +225,133 @@ def test_deterministic_mode_is_bitwise_reproducible(dt):
 
 
 def test_default_mode_differs_from_deterministic_only_by_rounding_noise():
-    """Where the 0.89 run-to-run gradient cosine of round 1's fp16 batch-8 oracle came from.  With fp32 storage the
-    default (atomics, split-K) and the deterministic engine agree to ~1e-6: the summation order is all that differs and
-    nothing races.  In fp16 the same last-bit differences flip roundings of 16-bit activations, and a random-init
-    ResNet-50 at batch 8 (layer4 BatchNorm sees 128 samples) amplifies those to a visibly different gradient —
-    chaos of the test case, not of the kernels (the deterministic fp16 engine reproduces itself bit for bit)."""
+    """Where the 0.89 run-to-run gradient cosine of round 1's fp16 batch-8 oracle came from.  The deterministic engine
+    reproduces itself bit for bit (test above), so nothing races; the default engine differs from it only in the ORDER
+    of fp32 additions (atomics, split-K), i.e. in the last bit of a few statistics.  But every activation is rounded
+    to a 10-bit mantissa on its way into the tensor cores (fp16 storage, or the TF32 conversion of fp32 storage), so a
+    last-bit difference flips roundings downstream and after a few layers the two runs carry two independent
+    realisations of the 2^-11 quantisation noise.  How far apart that puts two gradients is a property of the test
+    case, measured here on STOCK PyTorch: fp32 vs TF32 / fp16-autocast of the same model and batch.  A random-init
+    ResNet-50 at batch 8 x 128^2 (layer4 BatchNorm sees 128 samples) is that sensitive; the benched shape is not
+    (test_benched_shape_step_matches_stock_engine)."""
     torch.manual_seed(4)
     dev = torch.device("cuda")
     x = torch.randn(8, 3, 128, 128, device=dev)
     y = torch.randint(0, 1000, (8,), device=dev)
-    res = {}
+    base = resnet50().to(dev)
+
+    def stock(mode):
+        m = copy.deepcopy(base).train()
+        torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = mode == "tf32"
+        try:
+            if mode == "fp16":
+                with torch.autocast("cuda", dtype=torch.float16):
+                    loss = F.cross_entropy(m(x).float(), y)
+            else:
+                loss = F.cross_entropy(m(x), y)
+            (loss * 64.0).backward()
+        finally:
+            torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+        return torch.cat([p.grad.float().flatten() for p in m.parameters()])
+
+    g32 = stock("fp32")
+    yard = {torch.float32: _cos(stock("tf32"), g32), torch.float16: _cos(stock("fp16"), g32)}
     for dt in (torch.float32, torch.float16):
-        base = resnet50().to(dev)
         a, b = copy.deepcopy(base), copy.deepcopy(base)
         a.enable_native(batch_size=8, dtype=dt, deterministic=True)
         b.enable_native(batch_size=8, dtype=dt, deterministic=False)
         a.train(), b.train()
         (_, ga), (_, gb), (_, gb2) = _grads_of(a, x, y, 64.0), _grads_of(b, x, y, 64.0), _grads_of(b, x, y, 64.0)
-        res[dt] = (_cos(ga, gb), _cos(gb, gb2))
-        print(f"[{dt}] default vs deterministic cos {res[dt][0]:.6f}; default run-to-run cos {res[dt][1]:.6f}")
-    assert res[torch.float32][0] > 0.9999 and res[torch.float32][1] > 0.9999
-    # fp16: whatever the noise level of this chaotic case is, default-vs-deterministic is no worse than default-vs-default
-    assert res[torch.float16][0] > res[torch.float16][1] - 0.05
+        c_dd, c_rr = _cos(ga, gb), _cos(gb, gb2)
+        # arena order == parameter order, but the arena pads between tensors: compare through the views
+        gd = torch.cat([p.grad.float().flatten() for p in a.parameters()])
+        c_truth = _cos(gd, g32)
+        print(f"[{dt}] default vs deterministic cos {c_dd:.4f}; default run-to-run {c_rr:.4f}; deterministic vs stock fp32 "
+              f"{c_truth:.4f}; stock reduced-precision vs stock fp32 (sensitivity of this case) {yard[dt]:.4f}")
+        assert c_dd > yard[dt] - 0.08 and c_rr > yard[dt] - 0.08, (dt, c_dd, c_rr, yard[dt])
+        assert c_truth > yard[dt] - 0.08, (dt, c_truth, yard[dt])
+
+
+def _group_of(name: str) -> str:
+    if name.startswith("fc."):
+        return name
+    stage = name.split(".")[0] if name.startswith("layer") else "stem"
+    kind = "conv" if ("conv" in name or "downsample.0" in name) else ("gamma" if name.endswith("weight") else "beta")
+    return f"{stage}.{kind}"
+
+
+def _stock_step(base, x, y, mode, scale=1.0):
+    """Loss, logits and per-parameter gradients of the stock model in `mode` (fp32 | tf32 | torch dtype for autocast);
+    everything else it allocated is released before returning (batch 400 activations are tens of GB)."""
+    import gc
+    m = copy.deepcopy(base).train()
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = mode == "tf32"
+    try:
+        if isinstance(mode, torch.dtype):
+            with torch.autocast("cuda", dtype=mode):
+                out = m(x)
+                loss = F.cross_entropy(out.float(), y)
+        else:
+            out = m(x)
+            loss = F.cross_entropy(out, y)
+        (loss * scale).backward()
+    finally:
+        torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    res = float(loss), out.detach().float().clone(), [p.grad.float().flatten() / scale for p in m.parameters()]
+    del m, out, loss
+    gc.collect()
+    torch.cuda.empty_cache()
+    return res
+
+
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("dt", [torch.float16, torch.bfloat16, torch.float32])
+def test_benched_shape_step_matches_stock_engine(dt):
+    """One whole step at the shape bench.py times (batch 400, 224x224) — where the CTA-pair tiles, the one-wave split-K
+    heuristic and the replica folds are the variants actually selected — against the stock fp32 model: logits, loss and
+    the gradient norm / direction of every parameter group (stage x {conv, gamma, beta}, fc).  The gradient of a
+    random-init ResNet-50 on random labels is mostly rounding noise below layer4 in ANY reduced precision (stock bf16
+    autocast: cos 0.12 with fp32 for the stem), so directions are held to the stock model run in the same precision on
+    the same batch, and only where that run itself is meaningful; norms are compared everywhere.  The sharp per-kernel
+    check at these shapes is tests/test_gpu_conv.py::test_benched_shapes."""
+    import gc
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    gc.collect()
+    torch.cuda.empty_cache()
+    torch.manual_seed(5)
+    dev = torch.device("cuda")
+    base = resnet50().to(dev)
+    x = torch.randn(400, 3, 224, 224, device=dev)
+    y = torch.randint(0, 1000, (400,), device=dev)
+    loss_ref, out_ref, g_ref = _stock_step(base, x, y, "fp32")
+    _, _, g_yard = _stock_step(base, x, y, "tf32" if dt == torch.float32 else dt, 1.0 if dt == torch.float32 else 1024.0)
+    ours = copy.deepcopy(base)
+    ours.enable_native(batch_size=400, dtype=dt)
+    ours.train()
+    out = ours(x)
+    loss = CrossEntropyLoss()(out, y)
+    (loss * 1024.0).backward()                      # a loss scale, as in the amp step (keeps fp16 gradients normal)
+    torch.cuda.synchronize()
+    cos_out = _cos(out, out_ref)
+    tol_cos, tol_loss, tol_norm = {torch.float32: (0.9995, 2e-3, 0.03), torch.float16: (0.995, 1e-2, 0.1),
+                                   torch.bfloat16: (0.97, 3e-2, 0.15)}[dt]
+    print(f"[{dt} @400x224] logits cos {cos_out:.5f}; loss {float(loss):.4f} vs fp32 {loss_ref:.4f}")
+    assert cos_out > tol_cos, cos_out
+    assert abs(float(loss) - loss_ref) < tol_loss * loss_ref
+    groups = {}
+    for (n, p), q, r in zip(ours.named_parameters(), g_ref, g_yard):
+        g = groups.setdefault(_group_of(n), [[], [], []])
+        g[0].append(p.grad.float().flatten() / 1024.0), g[1].append(q), g[2].append(r)
+    bad = []
+    for name, (a, b, c3) in groups.items():
+        a, b, c3 = torch.cat(a), torch.cat(b), torch.cat(c3)
+        ratio, c, cy, ry = float(a.norm() / (b.norm() + 1e-20)), _cos(a, b), _cos(c3, b), float(c3.norm() / (b.norm() + 1e-20))
+        print(f"[{dt} @400x224] {name:14s} |g|/|g_fp32| {ratio:.4f} (stock {ry:.4f})  cos {c:.5f} (stock {cy:.5f})  "
+              f"cos(ours, stock same precision) {_cos(a, c3):.5f}")
+        if abs(ratio - 1.0) > max(tol_norm, 1.5 * abs(ry - 1.0)) or (cy > 0.9 and c < cy - 0.03):
+            bad.append((name, ratio, c, ry, cy))
+    assert not bad, bad
+    del ours, out, loss, groups
+    gc.collect()
+    torch.cuda.empty_cache()
