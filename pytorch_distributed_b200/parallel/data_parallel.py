@@ -205,7 +205,9 @@ class DataParallel(nn.Module):
 
     # -- K4b: parameter + buffer broadcast --------------------------------------------------
     def _sharded(self, n: int) -> bool:
-        return n >= 3 and self.arena.params.is_cuda and _native_ok()
+        import os
+        # (two GPUs: the sharded scheme moves the same bytes as the direct one; PDB200_DP_SHARD_MIN=2 forces it for tests)
+        return n >= int(os.environ.get("PDB200_DP_SHARD_MIN", "3")) and self.arena.params.is_cuda and _native_ok()
 
     def _replicate(self, n: int) -> None:
         src_p, src_b = self.arena.params, self.buffer_arena.storage

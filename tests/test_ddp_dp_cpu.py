@@ -109,3 +109,16 @@ def test_data_parallel_balance_warning(monkeypatch):
     props[1] = props[0]
     assert dpm.check_balance(devs) is None
     assert dpm.check_balance([torch.device("cpu"), torch.device("cpu")]) is None
+
+
+def test_data_parallel_accepts_a_prescattered_batch():
+    """`prescatter` splits like `scatter` does; forward on the pre-split batch gives the same output as on the tensor."""
+    torch.manual_seed(0)
+    m = ResNet((1, 1, 1, 1), num_classes=10, width=8)
+    dp = DataParallel(m, device_ids=["cpu", "cpu", "cpu"])
+    x = torch.randn(7, 3, 32, 32)                       # 3 + 3 + 1: uneven chunks
+    pre = dp.prescatter(x)
+    assert [c.size(0) for c in pre.chunks] == [3, 3, 1] and pre.size(0) == 7 and tuple(pre.shape) == tuple(x.shape)
+    dp.eval()
+    with torch.no_grad():
+        assert torch.allclose(dp(pre), dp(x), rtol=1e-5, atol=1e-6)

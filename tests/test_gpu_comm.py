@@ -72,8 +72,8 @@ def test_dp_peer_kernels():
 
 
 @pytest.mark.timeout(600)
-@pytest.mark.parametrize("dt,det", [(torch.float32, True), (torch.float16, False)])
-def test_data_parallel_native_two_gpus(dt, det):
+@pytest.mark.parametrize("dt,det,shard_min", [(torch.float32, True, "3"), (torch.float32, True, "2"), (torch.float16, False, "3")])
+def test_data_parallel_native_two_gpus(dt, det, shard_min, monkeypatch):
     """DP mode with the native engine per replica: gradients are the SUM over replicas on GPU 0
     (ref:resnet_dp.py:24,82).  In deterministic fp32 mode every sum has a fixed order, so the two-replica result must
     equal the sequential oracle (same two chunks through one engine) to rounding of a single addition; the fp16
@@ -83,6 +83,7 @@ def test_data_parallel_native_two_gpus(dt, det):
     from pytorch_distributed_b200.models import resnet50
     from pytorch_distributed_b200.nn import CrossEntropyLoss
     from pytorch_distributed_b200.parallel import DataParallel
+    monkeypatch.setenv("PDB200_DP_SHARD_MIN", shard_min)       # "2": the sharded replicate / reduce on two GPUs
     torch.manual_seed(0)
     base = resnet50().cuda(0)
     ref = copy.deepcopy(base)
@@ -91,7 +92,8 @@ def test_data_parallel_native_two_gpus(dt, det):
     dp = DataParallel(base, device_ids=[0, 1], output_device=0)
     x = torch.randn(16, 3, 128, 128, device="cuda:0")
     y = torch.randint(0, 1000, (16,), device="cuda:0")
-    out = dp(x)
+    # the batch comes from pinned host memory, each half straight to its GPU (what harness.train does in dp mode)
+    out = dp(dp.prescatter(x.cpu().pin_memory()))
     assert out.shape == (16, 1000) and out.device.index == 0
     (CrossEntropyLoss()(out, y) * 2 * 64).backward()          # mean over 16 rows (x64: keep fp16 grads normal)
     torch.cuda.synchronize()
