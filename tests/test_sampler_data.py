@@ -133,3 +133,26 @@ def test_hfai_shim_reads_real_data_when_a_root_is_configured(tmp_path, monkeypat
     monkeypatch.setenv("PDB200_DATA_ROOT", str(tmp_path))
     ds = hfai.datasets.ImageNet("val", transform=transforms.val_transform(8))
     assert type(ds).__name__ == "ImageFolder" and len(ds) == 4
+
+
+def test_folder_loader_worker_processes_match_worker_threads(tmp_path):
+    """num_workers decode PROCESSES (the default, like the reference's DataLoader workers) write into shared batch
+    buffers; they must deliver exactly what the in-process thread pool delivers, epoch after epoch."""
+    from pytorch_distributed_b200.data import ImageNet
+    _make_image_tree(tmp_path)
+    tr = ImageNet("train", transform=transforms.train_transform(16), synthetic=False, root=str(tmp_path))
+    lp = tr.loader(batch_size=4, num_workers=2, pin_memory=False, shuffle=True)
+    lt = tr.loader(batch_size=4, num_workers=2, pin_memory=False, shuffle=True, workers="thread")
+    assert lp.workers == "process" and lt.workers == "thread"
+    try:
+        for epoch in range(2):
+            tr.set_epoch(epoch)
+            got = [(x.clone(), y.clone()) for x, y in lp]            # batches are views of a ring: copy before the next one
+            want = list(lt)
+            assert len(got) == len(want) == 4
+            for (x, y), (xr, yr) in zip(got, want):
+                assert torch.equal(y, yr) and torch.equal(x, xr)
+        assert lp._pool is not None and all(p.is_alive() for p in lp._pool.procs)      # persistent across epochs
+    finally:
+        lp.close()
+    assert lp._pool is None
