@@ -62,15 +62,27 @@ def main():
         def run_native():
             comm.allreduce_range(buf, 0, n, average=True)
             comm.wait_all()
+        one_shot_default = 4 * n <= comm.oneshot_bytes
+        if 4 * n <= (1 << 20):            # the one-shot kernel (the default up to 256 KB) against the two-shot ones
+            keep = comm.oneshot_bytes
+            comm.oneshot_bytes = 1 << 20
+            ms = timed(run_native, iters, dev)
+            comm.oneshot_bytes = keep
+            rec["oneshot_us"] = round(ms * 1e3, 2)
+            rec["oneshot_busbw_GBs"] = round(2 * (world - 1) / world * n * 4 / (ms * 1e-3) / 1e9, 1)
+        rec["default_algo"] = "oneshot" if one_shot_default else ("nvls" if has_mc else "p2p")
+        keep = comm.oneshot_bytes
+        comm.oneshot_bytes = 0            # force the two-shot kernels for the p2p / nvls columns
         for mode in (["p2p", "nvls"] if has_mc else ["p2p"]):
             comm.use_multicast = mode == "nvls"
             ms = timed(run_native, iters, dev)
             rec[f"{mode}_us"] = round(ms * 1e3, 2)
             rec[f"{mode}_busbw_GBs"] = round(2 * (world - 1) / world * n * 4 / (ms * 1e-3) / 1e9, 1)
+        comm.oneshot_bytes = keep
         ms = timed(lambda: dist.all_reduce(plain[:n]), iters, dev)
         rec["nccl_us"] = round(ms * 1e3, 2)
         rec["nccl_busbw_GBs"] = round(2 * (world - 1) / world * n * 4 / (ms * 1e-3) / 1e9, 1)
-        best = max(rec.get("p2p_busbw_GBs", 0), rec.get("nvls_busbw_GBs", 0))
+        best = max(rec.get("p2p_busbw_GBs", 0), rec.get("nvls_busbw_GBs", 0), rec.get("oneshot_busbw_GBs", 0))
         rec["roofline_frac_of_770GBs"] = round(best / 770.0, 3)
         rows.append(rec)
         if rank == 0:
