@@ -93,7 +93,7 @@ def main():
         t = by_tag.setdefault(tag, [0, 0.0, 0.0])
         t[0] += 1; t[1] += ms; t[2] += flops
     total = a0.elapsed_time(a1)
-    out = {"batch": args.batch, "step_ms_serialised": total, "launches": len(records),
+    out = {"batch": args.batch, "dtype": args.dtype, "step_ms_serialised": total, "launches": len(records),
            "by_class": {k: {"n": v[0], "ms": round(v[1], 3), "tflops": round(v[2] / v[1] / 1e9, 1) if v[1] > 0 and v[2] > 0 else None}
                         for k, v in sorted(by_class.items(), key=lambda kv: -kv[1][1])},
            "by_shape": {k: {"n": v[0], "ms": round(v[1], 3),

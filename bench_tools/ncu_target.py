@@ -1,5 +1,9 @@
 """Short single-GPU program for ncu captures: runs one kernel family a few times on a real ResNet-50 shape
-at batch 400.   python bench_tools/ncu_target.py {fprop|wgrad|bn|step}"""
+at batch 400.   python bench_tools/ncu_target.py {fprop|wgrad|bn|step|fprop_tf32|wgrad_tf32|comm}
+
+`comm`: the cross-GPU kernels launched with world = 1 (one buffer, one signal pad: the meetings are trivially met, the
+data path is the real one) — ncu replays every kernel ~40 times, which a kernel that waits for a peer cannot survive,
+but a loopback launch can; it also puts allreduce_kernel & co. into a single-GPU launch census."""
 import os
 import sys
 
@@ -38,7 +42,27 @@ def main():
         for _ in range(4):
             ops.stem_fprop(xs, ws, y, stats=st, stats_scratch=scr)
             ops.stem_wgrad(xs, dy, dws)
-    elif what in ("fprop", "wgrad"):
+    elif what == "comm":
+        import ctypes
+        from pytorch_distributed_b200.ops._lib import check, require
+        L = require()
+        n = 7875584                                   # the largest ResNet-50 DDP bucket (31.5 MB)
+        buf = torch.randn(n, device="cuda")
+        pad = torch.zeros(64 * 16, dtype=torch.int32, device="cuda")
+        flag = torch.zeros(64, device="cuda")
+        stage = torch.zeros(2 * 8192, device="cuda")
+        arr = lambda t: (ctypes.c_void_p * 1)(t.data_ptr())        # noqa: E731
+        st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        inv = torch.tensor(1.0 / 1024, device="cuda")
+        small = torch.randn(4096, device="cuda")
+        for _ in range(3):
+            check(L.pdb_allreduce_inplace(arr(buf), arr(pad), arr(flag), None, 0, 1, 0, n, 1.0, ctypes.c_void_p(inv.data_ptr()), 32, st), "allreduce")
+            check(L.pdb_allreduce_oneshot(arr(buf), arr(pad), arr(flag), 0, 1, 0, 65536, 1.0, ctypes.c_void_p(inv.data_ptr()), st), "oneshot")
+            check(L.pdb_broadcast_inplace(arr(buf), arr(pad), 0, 1, 0, 0, 53120, 4, st), "broadcast")
+            check(L.pdb_small_allreduce(arr(stage), arr(pad), 0, 1, ctypes.c_void_p(small.data_ptr()), 4096, 8192, st), "small")
+    elif what in ("fprop", "wgrad", "fprop_tf32", "wgrad_tf32"):
+        if what.endswith("_tf32"):
+            what, dt = what[:-5], torch.float32
         H, C, K, R = 14, 256, 256, 3
         x = torch.randn(N, H, H, C, device="cuda", dtype=dt)
         sh = ConvShape(N, H, H, C, K, R, R, 1, 1)

@@ -175,6 +175,7 @@ def train(dataloader, model, criterion, optimizer, scheduler, epoch: int, start_
             extra = {"buckets": ddp_comm.bucket_times()} if hasattr(ddp_comm, "bucket_times") else {}
             if logger is not None and logger.enabled:
                 logger.log(event="step_time", epoch=epoch, step=step, ms=ms,
+                           world=comm.get_world_size() if cfg.mode in ("ddp", "ddp_amp") else 1,
                            images_per_s=samples.size(0) * max(1, comm.get_world_size() if cfg.mode in ("ddp", "ddp_amp") else 1) / (ms / 1e3),
                            **extra)
 
