@@ -90,11 +90,11 @@ def comm_table(path, link=770.0):
     out = [f"## Collectives ({w} GPUs, idle-GPU sweep, `{os.path.relpath(path, ROOT)}`)", "",
            f"Bus bandwidth = 2(w-1)/w x bytes / device time (max over ranks), against the measured {link:.0f} GB/s per NVLink direction.  "
            "`default`: the algorithm `NativeComm.allreduce_range` picks for that size.", "",
-           "| message | kind | one-shot us | P2P two-shot us | NVLS us | NCCL us | default | best bus GB/s | of link roofline |", "|---|---|---|---|---|---|---|---|---|"]
+           "| message | kind | one-shot us | P2P two-shot us | NVLS us | NCCL us | default | default kernel alone us | best bus GB/s | of link roofline |", "|---|---|---|---|---|---|---|---|---|---|"]
     for r in d["rows"]:
-        best = max(r.get("p2p_busbw_GBs", 0), r.get("nvls_busbw_GBs", 0), r.get("oneshot_busbw_GBs", 0))
+        best = max(r.get("p2p_busbw_GBs", 0), r.get("nvls_busbw_GBs", 0), r.get("oneshot_busbw_GBs", 0), r.get("default_kernel_busbw_GBs", 0))
         out.append(f"| {r['bytes'] / 1e6:.2f} MB | {'DDP bucket' if r['bucket'] else 'sweep'} | {r.get('oneshot_us', '')} | {r.get('p2p_us', '')} | "
-                   f"{r.get('nvls_us', '')} | {r['nccl_us']} | {r.get('default_algo', '')} | {best:.0f} | {best / link:.2f} |")
+                   f"{r.get('nvls_us', '')} | {r['nccl_us']} | {r.get('default_algo', '')} | {r.get('default_kernel_us', '')} | {best:.0f} | {best / link:.2f} |")
     return out + [""]
 
 

@@ -136,12 +136,20 @@ class BatchLoader:
         y = torch.empty(b, dtype=torch.int64, pin_memory=self.pin_memory)
         return x, y
 
-    def _assemble(self, idx: torch.Tensor, out=None):
+    def _assemble(self, idx: torch.Tensor, out=None, pool=None):
         ds = self.dataset
         x, y = out if out is not None else self._alloc(idx.numel())
         x, y = x[: idx.numel()], y[: idx.numel()]
         if ds.transform is None:
-            torch.index_select(ds._pool_images(), 0, idx % ds.pool, out=x)
+            src, sel = ds._pool_images(), idx % ds.pool
+            if pool is None or idx.numel() < 64:
+                torch.index_select(src, 0, sel, out=x)
+            else:
+                # a 400-image batch is 240 MB: one thread copies it in ~25 ms, the engine consumes one every 28 ms —
+                # split the gather over the worker threads (index_select releases the GIL)
+                n, w = idx.numel(), self.num_workers
+                per = -(-n // w)
+                list(pool.map(lambda a: torch.index_select(src, 0, sel[a:a + per], out=x[a:a + per]), range(0, n, per)))
         else:
             for k, i in enumerate(idx.tolist()):
                 x[k] = ds[i][0]
@@ -149,11 +157,11 @@ class BatchLoader:
         return x, y
 
     def _iter_ring(self) -> Iterator:
-        if self._ring is None:
+        if getattr(self, "_fixed_ring", None) is None:
             base = torch.arange(self.batch_size)
-            self._ring = [self._assemble(base + k * self.batch_size) for k in range(self.ring_size)]
+            self._fixed_ring = [self._assemble(base + k * self.batch_size) for k in range(self.ring_size)]
         for k in range(len(self)):
-            yield self._ring[k % self.ring_size]
+            yield self._fixed_ring[k % self.ring_size]
 
     def _iter_gather(self) -> Iterator:
         index = self._index_tensor()
@@ -162,12 +170,19 @@ class BatchLoader:
         stop = threading.Event()
 
         def work():
+            # Pinned batch buffers are allocated ONCE and recycled: a cudaHostAlloc of 240 MB per step costs more than
+            # the step.  The queue holds <= prefetch batches, the consumer one, one more may still be in its H2D copy,
+            # and the producer fills one: prefetch + 3 slots.
+            from concurrent.futures import ThreadPoolExecutor
             try:
-                for b in range(nb):
-                    if stop.is_set():
-                        return
-                    idx = index[b * self.batch_size: (b + 1) * self.batch_size]
-                    q.put(self._assemble(idx))
+                if self._ring is None or len(self._ring) < self.prefetch + 3 or self._ring[0][0].shape[0] != self.batch_size:
+                    self._ring = [self._alloc(self.batch_size) for _ in range(self.prefetch + 3)]
+                with ThreadPoolExecutor(max(1, self.num_workers), thread_name_prefix="pdb200-gather") as pool:
+                    for b in range(nb):
+                        if stop.is_set():
+                            return
+                        idx = index[b * self.batch_size: (b + 1) * self.batch_size]
+                        q.put(self._assemble(idx, out=self._ring[b % len(self._ring)], pool=pool))
                 q.put(None)
             except BaseException as e:  # surface worker errors in the consumer
                 q.put(e)
