@@ -137,6 +137,14 @@ def make_comm(backend: str = "auto", group=None):
         return TorchComm(group)
     want_native = backend == "native"
     if torch.cuda.is_available() and is_initialized() and dist.get_backend(group) == "nccl" \
+            and dist.get_world_size(group) > torch.cuda.device_count() and not want_native:
+        # More ranks than local GPUs: the job spans hosts (the reference's "Apex * 4" run).  Peer memory and NVLS end at
+        # the NVSwitch domain, so the gradient path of a multi-node job is NCCL; this is a decision, not a fallback.
+        import warnings
+        warnings.warn("pdb200: multi-node job — gradient all-reduce goes through NCCL (the native peer-memory backend "
+                      "covers one NVSwitch domain)")
+        return TorchComm(group)
+    if torch.cuda.is_available() and is_initialized() and dist.get_backend(group) == "nccl" \
             and dist.get_world_size(group) > 1:
         try:
             from .symm import NativeComm
