@@ -243,11 +243,23 @@ __global__ void __launch_bounds__(kThreads, 3) bn_bwd_reduce_kernel(const T* __r
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
-    float acc = 0.f;
+  if (((reinterpret_cast<uintptr_t>(dsums) | reinterpret_cast<uintptr_t>(rep)) & 15) == 0) {      // C % 8 == 0 always
+    for (int c4 = threadIdx.x; c4 < C / 2; c4 += blockDim.x) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-    for (int r = 0; r < kReduceReplicas; ++r) acc += __ldcg(rep + (size_t)r * 2 * C + c);
-    dsums[c] = acc;
+      for (int r = 0; r < kReduceReplicas; ++r) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(rep + (size_t)r * 2 * C) + c4);
+        a.x += v.x, a.y += v.y, a.z += v.z, a.w += v.w;
+      }
+      reinterpret_cast<float4*>(dsums)[c4] = a;
+    }
+  } else {
+    for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
+      float acc = 0.f;
+#pragma unroll
+      for (int r = 0; r < kReduceReplicas; ++r) acc += __ldcg(rep + (size_t)r * 2 * C + c);
+      dsums[c] = acc;
+    }
   }
   // SyncBatchNorm backward (torch:nn/modules/_functions.py:126-209 all-reduces [sum_dy, sum_dy_xmu]): the block that
   // folded the replicas exchanges the [2C] sums with its peers right here — no extra launch, one cross-GPU meeting
