@@ -106,15 +106,24 @@ def step_table(path, link=770.0):
     steps = steps[len(steps) // 2:]                    # the second half: CUDA graphs are warm
     nb = len(steps[0]["buckets"])
     out = [f"## Gradient buckets inside the training step (`{os.path.relpath(path, ROOT)}`, mean of {len(steps)} warm steps)", "",
-           "Event pairs around every bucket's all-reduce on the comm stream while backward keeps running on the compute stream: "
-           "the time includes waiting for the slowest rank at the kernel's first meeting and sharing SMs / HBM with backward.", "",
-           "| bucket | MB | in-step us | bus GB/s | of link roofline |", "|---|---|---|---|---|"]
+           "Every bucket's all-reduce runs on the comm stream while backward keeps running on the compute stream.  `event us`: CUDA "
+           "events around the launch.  The kernel also stamps the GPU's global timer at entry, after its first cross-rank meeting and "
+           "at exit: `wait us` is the time until the SLOWEST rank's backward has reached this bucket (not communication), `collective "
+           "us` is reduce-scatter + all-gather + the closing meeting, sharing SMs and HBM with the backward kernels; the roofline "
+           "fraction is taken on that part.", "",
+           "| bucket | MB | event us | wait us | collective us | collective bus GB/s | of link roofline |", "|---|---|---|---|---|---|---|"]
     for b in range(nb):
-        us = sum(s["buckets"][b]["us"] for s in steps) / len(steps)
+        mean = lambda k: sum(s["buckets"][b].get(k, 0.0) for s in steps) / len(steps)          # noqa: E731
+        us = mean("us")
         by = steps[0]["buckets"][b]["bytes"]
         world = steps[0].get("world", 8)
-        bus = 2.0 * (world - 1) / world * by / us / 1e3
-        out.append(f"| {b} | {by / 1e6:.2f} | {us:.1f} | {bus:.0f} | {bus / link:.2f} |")
+        if "xfer_us" in steps[0]["buckets"][b]:
+            xf = mean("xfer_us")
+            bus = 2.0 * (world - 1) / world * by / xf / 1e3
+            out.append(f"| {b} | {by / 1e6:.2f} | {us:.1f} | {mean('wait_us'):.1f} | {xf:.1f} | {bus:.0f} | {bus / link:.2f} |")
+        else:
+            bus = 2.0 * (world - 1) / world * by / us / 1e3
+            out.append(f"| {b} | {by / 1e6:.2f} | {us:.1f} | | | {bus:.0f} (whole event) | {bus / link:.2f} |")
     ms = sum(s["ms"] for s in steps) / len(steps)
     out += ["", f"Step time (device, max over ranks) in the same run: {ms:.2f} ms.", ""]
     return out

@@ -55,11 +55,16 @@ __device__ __forceinline__ void multimem_st(float* mc, const float4& v) {
 
 // Two-shot in-place all-reduce of elements [start, start + n) of every rank's buffer.
 // kMulticast: reduce and broadcast through the NVLS multicast address `mc` instead of per-peer loads/stores.
+// trace (nullable): block 0 stamps the global timer at entry, after the first meeting and at exit — inside a training
+// step the first interval is the wait for the slowest rank's backward, the second is the collective itself.
 template <bool kMulticast>
 __global__ void __launch_bounds__(kCommThreads) allreduce_kernel(PeerPtrs pp, float* mc, int rank, int world,
                                                                  int64_t start, int64_t n, float scale,
-                                                                 const float* __restrict__ inv_scale) {
+                                                                 const float* __restrict__ inv_scale,
+                                                                 unsigned long long* __restrict__ trace) {
+  if (trace && blockIdx.x == 0 && threadIdx.x == 0) trace[0] = globaltimer_ns();
   cross_rank_barrier(pp.pad, rank, world);            // everybody's gradients for this range are final
+  if (trace && blockIdx.x == 0 && threadIdx.x == 0) trace[1] = globaltimer_ns();
   const float s = scale * (inv_scale ? *inv_scale : 1.0f);
   // shard r = [lo, hi) in units of float4, split evenly
   const int64_t n4 = n / 4;
@@ -129,6 +134,7 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_kernel(PeerPtrs pp, fl
   }
   __threadfence_system();
   cross_rank_barrier(pp.pad, rank, world);            // all shards have landed everywhere
+  if (trace && blockIdx.x == 0 && threadIdx.x == 0) trace[2] = globaltimer_ns();
 }
 
 // ---- 16-bit wire variant (fp16_compress / bf16_compress hooks, default_comm_hooks.hpp:9-34) -------------------
@@ -402,6 +408,18 @@ static int fill_peers(PeerPtrs* pp, void* const* bufs, void* const* pads, void* 
 }  // namespace pdb
 using namespace pdb;
 
+// --profile: a device buffer of 3 x capacity uint64 that successive pdb_allreduce_inplace launches stamp (see
+// allreduce_kernel); null switches tracing off.  Returns the number of launches traced so far into the previous buffer.
+static unsigned long long* g_trace = nullptr;
+static int g_trace_cap = 0, g_trace_next = 0;
+extern "C" int pdb_comm_set_trace(void* buf, int capacity) {
+  const int used = g_trace_next;
+  g_trace = static_cast<unsigned long long*>(buf);
+  g_trace_cap = buf ? capacity : 0;
+  g_trace_next = 0;
+  return used;
+}
+
 extern "C" int pdb_comm_max_blocks(int world, size_t signal_pad_bytes) {
   const size_t slots = signal_pad_bytes / sizeof(uint32_t);
   int b = (int)(slots / (size_t)(world > 0 ? world : 1));
@@ -420,10 +438,12 @@ extern "C" int pdb_allreduce_inplace(void* const* bufs, void* const* pads, void*
   PeerPtrs pp;
   if (int e = fill_peers(&pp, bufs, pads, flags, world)) return e;
   cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long* tr = nullptr;
+  if (g_trace && g_trace_next < g_trace_cap) tr = g_trace + 3 * (g_trace_next++);
   if (multicast)
-    allreduce_kernel<true><<<blocks, kCommThreads, 0, st>>>(pp, static_cast<float*>(multicast), rank, world, start, n, scale, inv_scale);
+    allreduce_kernel<true><<<blocks, kCommThreads, 0, st>>>(pp, static_cast<float*>(multicast), rank, world, start, n, scale, inv_scale, tr);
   else
-    allreduce_kernel<false><<<blocks, kCommThreads, 0, st>>>(pp, nullptr, rank, world, start, n, scale, inv_scale);
+    allreduce_kernel<false><<<blocks, kCommThreads, 0, st>>>(pp, nullptr, rank, world, start, n, scale, inv_scale, tr);
   PDB_LAUNCH_CHECK();
   return 0;
 }

@@ -243,6 +243,11 @@ int pdb_colsum16(const void* a, float* out, int dtype, int rows, int cols, void*
  * same `blocks` (<= pdb_comm_max_blocks); kernels of different ranks wait for each other, so each rank
  * needs its own GPU.  Spins are bounded (20 s) and trap. */
 int pdb_comm_max_blocks(int world, size_t signal_pad_bytes);
+/* Profiling aid: buf = device array of 3 x capacity uint64.  While set, launch i of pdb_allreduce_inplace
+ * stamps buf[3i..3i+2] with the GPU's global timer (ns) at kernel entry, after the first cross-rank meeting, and at exit:
+ * inside a training step the first interval is the wait for the slowest rank, the second the collective itself.
+ * buf = NULL switches it off.  Returns how many launches were traced into the previously set buffer. */
+int pdb_comm_set_trace(void* buf, int capacity);
 
 /* K1 (ref:restnet_ddp.py:29 loss.backward() -> Reducer all_reduce_bucket -> ncclAllReduce): in-place
  * all-reduce of fp32 elements [start, start+n) of every rank's buffer: reduce-scatter by P2P loads (or

@@ -75,4 +75,5 @@ OPTIONAL = {
     "pdb_reduce_to_root": [P, P, c_int, c_int64, P],
     "pdb_peer_gather": [P, P, c_int, c_int64, c_int64, c_int, P],
     "pdb_comm_max_blocks": [c_int, c_size_t],
+    "pdb_comm_set_trace": [P, c_int],
 }

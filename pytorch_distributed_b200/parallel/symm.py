@@ -83,6 +83,8 @@ class NativeComm:
         # --profile: an event pair around every bucket's kernel (per-bucket bus GB/s in the JSONL log)
         self.profile = False
         self._bucket_marks: List[tuple] = []
+        self._trace: Optional[torch.Tensor] = None
+        self._trace_read = 0
         torch.cuda.synchronize(self.device)
         dist.barrier(group)
 
@@ -193,6 +195,12 @@ class NativeComm:
                     self._bucket_marks.append((4 * n, t0, done))
                 self._events.append(done)
                 return
+            if t0 is not None and self._trace is None and hasattr(require(), "pdb_comm_set_trace"):
+                # in-kernel timestamps (entry / after the first meeting / exit) for every two-shot launch from now on
+                self._trace = torch.zeros(3 * 4096, dtype=torch.int64, device=self.device)
+                require().pdb_comm_set_trace(ptr(self._trace), 4096)
+                self._trace_read = 0
+            traced = t0 is not None and self._trace is not None
             check(require().pdb_allreduce_inplace(
                 m.bufs, m.pads, self._flag_ptrs if found_inf is not None else None,
                 ctypes.c_void_p(m.multicast if self.use_multicast else 0), self.rank, self.world, start, n,
@@ -202,7 +210,7 @@ class NativeComm:
             done = torch.cuda.Event(enable_timing=t0 is not None)
             done.record(self.stream)
             if t0 is not None:
-                self._bucket_marks.append((4 * n, t0, done))
+                self._bucket_marks.append((4 * n, t0, done, traced))
         self._events.append(done)
 
     def bucket_times(self, link_gbs: float = 770.0):
@@ -210,12 +218,25 @@ class NativeComm:
         step): bytes, microseconds, bus bandwidth 2(w-1)/w * bytes / t, and its fraction of the NVLink roofline.
         In-step numbers include waiting for the slowest rank at the kernel's first cross-rank barrier."""
         out = []
-        for nbytes, t0, t1 in self._bucket_marks:
+        stamps = None
+        for mark in self._bucket_marks:
+            nbytes, t0, t1 = mark[:3]
             t1.synchronize()
             us = 1e3 * t0.elapsed_time(t1)
             bus = 2.0 * (self.world - 1) / self.world * nbytes / max(us, 1e-3) / 1e3        # GB/s
-            out.append({"bytes": nbytes, "us": round(us, 1), "bus_gbs": round(bus, 1),
-                        "roofline_frac": round(bus / link_gbs, 3)})
+            rec = {"bytes": nbytes, "us": round(us, 1), "bus_gbs": round(bus, 1), "roofline_frac": round(bus / link_gbs, 3)}
+            if len(mark) > 3 and mark[3] and self._trace is not None and self._trace_read < 4096:
+                # the kernel's own clock: how long it waited for the slowest rank, and how long the collective itself took
+                if stamps is None:
+                    stamps = self._trace.view(-1, 3).cpu()
+                a, b, c = (int(v) for v in stamps[self._trace_read])
+                self._trace_read += 1
+                if a and b >= a and c >= b:
+                    xfer = (c - b) / 1e3
+                    xbus = 2.0 * (self.world - 1) / self.world * nbytes / max(xfer, 1e-3) / 1e3
+                    rec.update(wait_us=round((b - a) / 1e3, 1), xfer_us=round(xfer, 1), xfer_bus_gbs=round(xbus, 1),
+                               xfer_roofline_frac=round(xbus / link_gbs, 3))
+            out.append(rec)
         self._bucket_marks.clear()
         return out
 
