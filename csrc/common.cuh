@@ -107,25 +107,56 @@ template <typename T>
 struct V8 {
   uint4 q[sizeof(T) / 2];
 };
+// fp32: ONE 256-bit access per lane (sm_100 has LDG.256 / STG.256).  Two 128-bit accesses per lane touch every 32-byte
+// sector twice with half of it used each time; with the no-allocate hint the second touch goes back to L2, i.e. twice
+// the L2->SM sectors of the 16-bit kernels for the same bytes (the fp32 BatchNorm passes ran at 5.4 TB/s where the
+// 16-bit ones reach 6.3).  Needs 32-byte aligned addresses: the entry points check that for PDB_FP32.
 template <typename T>
 __device__ __forceinline__ V8<T> ld8(const T* p) {
   V8<T> v;
-#pragma unroll
-  for (int j = 0; j < (int)sizeof(T) / 2; ++j) v.q[j] = __ldg(reinterpret_cast<const uint4*>(p) + j);
+  if constexpr (sizeof(T) == 4) {
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v.q[0].x), "=r"(v.q[0].y), "=r"(v.q[0].z), "=r"(v.q[0].w), "=r"(v.q[1].x), "=r"(v.q[1].y), "=r"(v.q[1].z), "=r"(v.q[1].w)
+                 : "l"(p));
+  } else {
+    v.q[0] = __ldg(reinterpret_cast<const uint4*>(p));
+  }
   return v;
 }
 template <typename T>
 __device__ __forceinline__ V8<T> ld8s(const T* p) {           // streaming (read-once) variant
   V8<T> v;
-#pragma unroll
-  for (int j = 0; j < (int)sizeof(T) / 2; ++j) v.q[j] = ldg128_stream(reinterpret_cast<const uint4*>(p) + j);
+  if constexpr (sizeof(T) == 4) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v.q[0].x), "=r"(v.q[0].y), "=r"(v.q[0].z), "=r"(v.q[0].w), "=r"(v.q[1].x), "=r"(v.q[1].y), "=r"(v.q[1].z), "=r"(v.q[1].w)
+                 : "l"(p));
+  } else {
+    v.q[0] = ldg128_stream(reinterpret_cast<const uint4*>(p));
+  }
   return v;
 }
 template <typename T>
 __device__ __forceinline__ void st8(T* p, const V8<T>& v) {
-#pragma unroll
-  for (int j = 0; j < (int)sizeof(T) / 2; ++j) reinterpret_cast<uint4*>(p)[j] = v.q[j];
+  if constexpr (sizeof(T) == 4) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v.q[0].x), "r"(v.q[0].y), "r"(v.q[0].z), "r"(v.q[0].w),
+                 "r"(v.q[1].x), "r"(v.q[1].y), "r"(v.q[1].z), "r"(v.q[1].w)
+                 : "memory");
+  } else {
+    reinterpret_cast<uint4*>(p)[0] = v.q[0];
+  }
 }
+// fp32 activations are accessed 256 bits at a time: every activation pointer of such a call must be 32-byte aligned
+#define PDB_CHECK_ALIGN32(dtype, who, ...)                                                                        \
+  do {                                                                                                            \
+    if ((dtype) == PDB_FP32) {                                                                                    \
+      const void* ptrs__[] = {__VA_ARGS__};                                                                       \
+      for (const void* q__ : ptrs__)                                                                              \
+        if ((reinterpret_cast<uintptr_t>(q__) & 31) != 0) {                                                        \
+          ::pdb::set_error("%s: fp32 activations must be 32-byte aligned (256-bit accesses), got %p", who, q__);  \
+          return 1;                                                                                               \
+        }                                                                                                         \
+    }                                                                                                             \
+  } while (0)
 template <typename T>
 __device__ __forceinline__ V8<T> zero8() {
   V8<T> v;

@@ -534,6 +534,7 @@ extern "C" size_t pdb_bn_stats_scratch_bytes(int C) {
 
 extern "C" int pdb_bn_stats(const void* x, int dtype, int64_t rows, int C, float* sums, void* scratch,
                             size_t scratch_bytes, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_bn_stats", x);
   PDB_CHECK_ARG(x && sums && scratch, "pdb_bn_stats: null pointer");
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC, "pdb_bn_stats: C=%d must be a multiple of 8 and <= %d", C, kMaxC);
   PDB_CHECK_ARG(rows > 0, "pdb_bn_stats: rows must be positive");
@@ -553,6 +554,7 @@ extern "C" int pdb_bn_stats(const void* x, int dtype, int64_t rows, int C, float
 extern "C" int pdb_bn_stats_sync(const void* x, int dtype, int64_t rows, int C, float* sums, void* scratch,
                                  size_t scratch_bytes, void* const* staging, void* const* pads, int rank, int world,
                                  int slot_stride, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_bn_stats_sync", x);
   PDB_CHECK_ARG(x && sums && scratch && staging && pads, "pdb_bn_stats_sync: null pointer");
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_stats_sync: bad shape rows=%lld C=%d", (long long)rows, C);
   PDB_CHECK_ARG(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "pdb_bn_stats_sync: bad rank/world");
@@ -576,6 +578,7 @@ extern "C" size_t pdb_bn_bwd_reduce_scratch_floats(int C) { return (size_t)kRedu
 extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, int dtype,
                                  int64_t rows, int C, const float* mean, const float* rstd, float* dsums,
                                  float* scratch, const pdb_sync_peers* sync, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_bn_bwd_reduce", dz, z, x);
   PDB_CHECK_ARG(dz && x && mean && rstd && dsums, "pdb_bn_bwd_reduce: null pointer");
   SyncPeers sp{};
   if (sync && sync->world > 1) {
@@ -612,6 +615,7 @@ extern "C" int pdb_bn_bwd_reduce(const void* dz, const void* z, const uint8_t* r
 extern "C" int pdb_bn_bwd_reduce_det(const void* dz, const void* z, const uint8_t* relu_mask, const void* x, int dtype,
                                      int64_t rows, int C, const float* mean, const float* rstd, float* dsums,
                                      void* scratch, size_t scratch_bytes, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_bn_bwd_reduce_det", dz, z, x);
   PDB_CHECK_ARG(dz && x && mean && rstd && dsums && scratch, "pdb_bn_bwd_reduce_det: null pointer");
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_bwd_reduce_det: bad shape rows=%lld C=%d",
                 (long long)rows, C);
@@ -642,6 +646,7 @@ extern "C" int pdb_bn_apply(const void* x, const void* residual, void* y, int dt
                             const float* sums, double count, const float* gamma, const float* beta, float eps,
                             float momentum, float* running_mean, float* running_var, int64_t* num_batches_tracked,
                             float* save_mean, float* save_rstd, int relu, uint8_t* relu_mask, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_bn_apply", x, residual, y);
   PDB_CHECK_ARG(x && y && sums && gamma && beta, "pdb_bn_apply: null pointer");
   PDB_CHECK_ARG(!relu_mask || (relu && bn_fast_ok(C)),
                 "pdb_bn_apply: relu_mask needs relu and a channel count whose 8-channel groups divide 256 (C=%d)", C);
@@ -686,6 +691,7 @@ extern "C" int pdb_bn_apply(const void* x, const void* residual, void* y, int dt
 extern "C" int pdb_bn_apply_eval(const void* x, const void* residual, void* y, int dtype, int64_t rows, int C,
                                  const float* running_mean, const float* running_var, const float* gamma,
                                  const float* beta, float eps, int relu, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_bn_apply_eval", x, residual, y);
   PDB_CHECK_ARG(x && y && running_mean && running_var && gamma && beta, "pdb_bn_apply_eval: null pointer");
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0, "pdb_bn_apply_eval: bad shape");
   const int64_t nvec = rows * C / 8;
@@ -725,6 +731,7 @@ extern "C" int pdb_bn_bwd_apply(const void* dz, const void* z, const uint8_t* re
                                 void* dres, int dtype, int64_t rows, int C, const float* mean, const float* rstd,
                                 const float* gamma, const float* dsums, double count, float* dgamma, float* dbeta,
                                 void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_bn_bwd_apply", dz, z, x, dx, dres);
   PDB_CHECK_ARG(dz && x && dx && mean && rstd && gamma && dsums, "pdb_bn_bwd_apply: null pointer");
   PDB_CHECK_ARG(!relu_mask || bn_fast_ok(C), "pdb_bn_bwd_apply: relu_mask needs a power-of-two channel count (C=%d)", C);
   PDB_CHECK_ARG(C > 0 && C % 8 == 0 && C <= kMaxC && rows > 0 && count > 0, "pdb_bn_bwd_apply: bad shape");
@@ -802,6 +809,7 @@ static void* g_noalloc_ptr[kMaxDevices] = {};      // per-device address of g_bn
 }  // namespace pdb
 
 extern "C" int pdb_bn_stats_noalloc(const void* x, int dtype, int64_t rows, int C, float* sums, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_bn_stats_noalloc", x);
   PDB_CHECK_ARG(x && sums, "pdb_bn_stats_noalloc: null pointer");
   PDB_CHECK_ARG(C > 0 && C % 8 == 0, "pdb_bn_stats_noalloc: C=%d must be a positive multiple of 8", C);
   PDB_CHECK_ARG(C <= kNoAllocMaxC,

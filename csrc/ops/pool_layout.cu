@@ -317,6 +317,7 @@ using namespace pdb;
 
 extern "C" int pdb_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int dtype, int N, int H, int W, int C,
                                     void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_maxpool3x3s2_fwd", x, y);
   PDB_CHECK_ARG(x && y && argmax && N > 0 && H > 0 && W > 0 && C % 8 == 0, "pdb_maxpool3x3s2_fwd: bad arguments");
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   PDB_CHECK_ARG((int64_t)N * Ho < (1ll << 31), "pdb_maxpool3x3s2_fwd: too many rows");
@@ -327,6 +328,7 @@ extern "C" int pdb_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int
 
 extern "C" int pdb_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int dtype, int N, int H, int W,
                                     int C, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_maxpool3x3s2_bwd", dy, dx);
   PDB_CHECK_ARG(dy && dx && argmax && N > 0 && H > 0 && W > 0 && C % 8 == 0, "pdb_maxpool3x3s2_bwd: bad arguments");
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   PDB_CHECK_ARG((int64_t)N * H < (1ll << 31), "pdb_maxpool3x3s2_bwd: too many rows");
@@ -336,6 +338,7 @@ extern "C" int pdb_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void*
 }
 
 extern "C" int pdb_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW, int C, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_avgpool_fwd", x, y);
   PDB_CHECK_ARG(x && y && N > 0 && HW > 0 && C % 8 == 0, "pdb_avgpool_fwd: bad arguments");
   PDB_DISPATCH_ACT(dtype, T, (avgpool_fwd_kernel<T><<<ew_grid((int64_t)N * C / 8, 128), 128, 0, ST>>>((const T*)x, (T*)y,
                                                                                                       N, HW, C)));
@@ -344,6 +347,7 @@ extern "C" int pdb_avgpool_fwd(const void* x, void* y, int dtype, int N, int HW,
 }
 
 extern "C" int pdb_avgpool_bwd(const void* dy, void* dx, int dtype, int N, int HW, int C, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_avgpool_bwd", dy, dx);
   PDB_CHECK_ARG(dy && dx && N > 0 && HW > 0 && C % 8 == 0, "pdb_avgpool_bwd: bad arguments");
   PDB_DISPATCH_ACT(dtype, T, (avgpool_bwd_kernel<T><<<ew_grid((int64_t)N * HW * C / 8), 256, 0, ST>>>((const T*)dy,
                                                                                                       (T*)dx, N, HW, C)));
@@ -359,6 +363,7 @@ extern "C" int pdb_nchw_f32_to_nhwc16(const float* x, void* y, int dtype, int N,
 }
 
 extern "C" int pdb_stem_im2col(const float* x, void* col, int dtype, int N, int H, int W, int Kpad, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_stem_im2col", col);
   PDB_CHECK_ARG(x && col && N > 0 && H > 0 && W > 0 && Kpad >= 147 && Kpad % 8 == 0, "pdb_stem_im2col: bad arguments");
   PDB_CHECK_ARG(Kpad <= 160, "pdb_stem_im2col: Kpad must be <= 160");
   const int Ho = (H + 6 - 7) / 2 + 1, Wo = (W + 6 - 7) / 2 + 1;
@@ -370,6 +375,7 @@ extern "C" int pdb_stem_im2col(const float* x, void* col, int dtype, int N, int 
 }
 
 extern "C" int pdb_add16(const void* a, const void* b, void* out, int dtype, int64_t n, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_add16", a, b, out);
   PDB_CHECK_ARG(a && b && out && n > 0 && n % 8 == 0, "pdb_add16: bad arguments");
   PDB_DISPATCH_ACT(dtype, T, (add16_kernel<T><<<(int)((n / 8 + (dtype == PDB_FP32 ? 1023 : 2047)) / (dtype == PDB_FP32 ? 1024 : 2048)), 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out, n / 8)));
   PDB_LAUNCH_CHECK();
@@ -377,6 +383,7 @@ extern "C" int pdb_add16(const void* a, const void* b, void* out, int dtype, int
 }
 
 extern "C" int pdb_upsample2_zero(const void* src, void* dst, int dtype, int N, int Ho, int Wo, int C, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_upsample2_zero", src, dst);
   PDB_CHECK_ARG(src && dst && N > 0 && Ho > 0 && Wo > 0 && C % 8 == 0, "pdb_upsample2_zero: bad arguments");
   PDB_CHECK_ARG((int64_t)N * Ho * 2 < (1ll << 31), "pdb_upsample2_zero: too many rows");
   PDB_DISPATCH_ACT(dtype, T, (upsample2_kernel<T><<<N * Ho * 2, 256, 0, ST>>>((const T*)src, (T*)dst, Ho, Wo, C)));
@@ -386,6 +393,7 @@ extern "C" int pdb_upsample2_zero(const void* src, void* dst, int dtype, int N, 
 
 extern "C" int pdb_add_strided2(const void* a, const void* b, void* out, int dtype, int N, int H, int W, int C,
                                 void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_add_strided2", a, b, out);
   PDB_CHECK_ARG(a && b && out && N > 0 && H % 2 == 0 && W % 2 == 0 && C % 8 == 0, "pdb_add_strided2: bad arguments");
   PDB_CHECK_ARG((int64_t)N * H < (1ll << 31), "pdb_add_strided2: too many rows");
   PDB_DISPATCH_ACT(dtype, T, (add_strided2_kernel<T><<<N * H, 256, 0, ST>>>((const T*)a, (const T*)b, (T*)out, H, W, C)));
@@ -505,6 +513,7 @@ extern "C" int pdb_weight_dgrad_layout_batched(const void* w_base, void* wt_base
 }
 
 extern "C" int pdb_stem_s2d(const float* x, void* xs, int dtype, int N, int H, int W, void* stream) {
+  PDB_CHECK_ALIGN32(dtype, "pdb_stem_s2d", xs);
   PDB_CHECK_ARG(x && xs && N > 0 && H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0, "pdb_stem_s2d: H and W must be even");
   PDB_CHECK_ARG((reinterpret_cast<uintptr_t>(x) & 7) == 0, "pdb_stem_s2d: input must be 8-byte aligned");
   PDB_DISPATCH_ACT(dtype, T, (stem_s2d_kernel<T><<<N * (H / 2), 128, 0, ST>>>(x, (T*)xs, H, W)));

@@ -156,3 +156,22 @@ def test_folder_loader_worker_processes_match_worker_threads(tmp_path):
     finally:
         lp.close()
     assert lp._pool is None
+
+
+def test_synthetic_loader_recycles_sample_buffers_but_not_labels():
+    """Default mode for transform-free synthetic data: after the first ring of batches the pinned sample buffers are
+    re-used as they are (no 240 MB host gather per step), while every batch still carries the labels of ITS indices."""
+    from pytorch_distributed_b200.data.dataset import _label_of
+    ds = SyntheticImageNet("train", num_samples=8 * 12, image_size=8, num_classes=10, pool=8)
+    loader = ds.loader(8, num_workers=2, prefetch=1)          # ring = prefetch + 3 = 4 slots
+    assert loader.mode == "recycle"
+    seen = []
+    for b, (x, y) in enumerate(loader):
+        idx = torch.arange(b * 8, (b + 1) * 8)
+        assert torch.equal(y, _label_of(idx, 10) % 10), b
+        if b < 4:
+            assert torch.equal(x[0], ds[b * 8][0])            # the first ring is assembled exactly
+        seen.append(x.data_ptr())
+    assert len(seen) == 12 and seen[4] == seen[0] and seen[9] == seen[1]
+    exact = list(ds.loader(8, num_workers=2, mode="gather"))
+    assert len(exact) == 12
