@@ -135,6 +135,15 @@ __device__ __forceinline__ V8<T> ld8s(const T* p) {           // streaming (read
   }
   return v;
 }
+// Two 128-bit streaming loads per lane for fp32 (the pre-256-bit form): the BN backward reduction, which keeps three
+// input streams of four rows in flight under an 85-register cap, measured 6 % FASTER with it than with LDG.256.
+template <typename T>
+__device__ __forceinline__ V8<T> ld8s_split(const T* p) {
+  V8<T> v;
+#pragma unroll
+  for (int j = 0; j < (int)sizeof(T) / 2; ++j) v.q[j] = ldg128_stream(reinterpret_cast<const uint4*>(p) + j);
+  return v;
+}
 template <typename T>
 __device__ __forceinline__ void st8(T* p, const V8<T>& v) {
   if constexpr (sizeof(T) == 4) {

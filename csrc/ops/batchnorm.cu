@@ -47,10 +47,10 @@ __device__ __forceinline__ void reduce_rows(const T* __restrict__ a, const T* __
       const int64_t r = r0 + u * rstride;
       if (r < rows) {
         const int64_t off = r * C + (int64_t)cg * 8;
-        va[u] = ld8s<T>(a + off);
+        va[u] = MODE == 1 ? ld8s_split<T>(a + off) : ld8s<T>(a + off);
         if (MODE == 1) {
-          vx[u] = ld8s<T>(x + off);
-          if (kMask == 1) vz[u] = ld8s<T>(z + off);
+          vx[u] = ld8s_split<T>(x + off);
+          if (kMask == 1) vz[u] = ld8s_split<T>(z + off);
           if (kMask == 2) vb[u] = __ldg(bits + (off >> 3));
         }
       }
