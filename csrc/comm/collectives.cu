@@ -20,6 +20,8 @@
 // Algorithm per payload size (chosen by the caller, parallel/symm.py): up to 256 KB the ONE-SHOT kernel (every rank
 // reads every copy and keeps the sum: one NVLink latency, no all-gather), above it the two-shot kernel (reduce-scatter
 // + all-gather, through the NVLS multicast address when there is one).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "comm/peer_sync.cuh"
 
@@ -57,8 +59,12 @@ __device__ __forceinline__ void multimem_st(float* mc, const float4& v) {
 // kMulticast: reduce and broadcast through the NVLS multicast address `mc` instead of per-peer loads/stores.
 // trace (nullable): block 0 stamps the global timer at entry, after the first meeting and at exit — inside a training
 // step the first interval is the wait for the slowest rank's backward, the second is the collective itself.
-template <bool kMulticast>
-__global__ void __launch_bounds__(kCommThreads) allreduce_kernel(PeerPtrs pp, float* mc, int rank, int world,
+// kSmall: 256 threads, <= 80 registers (3 CTAs' worth of the register file), 4 requests in flight per thread.  A
+// persistent convolution CTA leaves 27 K registers and ~1,700 thread slots of its SM unused; the 512-thread / 128-register
+// variant needs a WHOLE register file, so behind a convolution it waits for the kernel boundary, while the small variant
+// can start next to it (PDB200_COMM_SMALL_CTA=1, with twice the CTAs).
+template <bool kMulticast, bool kSmall = false>
+__global__ void __launch_bounds__(kSmall ? 256 : kCommThreads, kSmall ? 3 : 1) allreduce_kernel(PeerPtrs pp, float* mc, int rank, int world,
                                                                  int64_t start, int64_t n, float scale,
                                                                  const float* __restrict__ inv_scale,
                                                                  unsigned long long* __restrict__ trace) {
@@ -74,7 +80,7 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_kernel(PeerPtrs pp, fl
   // Latency-bound over NVLink (~2 us per remote access): keep kUnroll independent 16-byte requests in
   // flight per thread (32 CTAs x 512 threads x 8 x 16 B = 2 MB, the bandwidth-delay product of one
   // NVLink direction), issue all loads of a batch before the first add.
-  constexpr int kUnroll = 8;
+  constexpr int kUnroll = kSmall ? 4 : 8;
   const int64_t tile = (int64_t)blockDim.x * kUnroll;
   for (int64_t base = lo + (int64_t)blockIdx.x * tile; base < hi; base += (int64_t)gridDim.x * tile) {
     float4 acc[kUnroll];
@@ -440,7 +446,13 @@ extern "C" int pdb_allreduce_inplace(void* const* bufs, void* const* pads, void*
   cudaStream_t st = (cudaStream_t)stream;
   unsigned long long* tr = nullptr;
   if (g_trace && g_trace_next < g_trace_cap) tr = g_trace + 3 * (g_trace_next++);
-  if (multicast)
+  static const bool small_cta = [] { const char* e = getenv("PDB200_COMM_SMALL_CTA"); return e && e[0] == '1'; }();
+  if (small_cta) {
+    if (multicast)
+      allreduce_kernel<true, true><<<blocks, 256, 0, st>>>(pp, static_cast<float*>(multicast), rank, world, start, n, scale, inv_scale, tr);
+    else
+      allreduce_kernel<false, true><<<blocks, 256, 0, st>>>(pp, nullptr, rank, world, start, n, scale, inv_scale, tr);
+  } else if (multicast)
     allreduce_kernel<true><<<blocks, kCommThreads, 0, st>>>(pp, static_cast<float*>(multicast), rank, world, start, n, scale, inv_scale, tr);
   else
     allreduce_kernel<false><<<blocks, kCommThreads, 0, st>>>(pp, nullptr, rank, world, start, n, scale, inv_scale, tr);

@@ -75,7 +75,8 @@ class NativeComm:
         self._sync.rank, self._sync.world, self._sync.slot_stride, self._sync.row = self.rank, self.world, self.slot, 0
         self.oneshot_bytes = int(os.environ.get("PDB200_ONESHOT_BYTES", str(256 << 10)))
         self.use_multicast = os.environ.get("PDB200_NVLS", "1") != "0"
-        self.blocks = int(os.environ.get("PDB200_COMM_BLOCKS", "32"))
+        # PDB200_COMM_SMALL_CTA=1: 256-thread / 80-register CTAs that fit beside a persistent convolution CTA, twice as many
+        self.blocks = int(os.environ.get("PDB200_COMM_BLOCKS", "64" if os.environ.get("PDB200_COMM_SMALL_CTA") == "1" else "32"))
         self._wire: Dict[torch.dtype, tuple] = {}       # wire dtype -> (mapped staging, half_elems)
         self._events: List[torch.cuda.Event] = []
         self._pass_started = False
