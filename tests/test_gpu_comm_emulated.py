@@ -219,3 +219,24 @@ def test_dp_peer_pull_and_reduce_to_root_one_device():
     ops.reduce_to_root(root, peers)
     torch.cuda.synchronize()
     assert rel_err(root, want) < 1e-6
+
+
+def test_allreduce_trace_stamps_are_ordered():
+    """--profile support: while a trace buffer is set, every two-shot launch stamps entry / first meeting / exit."""
+    L = require()
+    world, n = 2, 1 << 16
+    e = Emu(world, n, seed=10)
+    trace = torch.zeros(3 * 8, dtype=torch.int64, device="cuda")
+    L.pdb_comm_set_trace(ptr(trace), 8)
+    try:
+        bufs, pads, flags = e.arr(e.bufs), e.arr(e.pads), e.arr(e.flags)
+        for _ in range(2):
+            e.each(lambda r, st: check(L.pdb_allreduce_inplace(bufs, pads, flags, None, r, world, 0, n, 1.0, None, 4, st), "allreduce"))
+    finally:
+        used = L.pdb_comm_set_trace(None, 0)
+    assert used == 4
+    t = trace.view(-1, 3).cpu()
+    for i in range(4):
+        a, b, c = (int(v) for v in t[i])
+        assert 0 < a <= b <= c and c - a < 5_000_000_000, (i, a, b, c)
+    assert int(t[4:].abs().sum()) == 0
