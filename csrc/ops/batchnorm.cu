@@ -17,6 +17,9 @@ namespace pdb {
 
 int fill_sync(SyncPeers* sp, void* const* staging, void* const* pads, int rank, int world, int slot_stride, int row);   // collectives.cu
 
+#ifndef PDB_BN_REDUCE_MINBLOCKS
+#define PDB_BN_REDUCE_MINBLOCKS 3      // resident blocks per SM the backward reduction is compiled for (85 registers)
+#endif
 constexpr int kThreads = 256;
 constexpr int kMaxC = 4096;
 
@@ -210,7 +213,7 @@ __global__ void __launch_bounds__(kThreads) bn_stats_sync_kernel(const T* __rest
 constexpr int kReduceReplicas = 16;
 
 template <typename T, int kMask>
-__global__ void __launch_bounds__(kThreads, 3) bn_bwd_reduce_kernel(const T* __restrict__ dz, const T* __restrict__ z,
+__global__ void __launch_bounds__(kThreads, PDB_BN_REDUCE_MINBLOCKS) bn_bwd_reduce_kernel(const T* __restrict__ dz, const T* __restrict__ z,
                                                                     const uint8_t* __restrict__ bits,
                                                                     const T* __restrict__ x, int64_t rows, int C, int cx,
                                                                     int ry, const float* __restrict__ mean,
