@@ -20,6 +20,8 @@
 // statistics pass of the delegate's BN kernel (torch:nn/modules/batchnorm.py:144-210 over cuDNN) disappears.
 //
 // Delegates being replaced: cuDNN 9.22 convolutions and cuBLAS(Lt) linear.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "tc05.cuh"
 #include "comm/peer_sync.cuh"
@@ -110,16 +112,23 @@ struct FpropParams {
 // ES: bytes per output element.  The epilogue stages the tile in boxes of 128 rows x 128 B (64 16-bit or 32 fp32
 // columns); a pass is at most 32 KB of them (128 16-bit or 64 fp32 columns), so that a wide tile does not spend
 // pipeline stages on staging.
-template <int BLOCK_N, bool kPair = false, int ES = 2>
+// kTwoOut: TWO staging buffers used alternately, so that the TMA store of pass i reads its buffer while pass i+1 is
+// being converted into the other one (one buffer: every pass first waits until the previous store has drained it).
+// Paid for with pipeline stages, so it is the variant for the short-K layers (<= 4 k-blocks per tile), where the
+// epilogue, not the main loop, sets the tile rate and two or three stages in flight are all the main loop can use.
+template <int BLOCK_N, bool kPair = false, int ES = 2, bool kTwoOut = false>
 struct FpropSmem {
   static constexpr uint32_t B_STAGE_BYTES = (kPair ? BLOCK_N / 2 : BLOCK_N) * 128;
   static constexpr uint32_t STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int BOX_N = 128 / ES;                               // columns per staging box: 64 / 32
   static constexpr int PASS_MAX = 2 * BOX_N;                           // two boxes per pass
   static constexpr int PASS_N = BLOCK_N < PASS_MAX ? BLOCK_N : PASS_MAX;   // columns staged per epilogue pass
-  static constexpr int kStages = kPair ? (BLOCK_N == 256 ? 6 : 8) : (BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8));
   static constexpr uint32_t OUT_BYTES = (PASS_N / BOX_N) * 16384;      // 128 rows x 128 B per box
-  static constexpr uint32_t BAR_OFFSET = kStages * STAGE_BYTES + OUT_BYTES;
+  static constexpr int OUT_BUFS = kTwoOut ? 2 : 1;
+  static constexpr int kNominal = kPair ? (BLOCK_N == 256 ? 6 : 8) : (BLOCK_N == 256 ? 4 : (BLOCK_N == 128 ? 6 : 8));
+  static constexpr int kFit = (int)((232448u - 1280u - OUT_BUFS * OUT_BYTES) / STAGE_BYTES);     // 227 KB per CTA
+  static constexpr int kStages = kNominal < kFit ? kNominal : kFit;
+  static constexpr uint32_t BAR_OFFSET = kStages * STAGE_BYTES + OUT_BUFS * OUT_BYTES;
   static constexpr uint32_t TOTAL = BAR_OFFSET + 256 + 1024;           // barriers + alignment slack
 };
 
@@ -142,7 +151,7 @@ __device__ __forceinline__ float2 unpack2(uint32_t w) {
 // kStem: the 7x7/2 stem as a 4x4/1 convolution over the space-to-depth input (16 channels per pixel, see
 // pdb_stem_fprop): a pipeline stage holds one row of four filter taps, each tap a [128 pixels x 32 B] block (A) and a
 // [64 couts x 32 B] block (B) in 32-byte-swizzled K-major layout; one MMA (K = 16) consumes one tap.
-template <int BLOCK_N, int kFmt, bool kPair, bool kStem = false>
+template <int BLOCK_N, int kFmt, bool kPair, bool kStem = false, bool kTwoOut = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const __grid_constant__ CUtensorMap tmD, const FpropParams p) {
@@ -150,7 +159,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   constexpr bool kTf32 = kFmt == kFmtTf32;
   constexpr int BLOCK_K = F::BLOCK_K, UMMA_K = F::UMMA_K;
   static_assert(!(kStem && kTf32), "the space-to-depth stem kernels are 16-bit only");
-  using L = FpropSmem<BLOCK_N, kPair, F::ES>;
+  static_assert(!(kStem && kTwoOut), "the stem kernel keeps one staging buffer");
+  using L = FpropSmem<BLOCK_N, kPair, F::ES, kTwoOut>;
   // pair mode: rank 0 is the leader (issues the MMAs, owns the full / tmem-empty barriers that are waited on)
   const uint32_t rank = kPair ? cluster_ctarank() : 0u;
   const int unit = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;        // tile-walking unit: CTA or CTA pair
@@ -348,7 +358,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
     };
     int acc = 0;
-    uint32_t acc_phase = 0;
+    uint32_t acc_phase = 0, obuf = 0;          // obuf: staging buffer of the current pass (kTwoOut: alternates)
     TileWalk walk(unit, num_units, num_tiles, p.tile_period);
     for (int tile; walk.next(tile);) {
       const int m_unit = (int)p.div_nb.div((uint32_t)tile), n_blk = tile - m_unit * p.num_n_blocks;
@@ -381,8 +391,13 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             else mbar_arrive(tempty + acc);
           }
         }
-        // the previous TMA store must have finished reading the staging buffer
-        if (leader) tma_store_wait_read0();
+        // the store that last used this staging buffer must have finished reading it
+        const uint32_t ob = kTwoOut ? obuf * L::OUT_BYTES : 0u;
+        if (kTwoOut) obuf ^= 1u;
+        if (leader) {
+          if (kTwoOut) tma_store_wait_read1();
+          else tma_store_wait_read0();
+        }
         named_bar_sync(1, kEpiThreads);
 #pragma unroll
         for (int b = 0; b < GPP; ++b) {
@@ -396,14 +411,14 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
           if (kTf32) {
             // fp32 output: this warp's 32 columns are one full 128-byte row of box lg
-            const uint32_t dst = out_stage_s + lg * 16384 + row * 128;
+            const uint32_t dst = out_stage_s + ob + lg * 16384 + row * 128;
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
               const uint4 w = make_uint4(v[b][4 * c], v[b][4 * c + 1], v[b][4 * c + 2], v[b][4 * c + 3]);
               sts128(dst + ((c ^ (row & 7)) << 4), w);
             }
           } else {
-            const uint32_t dst = out_stage_s + (lg >> 1) * 16384 + row * 128;
+            const uint32_t dst = out_stage_s + ob + (lg >> 1) * 16384 + row * 128;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {               // four 16-byte chunks of this group's half row
               uint4 w;
@@ -423,9 +438,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int nc = n0 + ps * PASS_N + j * BOX_N;
             if (nc < p.N) {
               if (p.accumulate)
-                tma_reduce_add_2d(&tmD, out_stage + j * 16384, nc, m_blk * BLOCK_M);
+                tma_reduce_add_2d(&tmD, out_stage + ob + j * 16384, nc, m_blk * BLOCK_M);
               else
-                tma_store_2d(&tmD, out_stage + j * 16384, nc, m_blk * BLOCK_M);
+                tma_store_2d(&tmD, out_stage + ob + j * 16384, nc, m_blk * BLOCK_M);
             }
           }
           tma_store_commit();
@@ -439,7 +454,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           for (int rb = 0; rb < BLOCK_M / 8; ++rb) {     // 8 rows per step: rows rg + 8*rb + i*G
 #pragma unroll
             for (int i = 0; i < SWZ; ++i) {
-              const float2 f = kTf32 ? lds64f(st_off[i] + rb * (8 * 128)) : unpack2<kFmt>(lds32(st_off[i] + rb * (8 * 128)));
+              const float2 f = kTf32 ? lds64f(st_off[i] + ob + rb * (8 * 128)) : unpack2<kFmt>(lds32(st_off[i] + ob + rb * (8 * 128)));
               st_sum[ps] = __fadd2_rn(st_sum[ps], f);
               st_sq[ps] = __ffma2_rn(f, f, st_sq[ps]);
             }
@@ -824,15 +839,15 @@ static int walk_period(int units, int n_blocks) {
   return n_blocks / a;          // n_blocks / gcd(units, n_blocks)
 }
 
-template <int kFmt>
+template <int kFmt, bool kTwoOut = false>
 static int launch_fprop_pair(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, FpropParams p,
                              cudaStream_t st) {
   constexpr int BN = 256;
   static bool configured[64] = {};
-  auto kernel = conv_fprop_kernel<BN, kFmt, true>;
+  auto kernel = conv_fprop_kernel<BN, kFmt, true, false, kTwoOut>;
   int dev = 0;
   PDB_CUDA(cudaGetDevice(&dev));
-  const uint32_t smem = FpropSmem<BN, true, Fmt<kFmt>::ES>::TOTAL;
+  const uint32_t smem = FpropSmem<BN, true, Fmt<kFmt>::ES, kTwoOut>::TOTAL;
   if (!configured[dev & 63]) {
     if (int e = set_smem(kernel, smem)) return e;
     configured[dev & 63] = true;
@@ -854,14 +869,14 @@ static int launch_fprop_pair(const CUtensorMap& a, const CUtensorMap& b, const C
   return 0;
 }
 
-template <int BLOCK_N, int kFmt, bool kStem = false>
+template <int BLOCK_N, int kFmt, bool kStem = false, bool kTwoOut = false>
 static int launch_fprop(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, FpropParams p,
                         cudaStream_t st) {
   // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute (the single-process
   // DataParallel mode launches from one process on every GPU)
   static bool configured[64] = {};
-  auto kernel = conv_fprop_kernel<BLOCK_N, kFmt, false, kStem>;
-  constexpr uint32_t smem = FpropSmem<BLOCK_N, false, Fmt<kFmt>::ES>::TOTAL;
+  auto kernel = conv_fprop_kernel<BLOCK_N, kFmt, false, kStem, kTwoOut>;
+  constexpr uint32_t smem = FpropSmem<BLOCK_N, false, Fmt<kFmt>::ES, kTwoOut>::TOTAL;
   int dev = 0;
   PDB_CUDA(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
@@ -963,17 +978,26 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
                             CU_TENSOR_MAP_SWIZZLE_128B, false)) return e;
 
   cudaStream_t st = (cudaStream_t)stream;
-  if (pair)
+  // short reductions (<= 4 k-blocks per tile): the epilogue bounds the tile rate -> two staging buffers, fewer stages.
+  // PDB200_FPROP_TWO_OUT = 0 / 1 forces the choice (A/B timing).
+  static const int two_out_env = [] { const char* e = getenv("PDB200_FPROP_TWO_OUT"); return e ? atoi(e) : -1; }();
+  const bool two_out = two_out_env >= 0 ? two_out_env != 0 : (p.taps * p.cin_blocks <= 4 && bn >= 128);
+  if (pair) {
+    if (two_out)
+      return dtype == PDB_BF16   ? launch_fprop_pair<0, true>(tmA, tmB, tmD, p, st)
+             : dtype == PDB_FP16 ? launch_fprop_pair<1, true>(tmA, tmB, tmD, p, st)
+                                 : launch_fprop_pair<2, true>(tmA, tmB, tmD, p, st);
     return dtype == PDB_BF16   ? launch_fprop_pair<0>(tmA, tmB, tmD, p, st)
            : dtype == PDB_FP16 ? launch_fprop_pair<1>(tmA, tmB, tmD, p, st)
                                : launch_fprop_pair<2>(tmA, tmB, tmD, p, st);
-#define GO(BN)                                                           \
-  (dtype == PDB_BF16   ? launch_fprop<BN, 0>(tmA, tmB, tmD, p, st)       \
-   : dtype == PDB_FP16 ? launch_fprop<BN, 1>(tmA, tmB, tmD, p, st)       \
-                       : launch_fprop<BN, 2>(tmA, tmB, tmD, p, st))
-  if (bn == 64) return GO(64);
-  if (bn == 128) return GO(128);
-  return GO(256);
+  }
+#define GO(BN, TWO)                                                                  \
+  (dtype == PDB_BF16   ? launch_fprop<BN, 0, false, TWO>(tmA, tmB, tmD, p, st)       \
+   : dtype == PDB_FP16 ? launch_fprop<BN, 1, false, TWO>(tmA, tmB, tmD, p, st)       \
+                       : launch_fprop<BN, 2, false, TWO>(tmA, tmB, tmD, p, st))
+  if (bn == 64) return GO(64, false);
+  if (bn == 128) return two_out ? GO(128, true) : GO(128, false);
+  return two_out ? GO(256, true) : GO(256, false);
 #undef GO
 }
 
