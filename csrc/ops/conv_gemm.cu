@@ -978,10 +978,12 @@ extern "C" int pdb_conv_fprop(const void* x, const void* w, void* y, int dtype, 
                             CU_TENSOR_MAP_SWIZZLE_128B, false)) return e;
 
   cudaStream_t st = (cudaStream_t)stream;
-  // short reductions (<= 4 k-blocks per tile): the epilogue bounds the tile rate -> two staging buffers, fewer stages.
-  // PDB200_FPROP_TWO_OUT = 0 / 1 forces the choice (A/B timing).
-  static const int two_out_env = [] { const char* e = getenv("PDB200_FPROP_TWO_OUT"); return e ? atoi(e) : -1; }();
-  const bool two_out = two_out_env >= 0 ? two_out_env != 0 : (p.taps * p.cin_blocks <= 4 && bn >= 128);
+  // Two alternating staging buffers (store of pass i overlaps the conversion of pass i+1, paid for with one pipeline
+  // stage): measured on all 22 shapes in both precisions, -4..-6 % on two short-K layers (128->512, 256->1024) and
+  // +2..+17 % on everything with a longer reduction — the store wait is not what bounds the epilogue.  Off unless
+  // PDB200_FPROP_TWO_OUT=1 (kept for A/B timing and because it is tested).
+  static const int two_out_env = [] { const char* e = getenv("PDB200_FPROP_TWO_OUT"); return e ? atoi(e) : 0; }();
+  const bool two_out = two_out_env != 0 && bn >= 128;
   if (pair) {
     if (two_out)
       return dtype == PDB_BF16   ? launch_fprop_pair<0, true>(tmA, tmB, tmD, p, st)
