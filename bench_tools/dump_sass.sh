@@ -18,8 +18,9 @@ declare -A K=(
 )
 names=$(cuobjdump -sass $SO | grep -o "Function : .*" | sed 's/Function : //')
 pick() { echo "$names" | grep -E "$1" | head -1; }
-K[allreduce_nvls]=$(pick 'allreduce_kernelILb1E')
-K[allreduce_p2p]=$(pick 'allreduce_kernelILb0E')
+K[allreduce_nvls]=$(pick 'allreduce_kernelILb1ELb0E')
+K[allreduce_p2p]=$(pick 'allreduce_kernelILb0ELb0E')
+K[allreduce_nvls_smallcta]=$(pick 'allreduce_kernelILb1ELb1E')
 K[allreduce_oneshot]=$(pick 'allreduce_oneshot_kernel')
 K[allreduce_wire16_bf16]=$(pick 'allreduce_wire16_kernelI13__nv_bfloat16')
 K[small_allreduce]=$(pick 'small_allreduce_kernel')
