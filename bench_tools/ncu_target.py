@@ -98,9 +98,11 @@ def main():
         from pytorch_distributed_b200.nn import CrossEntropyLoss
         from pytorch_distributed_b200.optim import SGD
         dev = torch.device("cuda", 0)
-        cfg = TrainConfig(mode="ddp_amp", batch_size=N, dtype="bf16", device="cuda")
+        name = {"step_fp16": "fp16", "step_fp32": "fp32"}.get(what, "bf16")          # step | step_fp16 | step_fp32
+        cfg = TrainConfig(mode="single" if name == "fp32" else "ddp_amp", batch_size=N, dtype=name, device="cuda")
         model = harness.build_model(cfg, dev)
-        model.enable_native(batch_size=N, dtype=dt)
+        os.environ["PDB200_GRAPHS"] = "0"            # eager launches: every kernel shows up by name
+        model.enable_native(batch_size=N, dtype=harness.torch_dtype(cfg))
         opt = SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
         sc = amp.GradScaler(device=dev)
         crit = CrossEntropyLoss()
