@@ -201,6 +201,10 @@ class NativeComm:
                 self._trace = torch.zeros(3 * 4096, dtype=torch.int64, device=self.device)
                 require().pdb_comm_set_trace(ptr(self._trace), 4096)
                 self._trace_read = 0
+            if t0 is None and self._trace is not None:
+                # profiling was switched off: stop stamping, so that marks and stamps stay paired when it comes back
+                require().pdb_comm_set_trace(None, 0)
+                self._trace = None
             traced = t0 is not None and self._trace is not None
             check(require().pdb_allreduce_inplace(
                 m.bufs, m.pads, self._flag_ptrs if found_inf is not None else None,
