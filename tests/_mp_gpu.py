@@ -100,7 +100,9 @@ def comm_worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
-def ddp_native_worker(rank, world, port, out_dir, backend, sync_bn):
+def ddp_native_worker(rank, world, port, out_dir, backend, sync_bn, precise=False):
+    """precise: the `ddp` mode as the reference runs it (fp32, no loss scaling) on the DETERMINISTIC engine — the two
+    comm backends then differ only in the association of the cross-rank sum, so the runs can be held to 1e-2."""
     dist = _init(rank, world, port)
     from pytorch_distributed_b200 import amp, harness
     from pytorch_distributed_b200.config import TrainConfig
@@ -108,13 +110,16 @@ def ddp_native_worker(rank, world, port, out_dir, backend, sync_bn):
     from pytorch_distributed_b200.optim import SGD
     from pytorch_distributed_b200.parallel import DistributedDataParallel
     dev = torch.device("cuda", rank)
-    cfg = TrainConfig(mode="ddp_amp", batch_size=16, dtype="bf16", device="cuda", seed=7 + rank, sync_bn=sync_bn)
+    cfg = TrainConfig(mode="ddp" if precise else "ddp_amp", batch_size=16, dtype="fp32" if precise else "bf16", device="cuda",
+                      seed=7 + rank, sync_bn=sync_bn)
     model = harness.build_model(cfg, dev)            # different init per rank: the ctor broadcast must fix it
-    model.enable_native(batch_size=16, dtype=torch.bfloat16, sync_bn=sync_bn)
+    model.enable_native(batch_size=16, dtype=harness.torch_dtype(cfg), sync_bn=sync_bn, deterministic=precise)
     ddp = DistributedDataParallel(model, device_ids=[rank], backend=backend)
     opt = SGD(ddp.parameters(), lr=0.01, momentum=0.9, weight_decay=1e-4)
-    sc = amp.GradScaler(device=dev)
-    ddp.attach_grad_scaler(sc)
+    sc = None
+    if not precise:
+        sc = amp.GradScaler(device=dev)
+        ddp.attach_grad_scaler(sc)
     crit = CrossEntropyLoss()
     g = torch.Generator(device=dev).manual_seed(5)          # same stream on all ranks; each takes its slice
     steps = 5              # two eager steps, then the captured forward / backward graphs are replayed
@@ -130,7 +135,7 @@ def ddp_native_worker(rank, world, port, out_dir, backend, sync_bn):
     arena = model._pdb200_arena
     buckets = ddp.comm.bucket_times() if hasattr(ddp.comm, "bucket_times") else None
     torch.save({"losses": losses, "params": arena.params.detach().cpu().clone(), "comm": ddp.comm.name, "buckets": buckets,
-                "bufs": model._pdb200_buffer_arena.floats.detach().cpu().clone(), "scale": sc.get_scale()},
-               os.path.join(out_dir, f"ddp_{backend}_{int(sync_bn)}_{rank}.pt"))
+                "bufs": model._pdb200_buffer_arena.floats.detach().cpu().clone(), "scale": sc.get_scale() if sc else None},
+               os.path.join(out_dir, f"ddp_{backend}_{int(sync_bn)}{'_precise' if precise else ''}_{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
