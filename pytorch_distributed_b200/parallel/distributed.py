@@ -94,6 +94,7 @@ class DistributedDataParallel(nn.Module):
         self._wire_dtype = _WIRE[comm_dtype]
         self._py_hook = None
         self._hook_results = []
+        self._buf_event = None           # completion of an early (overlapped) buffer broadcast for the next forward
 
         params = [p for p in module.parameters() if p.requires_grad]
         if not params:
@@ -258,16 +259,33 @@ class DistributedDataParallel(nn.Module):
         with torch.autograd.profiler.record_function("pdb200.DistributedDataParallel.forward"):
             if torch.is_grad_enabled() and self.require_backward_grad_sync:
                 self.require_forward_param_sync = True
-            if self.require_forward_param_sync and self.broadcast_buffers and self.world_size > 1 \
-                    and not self._buffers_replicated():
+            need_sync = self.require_forward_param_sync and self.broadcast_buffers and self.world_size > 1 \
+                and not self._buffers_replicated()
+            if self._buf_event is not None:
+                # K3 was already run, on the comm stream, while the previous step's backward was executing (always
+                # waited for, also when this forward would not have asked for it: the copy must not land mid-forward)
+                torch.cuda.current_stream(self.device).wait_event(self._buf_event)
+            elif need_sync:
                 self._sync_buffers()
+            self._buf_event = None
             if not torch.is_grad_enabled():
                 # delegate clears the flag after a no_grad forward (distributed.py:1649-1650), so an
                 # eval loop broadcasts buffers only on its first batch
                 self.require_forward_param_sync = False
             if self.device_ids and inputs and torch.is_tensor(inputs[0]) and inputs[0].device != self.device:
                 inputs = (inputs[0].to(self.device, non_blocking=True),) + tuple(inputs[1:])
-            return self.module(*inputs, **kwargs)
+            out = self.module(*inputs, **kwargs)
+            if need_sync and torch.is_grad_enabled() and self.require_backward_grad_sync and hasattr(self.comm, "broadcast_async"):
+                # The buffers only change in forward.  Rank 0's values — which the NEXT forward must start from
+                # (broadcast_buffers=True, torch:nn/parallel/distributed.py:2214-2257) — are final once this forward
+                # has run, so the broadcast is issued now, behind it, on the comm stream: it overlaps backward
+                # instead of putting a cross-rank meeting at the top of every step.
+                self._buf_event = self.comm.broadcast_async(self.buffer_arena.storage, 0)
+            return out
+
+    def load_state_dict(self, *args, **kwargs):
+        self._buf_event = None                      # loaded buffers must be broadcast afresh at the next forward
+        return super().load_state_dict(*args, **kwargs)
 
     def _get_ddp_logging_data(self):
         return {"bucket_sizes": ", ".join(str((e - s) * 4) for s, e in self.bucket_ranges),

@@ -150,6 +150,22 @@ class NativeComm:
               "pdb_broadcast_inplace")
         count_launch()
 
+    def broadcast_async(self, flat: torch.Tensor, src: int = 0):
+        """The same broadcast on the comm stream, ordered after everything enqueued so far on the current stream; returns
+        the event that marks its completion (or None when nothing was launched).  DDP uses it to refresh the BN buffers
+        for the NEXT forward while this step's backward runs, instead of opening every forward with a cross-rank meeting."""
+        if self.world == 1:
+            return None
+        cur = torch.cuda.current_stream(self.device)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.stream.wait_event(ev)
+        with torch.cuda.stream(self.stream):
+            self.broadcast_(flat, src)
+            done = torch.cuda.Event()
+            done.record(self.stream)
+        return done
+
     def allreduce_range(self, flat: torch.Tensor, start: int, end: int, *, average: bool = True,
                         wire_dtype=None, inv_scale=None, found_inf=None) -> None:
         if self.world == 1:
