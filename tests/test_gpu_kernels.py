@@ -287,3 +287,23 @@ def test_weight_dgrad_layout_batched_matches_permute():
         src = w[o:o + K * R * S * C].view(K, R, S, C)
         want = src.flip(1, 2).permute(3, 1, 2, 0).contiguous()          # [C, R, S, K]
         assert torch.equal(wt[o:o + K * R * S * C].view(C, R, S, K), want), (K, R, S, C)
+
+
+def test_fp16_subnormals_survive_bn_backward():
+    """The library is compiled with -ftz=true (fp32 denormals flush to zero).  That must not touch fp16 SUBNORMAL
+    gradients (|g| < 6.1e-5, what loss scaling exists to protect): widened to fp32 they are ordinary normal numbers, and
+    the residual-branch gradient the BN backward apply kernel passes through (dres = dz under the ReLU mask) must come
+    back bit for bit."""
+    rows, C = 4096, 64
+    g = torch.Generator(device="cuda").manual_seed(21)
+    x = torch.randn(rows, C, device="cuda", generator=g).half()
+    tiny = (torch.rand(rows, C, device="cuda", generator=g) * 5.9e-5 + 6e-8).half()       # all below the fp16 normal range
+    assert float(tiny.float().abs().max()) < 6.104e-5 and float(tiny.float().abs().min()) > 0
+    bits = torch.full((rows * C // 8,), 255, dtype=torch.uint8, device="cuda")            # ReLU passed everywhere
+    mean, rstd, gamma = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda"), torch.ones(C, device="cuda")
+    ds = torch.zeros(2 * C, device="cuda")
+    dx, dres = torch.empty_like(x), torch.empty_like(x)
+    ops.bn_bwd_apply(tiny, None, x, dx, dres, mean, rstd, gamma, ds, rows, None, None, relu_mask=bits)
+    torch.cuda.synchronize()
+    assert torch.equal(dres, tiny)
+    assert torch.equal(dx, tiny)            # zero sums, gamma = rstd = 1: dx = g exactly
