@@ -80,7 +80,9 @@ def layer_tables(path, hbm, burst):
     for k, v in d["by_class"].items():
         out.append(f"| {k} | {v['n']} | {v['ms']:.3f} | {v['tflops'] or ''} |")
     if over:
-        out += ["", f"Fractions above 1.0 (reads served by the 126 MB L2, e.g. a tensor the previous kernel just wrote): {over}"]
+        out += ["", f"Fractions above 1.0: {over}.  Memory fractions: reads served by the 126 MB L2 (e.g. a tensor the previous kernel just "
+                "wrote).  GEMM fractions: the denominator is the rate cuBLAS reached in the driver's 8192^3 measurement, not the hardware's "
+                f"nominal {'1,125 TF32' if fp32 else '2,250 bf16'} TFLOP/s, and a 0.2-0.4 ms kernel runs at boost clocks the 8192^3 GEMM does not hold."]
     return out + [""]
 
 
