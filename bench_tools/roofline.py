@@ -136,11 +136,12 @@ def main():
     ap.add_argument("--layers", nargs="*", default=[])
     ap.add_argument("--comm", default=None)
     ap.add_argument("--steps", default=None)
+    ap.add_argument("--peaks", default=None, help="hbm_gbs,bf16_burst_tflops,bf16_sustained_tflops instead of MEASURED_PEAKS.json")
     args = ap.parse_args()
-    hbm, burst, sustained = peaks()
+    hbm, burst, sustained = map(float, args.peaks.split(",")) if args.peaks else peaks()
     out = ["# Roofline fractions of the step's kernels", "",
-           f"Denominators from `MEASURED_PEAKS.json` (driver-written on this pool): HBM copy bandwidth **{hbm:.0f} GB/s**, cuBLAS bf16 "
-           f"**{burst:.0f} TFLOP/s burst** / {sustained:.0f} sustained.  Generated by `bench_tools/roofline.py` from the files named in each "
+           f"Denominators from `MEASURED_PEAKS.json` (driver-written on this pool): HBM copy bandwidth **{hbm:.1f} GB/s**, cuBLAS bf16 "
+           f"**{burst:.1f} TFLOP/s burst** / {sustained:.1f} sustained.  Generated by `bench_tools/roofline.py` from the files named in each "
            "section; isolated kernels are judged against the burst rate, the whole step (power-capped) against the sustained one.", ""]
     for p in args.layers:
         out += layer_tables(p, hbm, burst)
